@@ -1,0 +1,211 @@
+// api.cu — the C-ABI of libgsrast.so (declared in include/gsrast.h): argument validation,
+// workspace carving, stage orchestration, error strings.  No torch, no allocation.
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+#include "common.cuh"
+
+namespace gsr {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+// After each stage: always pick up launch-configuration errors; in debug mode also
+// synchronise and name the stage (role of CHECK_CUDA, auxiliary.h:193-200).
+int check_stage(const char* stage, bool debug, cudaStream_t stream) {
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess && debug) e = cudaStreamSynchronize(stream);
+    if (e != cudaSuccess) {
+        set_error("[CUDA ERROR] in stage '%s': %s", stage, cudaGetErrorString(e));
+        return GSR_ERR_CUDA;
+    }
+    return GSR_OK;
+}
+
+static int validate(const GsrParams* p, const GsrBuffers* buf) {
+    if (!p || !buf) { set_error("null argument"); return GSR_ERR_INVALID_ARG; }
+    if (p->P <= 0) { set_error("P must be > 0 (P == 0 is handled by the caller)"); return GSR_ERR_INVALID_ARG; }
+    if (p->W <= 0 || p->H <= 0) { set_error("image size must be positive"); return GSR_ERR_INVALID_ARG; }
+    if ((p->W + TILE_X - 1) / TILE_X > 65535 || (p->H + TILE_Y - 1) / TILE_Y > 65535) {
+        set_error("image too large: tile grid exceeds 65535 per axis"); return GSR_ERR_INVALID_ARG;
+    }
+    if (!p->means3D || !p->opacities || !p->background || !p->viewmatrix || !p->projmatrix || !p->campos) {
+        set_error("means3D, opacities, background, viewmatrix, projmatrix, campos are required");
+        return GSR_ERR_INVALID_ARG;
+    }
+    if ((p->shs == nullptr) == (p->colors_precomp == nullptr)) {
+        set_error("Please provide exactly one of either SHs or precomputed colors!");
+        return GSR_ERR_INVALID_ARG;
+    }
+    const bool have_sr = p->scales != nullptr && p->rotations != nullptr;
+    if (have_sr == (p->cov3D_precomp != nullptr) || ((p->scales != nullptr) != (p->rotations != nullptr))) {
+        set_error("Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!");
+        return GSR_ERR_INVALID_ARG;
+    }
+    if (p->shs) {
+        if (p->D < 0 || p->D > 3) { set_error("sh_degree must be in 0..3"); return GSR_ERR_INVALID_ARG; }
+        if (p->M < (p->D + 1) * (p->D + 1) || p->M > 16) {
+            set_error("shs must hold between (sh_degree+1)^2 and 16 coefficients per Gaussian (got M=%d, D=%d)", p->M, p->D);
+            return GSR_ERR_INVALID_ARG;
+        }
+    }
+    if (!buf->geom || buf->geom_bytes < gsr_geom_bytes(p->P)) {
+        set_error("geom buffer too small: %zu < %zu", buf->geom_bytes, gsr_geom_bytes(p->P));
+        return GSR_ERR_CAPACITY;
+    }
+    if (!buf->img || buf->img_bytes < gsr_img_bytes(p->W, p->H)) {
+        set_error("img buffer too small: %zu < %zu", buf->img_bytes, gsr_img_bytes(p->W, p->H));
+        return GSR_ERR_CAPACITY;
+    }
+    return GSR_OK;
+}
+
+static int validate_R(const GsrParams* p, const GsrBuffers* buf, int64_t R) {
+    if (R < 0 || R > 0x7fffffffLL) { set_error("num_rendered out of int32 range"); return GSR_ERR_OVERFLOW; }
+    if (!buf->bin || buf->bin_bytes < gsr_bin_bytes(R)) {
+        set_error("bin buffer too small: %zu < %zu", buf->bin_bytes, gsr_bin_bytes(R));
+        return GSR_ERR_CAPACITY;
+    }
+    if (!buf->scratch || buf->scratch_bytes < gsr_scratch_bytes(p->P, p->W, p->H, R)) {
+        set_error("scratch buffer too small: %zu < %zu", buf->scratch_bytes,
+                  gsr_scratch_bytes(p->P, p->W, p->H, R));
+        return GSR_ERR_CAPACITY;
+    }
+    return GSR_OK;
+}
+
+static inline size_t tiles_of(int W, int H) {
+    return (size_t)((W + TILE_X - 1) / TILE_X) * (size_t)((H + TILE_Y - 1) / TILE_Y);
+}
+
+}  // namespace gsr
+
+using namespace gsr;
+
+extern "C" {
+
+int gsr_version(void) { return GSR_VERSION; }
+const char* gsr_last_error(void) { return g_err; }
+
+size_t gsr_geom_bytes(int32_t P) {
+    size_t b; GeomState::carve(nullptr, (size_t)(P > 0 ? P : 1), &b); return b;
+}
+size_t gsr_img_bytes(int32_t W, int32_t H) {
+    size_t b; ImgState::carve(nullptr, (size_t)W * H, tiles_of(W, H), &b); return b;
+}
+size_t gsr_bin_bytes(int64_t R) {
+    size_t b; BinState::carve(nullptr, (size_t)(R > 0 ? R : 0), &b); return b;
+}
+size_t gsr_scratch_bytes(int32_t P, int32_t W, int32_t H, int64_t R) {
+    (void)W; (void)H;
+    size_t b; Scratch::carve(nullptr, (size_t)(P > 0 ? P : 1), (size_t)(R > 0 ? R : 0), &b); return b;
+}
+
+int32_t gsr_flat_grad_floats(int32_t M) { return 3 + 3 * M + 1 + 3 + 4; }
+
+int gsr_forward_stage1(const GsrParams* p, const GsrBuffers* buf, const GsrForwardOut* out, void* stream) {
+    int rc = validate(p, buf);
+    if (rc) return rc;
+    if (!out || !out->radii) { set_error("radii output is required"); return GSR_ERR_INVALID_ARG; }
+    if (!buf->scratch || buf->scratch_bytes < gsr_scratch_bytes(p->P, p->W, p->H, 0)) {
+        set_error("scratch buffer too small for stage 1: %zu < %zu", buf->scratch_bytes,
+                  gsr_scratch_bytes(p->P, p->W, p->H, 0));
+        return GSR_ERR_CAPACITY;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    GeomState g = GeomState::carve(buf->geom, p->P, nullptr);
+    // the P-sized part of the scratch layout does not depend on R
+    Scratch s = Scratch::carve(buf->scratch, p->P, 0, nullptr);
+    rc = launch_preprocess(*p, g, s, out->radii, st);
+    if (rc) return rc;
+    return launch_depth_order_and_scan(*p, g, s, buf->num_rendered_host, st);
+}
+
+int gsr_forward_stage2(const GsrParams* p, const GsrBuffers* buf, const GsrForwardOut* out, int64_t R,
+                       void* stream) {
+    int rc = validate(p, buf);
+    if (rc) return rc;
+    if (!out || !out->out_color || !out->out_invdepth) {
+        set_error("out_color and out_invdepth are required"); return GSR_ERR_INVALID_ARG;
+    }
+    rc = validate_R(p, buf, R);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    GeomState g = GeomState::carve(buf->geom, p->P, nullptr);
+    ImgState im = ImgState::carve(buf->img, (size_t)p->W * p->H, tiles_of(p->W, p->H), nullptr);
+    BinState b = BinState::carve(buf->bin, (size_t)R, nullptr);
+    Scratch s = Scratch::carve(buf->scratch, p->P, (size_t)R, nullptr);
+    rc = launch_binning(*p, g, im, b, s, R, st);
+    if (rc) return rc;
+    return launch_render_forward(*p, g, im, b, out->out_color, out->out_invdepth, st);
+}
+
+int gsr_forward(const GsrParams* p, const GsrBuffers* buf, const GsrForwardOut* out, int64_t* num_rendered,
+                void* stream) {
+    if (!buf || !buf->num_rendered_host) { set_error("num_rendered_host (pinned) is required"); return GSR_ERR_INVALID_ARG; }
+    int rc = gsr_forward_stage1(p, buf, out, stream);
+    if (rc) return rc;
+    GSR_CUDA_TRY(cudaStreamSynchronize((cudaStream_t)stream));
+    if (buf->num_rendered_host[1]) { set_error("num_rendered exceeds int32"); return GSR_ERR_OVERFLOW; }
+    const int64_t R = buf->num_rendered_host[0];
+    if (num_rendered) *num_rendered = R;
+    return gsr_forward_stage2(p, buf, out, R, stream);
+}
+
+int gsr_backward(const GsrParams* p, const GsrBuffers* buf, int64_t R, const int32_t* radii,
+                 const GsrBackwardIO* io, void* stream) {
+    int rc = validate(p, buf);
+    if (rc) return rc;
+    if (!io || !io->dL_dout_color || !radii) { set_error("dL_dout_color and radii are required"); return GSR_ERR_INVALID_ARG; }
+    rc = validate_R(p, buf, R);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    GeomState g = GeomState::carve(buf->geom, p->P, nullptr);
+    ImgState im = ImgState::carve(buf->img, (size_t)p->W * p->H, tiles_of(p->W, p->H), nullptr);
+    BinState b = BinState::carve(buf->bin, (size_t)R, nullptr);
+    Scratch s = Scratch::carve(buf->scratch, p->P, (size_t)R, nullptr);
+    rc = launch_render_backward(*p, g, im, b, s, io->dL_dout_color, io->dL_dout_invdepth, st);
+    if (rc) return rc;
+    return launch_preprocess_backward(*p, g, s, radii, io->dL_dout_invdepth != nullptr, *io, st);
+}
+
+int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                     uint8_t* present, void* stream) {
+    (void)projmatrix;   // read but unused by the reference's test (auxiliary.h:164-190)
+    if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) { set_error("bad arguments"); return GSR_ERR_INVALID_ARG; }
+    if (P == 0) return GSR_OK;
+    return launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)stream);
+}
+
+int gsr_debug_sorted_keys(const GsrParams* p, const GsrBuffers* buf, int64_t R, uint64_t* keys_out, void* stream) {
+    int rc = validate(p, buf);
+    if (rc) return rc;
+    GeomState g = GeomState::carve(buf->geom, p->P, nullptr);
+    ImgState im = ImgState::carve(buf->img, (size_t)p->W * p->H, tiles_of(p->W, p->H), nullptr);
+    BinState b = BinState::carve(buf->bin, (size_t)R, nullptr);
+    return launch_rebuild_keys(*p, g, im, b, R, keys_out, (cudaStream_t)stream);
+}
+
+int gsr_debug_state_ptrs(const GsrParams* p, const GsrBuffers* buf, int64_t R, const uint32_t** point_list,
+                         const uint32_t** ranges, const float** final_T, const uint32_t** n_contrib,
+                         const float** records) {
+    int rc = validate(p, buf);
+    if (rc) return rc;
+    GeomState g = GeomState::carve(buf->geom, p->P, nullptr);
+    ImgState im = ImgState::carve(buf->img, (size_t)p->W * p->H, tiles_of(p->W, p->H), nullptr);
+    BinState b = BinState::carve(buf->bin, (size_t)R, nullptr);
+    if (point_list) *point_list = b.point_list;
+    if (ranges) *ranges = reinterpret_cast<const uint32_t*>(im.ranges);
+    if (final_T) *final_T = im.final_T;
+    if (n_contrib) *n_contrib = im.n_contrib;
+    if (records) *records = reinterpret_cast<const float*>(g.rec);
+    return GSR_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,366 @@
+// binning.cu — kernel group 2 of the path: depth ordering, tile-count scan, instance
+// emission, stable tile ordering, tile ranges.
+//
+// Replaces cub::DeviceScan::InclusiveSum + duplicateWithKeys + cub::DeviceRadixSort::
+// SortPairs<u64,u32> + identifyTileRanges (DGR/cuda_rasterizer/rasterizer_impl.cu:78-164,
+// 309-350).  The reference sorts R (tile|depth) 64-bit keys in 6 radix passes.  Here the
+// same total order (tile, depth bits, Gaussian id) is produced in two cheaper steps:
+//   1. stable LSD radix sort of the P Gaussians by depth bits (4 passes over P items);
+//   2. instances are emitted in that depth order and then stably ordered by tile id
+//      only: ceil(getHigherMsb(T)/8) passes over R items (2 at every benchmark size).
+// Stability makes the result identical to the reference's stable sort of
+// (tile<<32 | depth) keys with emission order (id, tile) as the tie-break.
+#include "common.cuh"
+
+namespace gsr {
+
+// ---------------------------------------------------------------- block helpers
+__device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, int lane) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t n = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += n;
+    }
+    return v;
+}
+
+// Exclusive scan over the 256 threads of a block. s_w: 8 words of shared memory.
+// All threads must call. Returns exclusive prefix; *total gets the block total.
+__device__ __forceinline__ uint32_t block_excl_scan_256(uint32_t v, uint32_t* s_w, uint32_t* total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t inc = warp_incl_scan(v, lane);
+    __syncthreads();                       // protect s_w reuse
+    if (lane == 31) s_w[warp] = inc;
+    __syncthreads();
+    uint32_t wp = 0, tot = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++) {
+        uint32_t x = s_w[w];
+        if (w < warp) wp += x;
+        tot += x;
+    }
+    if (total) *total = tot;
+    return wp + inc - v;
+}
+
+// ---------------------------------------------------------------- radix sort (u64 items)
+__global__ void __launch_bounds__(SORT_THREADS)
+radix_hist_kernel(const uint64_t* __restrict__ in, uint32_t n, int shift,
+                  uint32_t* __restrict__ hist, uint32_t nb) {
+    __shared__ uint32_t h[256];
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    const uint32_t base = blockIdx.x * SORT_CHUNK;
+#pragma unroll
+    for (int i = 0; i < SORT_ITEMS; i++) {
+        uint32_t idx = base + i * SORT_THREADS + threadIdx.x;
+        if (idx < n) atomicAdd(&h[(uint32_t)(in[idx] >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    hist[threadIdx.x * nb + blockIdx.x] = h[threadIdx.x];
+}
+
+// One block per digit: exclusive scan of its row of per-block counts, in place.
+__global__ void __launch_bounds__(256)
+radix_rowscan_kernel(uint32_t* __restrict__ hist, uint32_t nb, uint32_t* __restrict__ digit_tot) {
+    __shared__ uint32_t s_w[8];
+    uint32_t* row = hist + (size_t)blockIdx.x * nb;
+    const uint32_t seg = (nb + 255) / 256;
+    const uint32_t b0 = threadIdx.x * seg;
+    const uint32_t b1 = min(nb, b0 + seg);
+    uint32_t sum = 0;
+    for (uint32_t b = b0; b < b1; b++) sum += row[b];
+    uint32_t total;
+    uint32_t run = block_excl_scan_256(sum, s_w, &total);
+    for (uint32_t b = b0; b < b1; b++) {
+        uint32_t c = row[b];
+        row[b] = run;
+        run += c;
+    }
+    if (threadIdx.x == 0) digit_tot[blockIdx.x] = total;
+}
+
+// Stable scatter of one 8-bit digit.  SPLIT: final pass, write low word to out_lo
+// (Gaussian id) and high word to out_hi (tile id) instead of the u64 item.
+template <bool SPLIT>
+__global__ void __launch_bounds__(SORT_THREADS)
+radix_scatter_kernel(const uint64_t* __restrict__ in, uint32_t n, int shift,
+                     const uint32_t* __restrict__ hist, uint32_t nb,
+                     const uint32_t* __restrict__ digit_tot,
+                     uint64_t* __restrict__ out, uint32_t* __restrict__ out_lo,
+                     uint32_t* __restrict__ out_hi) {
+    __shared__ uint32_t wh[8][256];
+    __shared__ uint64_t stage[SORT_CHUNK];
+    __shared__ uint32_t s_gbase[256];
+    __shared__ uint32_t s_dstart[256];
+    __shared__ uint32_t s_w[8];
+
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const uint32_t block_base = blockIdx.x * SORT_CHUNK;
+    const uint32_t n_block = min((uint32_t)SORT_CHUNK, n - block_base);
+
+    uint64_t items[SORT_ITEMS];
+    uint32_t ranks[SORT_ITEMS];
+#pragma unroll
+    for (int i = 0; i < SORT_ITEMS; i++) {
+        uint32_t idx = warp * (32 * SORT_ITEMS) + i * 32 + lane;
+        items[i] = idx < n_block ? in[block_base + idx] : ~0ull;
+    }
+#pragma unroll
+    for (int w = 0; w < 8; w++) wh[w][t] = 0;
+    __syncthreads();
+
+#pragma unroll
+    for (int i = 0; i < SORT_ITEMS; i++) {
+        uint32_t idx = warp * (32 * SORT_ITEMS) + i * 32 + lane;
+        bool valid = idx < n_block;
+        uint32_t d = valid ? ((uint32_t)(items[i] >> shift) & 255u) : 256u;
+        uint32_t mask = __match_any_sync(0xffffffffu, d);
+        int leader = __ffs(mask) - 1;
+        uint32_t r = __popc(mask & ((1u << lane) - 1u));
+        uint32_t old = 0;
+        if (lane == leader && valid) {
+            old = wh[warp][d];
+            wh[warp][d] = old + __popc(mask);
+        }
+        old = __shfl_sync(0xffffffffu, old, leader);
+        ranks[i] = old + r;
+        __syncwarp();
+    }
+    __syncthreads();
+
+    // per digit (thread t owns digit t): exclusive prefix over warps, block count
+    uint32_t run = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++) {
+        uint32_t c = wh[w][t];
+        wh[w][t] = run;
+        run += c;
+    }
+    uint32_t dstart = block_excl_scan_256(run, s_w, nullptr);
+    uint32_t dbase = block_excl_scan_256(digit_tot[t], s_w, nullptr);
+    s_dstart[t] = dstart;
+    s_gbase[t] = dbase + hist[(size_t)t * nb + blockIdx.x] - dstart;
+    __syncthreads();
+
+#pragma unroll
+    for (int i = 0; i < SORT_ITEMS; i++) {
+        uint32_t idx = warp * (32 * SORT_ITEMS) + i * 32 + lane;
+        if (idx < n_block) {
+            uint32_t d = (uint32_t)(items[i] >> shift) & 255u;
+            stage[s_dstart[d] + wh[warp][d] + ranks[i]] = items[i];
+        }
+    }
+    __syncthreads();
+
+#pragma unroll
+    for (int i = 0; i < SORT_ITEMS; i++) {
+        uint32_t idx = i * SORT_THREADS + t;
+        if (idx < n_block) {
+            uint64_t it = stage[idx];
+            uint32_t d = (uint32_t)(it >> shift) & 255u;
+            uint32_t pos = s_gbase[d] + idx;
+            if (SPLIT) {
+                out_lo[pos] = (uint32_t)it;
+                out_hi[pos] = (uint32_t)(it >> 32);
+            } else {
+                out[pos] = it;
+            }
+        }
+    }
+}
+
+// One LSD pass src -> dst on digit `shift`. split => final pass with split outputs.
+static int radix_pass(const uint64_t* src, uint64_t* dst, uint32_t n, int shift, Scratch s,
+                      bool split, uint32_t* out_lo, uint32_t* out_hi, cudaStream_t st) {
+    const uint32_t nb = div_up(n, SORT_CHUNK);
+    radix_hist_kernel<<<nb, SORT_THREADS, 0, st>>>(src, n, shift, s.hist, nb);
+    radix_rowscan_kernel<<<256, 256, 0, st>>>(s.hist, nb, s.digit_tot);
+    if (split)
+        radix_scatter_kernel<true><<<nb, SORT_THREADS, 0, st>>>(src, n, shift, s.hist, nb, s.digit_tot,
+                                                                nullptr, out_lo, out_hi);
+    else
+        radix_scatter_kernel<false><<<nb, SORT_THREADS, 0, st>>>(src, n, shift, s.hist, nb, s.digit_tot,
+                                                                 dst, nullptr, nullptr);
+    return GSR_OK;
+}
+
+// ---------------------------------------------------------------- tile-count scan
+__device__ __forceinline__ uint32_t rect_tiles(uint2 r) {
+    uint32_t w = (r.y & 0xffffu) - (r.x & 0xffffu);
+    uint32_t h = (r.y >> 16) - (r.x >> 16);
+    return w * h;
+}
+
+// Phase 1: tiles touched by the Gaussian at each depth rank -> offsets[] (raw counts)
+// and the per-block sums.
+__global__ void __launch_bounds__(SCAN_THREADS)
+scan_count_kernel(const uint64_t* __restrict__ sorted, const uint2* __restrict__ rects, uint32_t P,
+                  uint32_t* __restrict__ offsets, uint32_t* __restrict__ block_sums) {
+    __shared__ uint32_t s_w[8];
+    const uint32_t base = blockIdx.x * SCAN_CHUNK;
+    uint32_t sum = 0;
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; i++) {
+        uint32_t idx = base + i * SCAN_THREADS + threadIdx.x;
+        if (idx < P) {
+            uint32_t c = rect_tiles(rects[(uint32_t)sorted[idx]]);
+            offsets[idx] = c;
+            sum += c;
+        }
+    }
+    uint32_t total;
+    block_excl_scan_256(sum, s_w, &total);
+    if (threadIdx.x == 0) block_sums[blockIdx.x] = total;
+}
+
+// Phase 2: one block; exclusive scan of the block sums in place, total -> counters.
+__global__ void __launch_bounds__(256)
+scan_blocksums_kernel(uint32_t* __restrict__ block_sums, uint32_t nb, int32_t* __restrict__ counters) {
+    __shared__ uint32_t s_w[8];
+    unsigned long long carry = 0;
+    for (uint32_t b0 = 0; b0 < nb; b0 += 256) {
+        uint32_t b = b0 + threadIdx.x;
+        uint32_t v = b < nb ? block_sums[b] : 0u;
+        uint32_t total;
+        uint32_t ex = block_excl_scan_256(v, s_w, &total);
+        if (b < nb) block_sums[b] = (uint32_t)carry + ex;
+        carry += total;
+    }
+    if (threadIdx.x == 0) {
+        counters[0] = carry > 0x7fffffffull ? 0x7fffffff : (int32_t)carry;
+        counters[1] = carry > 0x7fffffffull ? 1 : 0;   // reference: int num_rendered (rasterizer_impl.cu:312)
+    }
+}
+
+// Phase 3: inclusive scan inside each block + block prefix, in place.
+__global__ void __launch_bounds__(SCAN_THREADS)
+scan_apply_kernel(uint32_t* __restrict__ offsets, uint32_t P, const uint32_t* __restrict__ block_sums) {
+    __shared__ uint32_t s_w[8];
+    const uint32_t base = blockIdx.x * SCAN_CHUNK + threadIdx.x * SCAN_ITEMS;
+    uint32_t v[SCAN_ITEMS];
+    uint32_t sum = 0;
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; i++) {
+        v[i] = (base + i < P) ? offsets[base + i] : 0u;
+        sum += v[i];
+    }
+    uint32_t run = block_excl_scan_256(sum, s_w, nullptr) + block_sums[blockIdx.x];
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; i++) {
+        run += v[i];
+        if (base + i < P) offsets[base + i] = run;
+    }
+}
+
+// ---------------------------------------------------------------- instance emission
+// duplicateWithKeys (rasterizer_impl.cu:78-126) in depth order; item = tile<<32 | id.
+__global__ void __launch_bounds__(256)
+emit_instances_kernel(const uint64_t* __restrict__ sorted, const uint2* __restrict__ rects,
+                      const uint32_t* __restrict__ offsets, uint32_t P, uint32_t grid_x,
+                      uint64_t* __restrict__ inst) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    uint64_t it = sorted[i];
+    if ((uint32_t)(it >> 32) == 0xFFFFFFFFu) return;   // culled
+    uint32_t g = (uint32_t)it;
+    uint2 r = rects[g];
+    uint32_t x0 = r.x & 0xffffu, y0 = r.x >> 16, x1 = r.y & 0xffffu, y1 = r.y >> 16;
+    uint32_t off = offsets[i] - (x1 - x0) * (y1 - y0);
+    for (uint32_t y = y0; y < y1; y++)
+        for (uint32_t x = x0; x < x1; x++)
+            inst[off++] = ((uint64_t)(y * grid_x + x) << 32) | g;
+}
+
+// identifyTileRanges (rasterizer_impl.cu:132-164) on the sorted tile ids.
+__global__ void __launch_bounds__(256)
+tile_ranges_kernel(const uint32_t* __restrict__ tile_ids, uint32_t L, uint2* __restrict__ ranges) {
+    uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= L) return;
+    uint32_t cur = tile_ids[idx];
+    if (idx == 0)
+        ranges[cur].x = 0;
+    else {
+        uint32_t prev = tile_ids[idx - 1];
+        if (cur != prev) {
+            ranges[prev].y = idx;
+            ranges[cur].x = idx;
+        }
+    }
+    if (idx == L - 1) ranges[cur].y = L;
+}
+
+// Test hook: rebuild the reference's sorted keys  tile<<32 | depth bits.
+__global__ void rebuild_keys_kernel(const uint2* __restrict__ ranges, uint32_t T,
+                                    const uint32_t* __restrict__ point_list,
+                                    const GsRecord* __restrict__ rec, uint64_t* __restrict__ keys) {
+    uint32_t tile = blockIdx.x;
+    if (tile >= T) return;
+    uint2 rg = ranges[tile];
+    for (uint32_t i = rg.x + threadIdx.x; i < rg.y; i += blockDim.x)
+        keys[i] = ((uint64_t)tile << 32) | __float_as_uint(rec[point_list[i]].q2.z);
+}
+
+// ---------------------------------------------------------------- launchers
+int launch_depth_order_and_scan(const GsrParams& p, GeomState g, Scratch s, int32_t* num_rendered_host,
+                                cudaStream_t st) {
+    const uint32_t P = (uint32_t)p.P;
+    // depth_a holds depth_bits<<32 | id (written by preprocess). 4 stable LSD passes.
+    uint64_t* a = s.depth_a;
+    uint64_t* b = s.depth_b;
+    for (int pass = 0; pass < 4; pass++) {
+        radix_pass(a, b, P, 32 + 8 * pass, s, false, nullptr, nullptr, st);
+        uint64_t* tmp = a; a = b; b = tmp;
+    }
+    int rc = check_stage("depth sort", p.debug, st);
+    if (rc) return rc;
+    // a == s.depth_a again (even number of passes)
+    const uint32_t nb = div_up(P, SCAN_CHUNK);
+    scan_count_kernel<<<nb, SCAN_THREADS, 0, st>>>(a, s.rects, P, s.offsets, s.scan_blocks);
+    scan_blocksums_kernel<<<1, 256, 0, st>>>(s.scan_blocks, nb, s.counters);
+    scan_apply_kernel<<<nb, SCAN_THREADS, 0, st>>>(s.offsets, P, s.scan_blocks);
+    rc = check_stage("tile-count scan", p.debug, st);
+    if (rc) return rc;
+    if (num_rendered_host)
+        GSR_CUDA_TRY(cudaMemcpyAsync(num_rendered_host, s.counters, 2 * sizeof(int32_t),
+                                     cudaMemcpyDeviceToHost, st));
+    return GSR_OK;
+}
+
+int launch_binning(const GsrParams& p, GeomState g, ImgState im, BinState b, Scratch s, int64_t R,
+                   cudaStream_t st) {
+    const uint32_t P = (uint32_t)p.P;
+    const uint32_t gx = div_up(p.W, TILE_X), gy = div_up(p.H, TILE_Y);
+    const uint32_t T = gx * gy;
+    GSR_CUDA_TRY(cudaMemsetAsync(im.ranges, 0, (size_t)T * sizeof(uint2), st));   // rasterizer_impl.cu:342
+    if (R <= 0) return GSR_OK;
+    const uint32_t n = (uint32_t)R;
+    emit_instances_kernel<<<div_up(P, 256), 256, 0, st>>>(s.depth_a, s.rects, s.offsets, P, gx, s.inst_a);
+    int rc = check_stage("emit instances", p.debug, st);
+    if (rc) return rc;
+    // reference sorts bits [0, 32+getHigherMsb(T)) (rasterizer_impl.cu:332-340); the low 32
+    // (depth) are already in order, so only the tile bits remain.
+    const int bits = (int)higher_msb(T);
+    const int passes = (bits + 7) / 8;
+    uint64_t* a = s.inst_a;
+    uint64_t* c = s.inst_b;
+    for (int pass = 0; pass < passes; pass++) {
+        const bool last = pass == passes - 1;
+        radix_pass(a, c, n, 32 + 8 * pass, s, last, b.point_list, s.tile_ids, st);
+        uint64_t* tmp = a; a = c; c = tmp;
+    }
+    rc = check_stage("tile sort", p.debug, st);
+    if (rc) return rc;
+    tile_ranges_kernel<<<div_up(n, 256), 256, 0, st>>>(s.tile_ids, n, im.ranges);
+    return check_stage("tile ranges", p.debug, st);
+}
+
+int launch_rebuild_keys(const GsrParams& p, GeomState g, ImgState im, BinState b, int64_t R,
+                        uint64_t* keys_out, cudaStream_t st) {
+    const uint32_t gx = div_up(p.W, TILE_X), gy = div_up(p.H, TILE_Y);
+    if (R <= 0) return GSR_OK;
+    rebuild_keys_kernel<<<gx * gy, 128, 0, st>>>(im.ranges, gx * gy, b.point_list, g.rec, keys_out);
+    return check_stage("rebuild keys", true, st);
+}
+
+}  // namespace gsr

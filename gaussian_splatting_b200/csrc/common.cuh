@@ -1,0 +1,174 @@
+// common.cuh — shared types and helpers for the sm_100a Gaussian rasterizer kernels.
+//
+// Data layout in HBM:
+//   GsRecord[P]   64 B per Gaussian, written by preprocess, gathered by the
+//                 render kernels with one 48 B (fwd) / 64 B (bwd) bulk copy.
+//   rects[P]      packed tile rectangle (4 x u16), consumed by instance emission.
+//   point_list[R] Gaussian ids ordered by (tile, depth, id)  == the reference's
+//                 sorted value list (rasterizer_impl.cu:335-340).
+//   ranges[T]     per-tile [start,end) into point_list (rasterizer_impl.cu:132-164).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include "../../include/gsrast.h"
+
+namespace gsr {
+
+constexpr int TILE_X = GSR_TILE_X;
+constexpr int TILE_Y = GSR_TILE_Y;
+constexpr int TILE_PIX = TILE_X * TILE_Y;
+
+// One Gaussian after projection.  16 floats, 64 B, 64 B aligned.
+//   q0 = {x, y, conic.x, conic.y}            pixel centre + conic a,b
+//   q1 = {conic.z, opacity*aa, r, g}
+//   q2 = {b, 1/depth, depth, radius(int bits)}
+//   q3 = {clamped bits (int), tiles_touched (int), unused, unused}
+struct __align__(16) GsRecord {
+    float4 q0, q1, q2, q3;
+};
+static_assert(sizeof(GsRecord) == GSR_RECORD_FLOATS * 4, "record size");
+
+// Gradient accumulator per Gaussian written by render backward (atomics) and
+// consumed by preprocess backward.  12 floats, 48 B:
+//   {dcolor r,g,b, dinvdepth | dmean2D x,y, dconic a,b | dconic c, dopacity, pad, pad}
+constexpr int ACC_FLOATS = 12;
+
+__host__ __device__ inline uint32_t div_up(uint32_t a, uint32_t b) { return (a + b - 1) / b; }
+
+// getHigherMsb (rasterizer_impl.cu:36-51): floor(log2 n) + 1 for n > 0.
+inline uint32_t higher_msb(uint32_t n) {
+    uint32_t msb = sizeof(n) * 4, step = msb;
+    while (step > 1) {
+        step /= 2;
+        if (n >> msb) msb += step; else msb -= step;
+    }
+    if (n >> msb) msb++;
+    return msb;
+}
+
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// Bump allocator over a caller-owned chunk (role of `obtain`, rasterizer_impl.h:25-35).
+struct Carver {
+    char* base; size_t off;
+    explicit Carver(void* p) : base(reinterpret_cast<char*>(p)), off(0) {}
+    template <typename T> T* take(size_t count) {
+        off = align_up(off, 256);
+        T* r = reinterpret_cast<T*>(base + off);
+        off += count * sizeof(T);
+        return r;
+    }
+    size_t used() const { return align_up(off, 256); }
+};
+
+// ---- state layouts -------------------------------------------------------
+struct GeomState {          // persists forward -> backward
+    GsRecord* rec;          // P
+    static GeomState carve(void* chunk, size_t P, size_t* bytes) {
+        Carver c(chunk); GeomState g;
+        g.rec = c.take<GsRecord>(P);
+        if (bytes) *bytes = c.used();
+        return g;
+    }
+};
+
+struct ImgState {           // persists forward -> backward
+    float*    final_T;      // N
+    uint32_t* n_contrib;    // N
+    uint2*    ranges;       // T
+    uint32_t* tile_max_contrib; // T : max n_contrib over the tile (backward start point)
+    static ImgState carve(void* chunk, size_t N, size_t T, size_t* bytes) {
+        Carver c(chunk); ImgState s;
+        s.final_T = c.take<float>(N);
+        s.n_contrib = c.take<uint32_t>(N);
+        s.ranges = c.take<uint2>(T);
+        s.tile_max_contrib = c.take<uint32_t>(T);
+        if (bytes) *bytes = c.used();
+        return s;
+    }
+};
+
+struct BinState {           // persists forward -> backward
+    uint32_t* point_list;   // R
+    static BinState carve(void* chunk, size_t R, size_t* bytes) {
+        Carver c(chunk); BinState s;
+        s.point_list = c.take<uint32_t>(R > 0 ? R : 1);
+        if (bytes) *bytes = c.used();
+        return s;
+    }
+};
+
+constexpr int SORT_THREADS = 256;
+constexpr int SORT_ITEMS = 16;
+constexpr int SORT_CHUNK = SORT_THREADS * SORT_ITEMS;   // 4096 items per block
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_ITEMS = 8;
+constexpr int SCAN_CHUNK = SCAN_THREADS * SCAN_ITEMS;   // 2048 items per block
+
+struct Scratch {            // only live inside one forward or backward call
+    // forward
+    uint2*    rects;        // P   packed rect {min.x | min.y<<16, max.x | max.y<<16}
+    uint64_t* depth_a;      // P   depth_bits<<32 | id   (ping)
+    uint64_t* depth_b;      // P   (pong)
+    uint32_t* offsets;      // P   inclusive scan of tiles_touched in depth order
+    uint32_t* scan_blocks;  // ceil(P / SCAN_CHUNK) + 1
+    uint32_t* hist;         // 256 * max(blocks(P), blocks(R))
+    uint32_t* digit_tot;    // 256
+    uint64_t* inst_a;       // R   tile<<32 | id (ping)
+    uint64_t* inst_b;       // R   (pong)
+    uint32_t* tile_ids;     // R   sorted tile id per instance
+    int32_t*  counters;     // 8   device-side {R, overflow, ...}
+    // backward
+    float*    acc;          // P * ACC_FLOATS
+    static Scratch carve(void* chunk, size_t P, size_t R, size_t* bytes) {
+        Carver c(chunk); Scratch s;
+        size_t Rn = R > 0 ? R : 1;
+        size_t Pn = P > 0 ? P : 1;
+        size_t nb = (Pn > Rn ? Pn : Rn) / SORT_CHUNK + 2;
+        s.counters = c.take<int32_t>(8);
+        s.rects = c.take<uint2>(Pn);
+        s.depth_a = c.take<uint64_t>(Pn);
+        s.depth_b = c.take<uint64_t>(Pn);
+        s.offsets = c.take<uint32_t>(Pn);
+        s.scan_blocks = c.take<uint32_t>(Pn / SCAN_CHUNK + 2);
+        s.hist = c.take<uint32_t>(256 * nb);
+        s.digit_tot = c.take<uint32_t>(256);
+        s.inst_a = c.take<uint64_t>(Rn);
+        s.inst_b = c.take<uint64_t>(Rn);
+        s.tile_ids = c.take<uint32_t>(Rn);
+        // the backward accumulator aliases the forward instance buffers when it fits
+        s.acc = c.take<float>(Pn * ACC_FLOATS);
+        if (bytes) *bytes = c.used();
+        return s;
+    }
+};
+
+// ---- error plumbing ------------------------------------------------------
+void set_error(const char* fmt, ...);
+int  check_stage(const char* stage, bool debug, cudaStream_t stream);
+
+#define GSR_CUDA_TRY(expr)                                                        \
+    do {                                                                          \
+        cudaError_t _e = (expr);                                                  \
+        if (_e != cudaSuccess) {                                                  \
+            gsr::set_error("%s failed: %s", #expr, cudaGetErrorString(_e));       \
+            return GSR_ERR_CUDA;                                                  \
+        }                                                                         \
+    } while (0)
+
+// ---- stage launchers (defined in the per-stage .cu files) ------------------
+int launch_preprocess(const GsrParams& p, GeomState g, Scratch s, int32_t* radii, cudaStream_t st);
+int launch_mark_visible(int P, const float* means, const float* view, uint8_t* present, cudaStream_t st);
+int launch_depth_order_and_scan(const GsrParams& p, GeomState g, Scratch s, int32_t* num_rendered_host, cudaStream_t st);
+int launch_binning(const GsrParams& p, GeomState g, ImgState im, BinState b, Scratch s, int64_t R, cudaStream_t st);
+int launch_render_forward(const GsrParams& p, GeomState g, ImgState im, BinState b,
+                          float* out_color, float* out_invdepth, cudaStream_t st);
+int launch_render_backward(const GsrParams& p, GeomState g, ImgState im, BinState b, Scratch s,
+                           const float* dL_dpix, const float* dL_dinvdepth, cudaStream_t st);
+int launch_preprocess_backward(const GsrParams& p, GeomState g, Scratch s, const int32_t* radii,
+                               bool have_invdepth, const GsrBackwardIO& io, cudaStream_t st);
+int launch_rebuild_keys(const GsrParams& p, GeomState g, ImgState im, BinState b, int64_t R,
+                        uint64_t* keys_out, cudaStream_t st);
+
+}  // namespace gsr

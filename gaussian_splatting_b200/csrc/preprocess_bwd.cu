@@ -1,0 +1,371 @@
+// preprocess_bwd.cu — kernel 4b of the path: fused per-Gaussian backward.
+//
+// One kernel replaces computeCov2DCUDA + preprocessCUDA backward + the ten torch::zeros
+// fills (DGR/cuda_rasterizer/backward.cu:153-290, 296-365, 372-429; rasterize_points.cu:
+// 186-204): it consumes the 12-float accumulator written by render_bwd.cu and writes every
+// output gradient exactly once (zeros for culled Gaussians), so no zero-init pass is needed.
+//
+// The tail of computeCov2DCUDA that this fork elided (backward.cu:285-290: dL_dcov3D and the
+// covariance / inverse-depth part of dL_dmeans) is implemented from the chain rule of
+// cov2D = (J Rw) Sigma (J Rw)^T   and validated against fp64 autograd.
+// Like the reference, d(scale) ignores scale_modifier and the 1.3*tanfov clamp only masks
+// dL/dt.x, dL/dt.y (x_grad_mul / y_grad_mul).
+#include "common.cuh"
+#include "gs_math.cuh"
+
+namespace gsr {
+
+constexpr int PB_THREADS = 128;
+constexpr int PB_WARPS = PB_THREADS / 32;
+constexpr int PB_ROW = 48;
+constexpr int PB_ROW_PAD = PB_ROW + 1;
+
+__device__ __forceinline__ float sq(float x) { return x * x; }
+
+// auxiliary.h:128-139
+__device__ __forceinline__ float3 dnormvdv(float3 v, float3 dv) {
+    float sum2 = v.x * v.x + v.y * v.y + v.z * v.z;
+    float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
+    float3 r;
+    r.x = ((+sum2 - v.x * v.x) * dv.x - v.y * v.x * dv.y - v.z * v.x * dv.z) * invsum32;
+    r.y = (-v.x * v.y * dv.x + (sum2 - v.y * v.y) * dv.y - v.z * v.y * dv.z) * invsum32;
+    r.z = (-v.x * v.z * dv.x - v.y * v.z * dv.y + (sum2 - v.z * v.z) * dv.z) * invsum32;
+    return r;
+}
+
+// SH backward for one Gaussian (backward.cu:12-146).  `row` is this lane's padded row in
+// shared memory holding the coefficients on entry (first 3*(deg+1)^2 floats valid) and the
+// coefficient gradients on exit (all `rowlen` floats written).  Returns dL/d(mean).
+__device__ __forceinline__ float3 sh_backward(float* row, int rowlen, int deg, float3 dir_orig,
+                                              const float dL_dRGB[3]) {
+    const float len = sqrtf(dir_orig.x * dir_orig.x + dir_orig.y * dir_orig.y + dir_orig.z * dir_orig.z);
+    const float x = dir_orig.x / len, y = dir_orig.y / len, z = dir_orig.z / len;
+    float w[16];                       // dRGB/dsh_k
+    float dx[3] = {0.f, 0.f, 0.f}, dy[3] = {0.f, 0.f, 0.f}, dz[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+    for (int k = 0; k < 16; k++) w[k] = 0.f;
+    w[0] = GSR_SH_C0;
+#define SHC(k, c) row[(k) * 3 + (c)]
+    if (deg > 0) {
+        w[1] = -GSR_SH_C1 * y;
+        w[2] = GSR_SH_C1 * z;
+        w[3] = -GSR_SH_C1 * x;
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            dx[c] = -GSR_SH_C1 * SHC(3, c);
+            dy[c] = -GSR_SH_C1 * SHC(1, c);
+            dz[c] = GSR_SH_C1 * SHC(2, c);
+        }
+        if (deg > 1) {
+            const float xx = x * x, yy = y * y, zz = z * z;
+            const float xy = x * y, yz = y * z, xz = x * z;
+            w[4] = GSR_SH_C2_0 * xy;
+            w[5] = GSR_SH_C2_1 * yz;
+            w[6] = GSR_SH_C2_2 * (2.f * zz - xx - yy);
+            w[7] = GSR_SH_C2_3 * xz;
+            w[8] = GSR_SH_C2_4 * (xx - yy);
+#pragma unroll
+            for (int c = 0; c < 3; c++) {
+                dx[c] += GSR_SH_C2_0 * y * SHC(4, c) + GSR_SH_C2_2 * 2.f * -x * SHC(6, c) +
+                         GSR_SH_C2_3 * z * SHC(7, c) + GSR_SH_C2_4 * 2.f * x * SHC(8, c);
+                dy[c] += GSR_SH_C2_0 * x * SHC(4, c) + GSR_SH_C2_1 * z * SHC(5, c) +
+                         GSR_SH_C2_2 * 2.f * -y * SHC(6, c) + GSR_SH_C2_4 * 2.f * -y * SHC(8, c);
+                dz[c] += GSR_SH_C2_1 * y * SHC(5, c) + GSR_SH_C2_2 * 2.f * 2.f * z * SHC(6, c) +
+                         GSR_SH_C2_3 * x * SHC(7, c);
+            }
+            if (deg > 2) {
+                w[9] = GSR_SH_C3_0 * y * (3.f * xx - yy);
+                w[10] = GSR_SH_C3_1 * xy * z;
+                w[11] = GSR_SH_C3_2 * y * (4.f * zz - xx - yy);
+                w[12] = GSR_SH_C3_3 * z * (2.f * zz - 3.f * xx - 3.f * yy);
+                w[13] = GSR_SH_C3_4 * x * (4.f * zz - xx - yy);
+                w[14] = GSR_SH_C3_5 * z * (xx - yy);
+                w[15] = GSR_SH_C3_6 * x * (xx - 3.f * yy);
+#pragma unroll
+                for (int c = 0; c < 3; c++) {
+                    dx[c] += (GSR_SH_C3_0 * SHC(9, c) * 3.f * 2.f * xy +
+                              GSR_SH_C3_1 * SHC(10, c) * yz +
+                              GSR_SH_C3_2 * SHC(11, c) * -2.f * xy +
+                              GSR_SH_C3_3 * SHC(12, c) * -3.f * 2.f * xz +
+                              GSR_SH_C3_4 * SHC(13, c) * (-3.f * xx + 4.f * zz - yy) +
+                              GSR_SH_C3_5 * SHC(14, c) * 2.f * xz +
+                              GSR_SH_C3_6 * SHC(15, c) * 3.f * (xx - yy));
+                    dy[c] += (GSR_SH_C3_0 * SHC(9, c) * 3.f * (xx - yy) +
+                              GSR_SH_C3_1 * SHC(10, c) * xz +
+                              GSR_SH_C3_2 * SHC(11, c) * (-3.f * yy + 4.f * zz - xx) +
+                              GSR_SH_C3_3 * SHC(12, c) * -3.f * 2.f * yz +
+                              GSR_SH_C3_4 * SHC(13, c) * -2.f * xy +
+                              GSR_SH_C3_5 * SHC(14, c) * -2.f * yz +
+                              GSR_SH_C3_6 * SHC(15, c) * -3.f * 2.f * xy);
+                    dz[c] += (GSR_SH_C3_1 * SHC(10, c) * xy +
+                              GSR_SH_C3_2 * SHC(11, c) * 4.f * 2.f * yz +
+                              GSR_SH_C3_3 * SHC(12, c) * 3.f * (2.f * zz - xx - yy) +
+                              GSR_SH_C3_4 * SHC(13, c) * 4.f * 2.f * xz +
+                              GSR_SH_C3_5 * SHC(14, c) * (xx - yy));
+                }
+            }
+        }
+    }
+#undef SHC
+    const int ncoef = (deg + 1) * (deg + 1);
+    const int nrow = rowlen / 3;
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+        if (k < nrow) {
+            const float wk = k < ncoef ? w[k] : 0.f;
+            row[k * 3 + 0] = wk * dL_dRGB[0];
+            row[k * 3 + 1] = wk * dL_dRGB[1];
+            row[k * 3 + 2] = wk * dL_dRGB[2];
+        }
+    }
+    float3 dL_ddir = {dx[0] * dL_dRGB[0] + dx[1] * dL_dRGB[1] + dx[2] * dL_dRGB[2],
+                      dy[0] * dL_dRGB[0] + dy[1] * dL_dRGB[1] + dy[2] * dL_dRGB[2],
+                      dz[0] * dL_dRGB[0] + dz[1] * dL_dRGB[1] + dz[2] * dL_dRGB[2]};
+    return dnormvdv(dir_orig, dL_ddir);
+}
+
+// cov3D backward (backward.cu:296-365) with GLM indexing m[c][r].
+__device__ __forceinline__ void cov3D_backward(float3 scale, float mod, float4 rot, const float* dL_dcov3D,
+                                               float3* dL_dscale, float4* dL_drot) {
+    const float r = rot.x, x = rot.y, y = rot.z, z = rot.w;
+    Mat3 R = quat_to_R(r, x, y, z);
+    Mat3 S = mat3_cols(1.f, 0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 1.f);
+    const float3 s = {mod * scale.x, mod * scale.y, mod * scale.z};
+    S.m[0][0] = s.x; S.m[1][1] = s.y; S.m[2][2] = s.z;
+    Mat3 M = mat3_mul(S, R);
+    Mat3 dL_dSigma = mat3_cols(
+        dL_dcov3D[0], 0.5f * dL_dcov3D[1], 0.5f * dL_dcov3D[2],
+        0.5f * dL_dcov3D[1], dL_dcov3D[3], 0.5f * dL_dcov3D[4],
+        0.5f * dL_dcov3D[2], 0.5f * dL_dcov3D[4], dL_dcov3D[5]);
+    Mat3 dL_dM = mat3_mul(M, dL_dSigma);
+#pragma unroll
+    for (int c = 0; c < 3; c++)
+#pragma unroll
+        for (int rr = 0; rr < 3; rr++) dL_dM.m[c][rr] *= 2.0f;
+    Mat3 Rt = mat3_transpose(R);
+    Mat3 dL_dMt = mat3_transpose(dL_dM);
+    dL_dscale->x = Rt.m[0][0] * dL_dMt.m[0][0] + Rt.m[0][1] * dL_dMt.m[0][1] + Rt.m[0][2] * dL_dMt.m[0][2];
+    dL_dscale->y = Rt.m[1][0] * dL_dMt.m[1][0] + Rt.m[1][1] * dL_dMt.m[1][1] + Rt.m[1][2] * dL_dMt.m[1][2];
+    dL_dscale->z = Rt.m[2][0] * dL_dMt.m[2][0] + Rt.m[2][1] * dL_dMt.m[2][1] + Rt.m[2][2] * dL_dMt.m[2][2];
+#pragma unroll
+    for (int rr = 0; rr < 3; rr++) {
+        dL_dMt.m[0][rr] *= s.x;
+        dL_dMt.m[1][rr] *= s.y;
+        dL_dMt.m[2][rr] *= s.z;
+    }
+    const Mat3& D = dL_dMt;
+    dL_drot->x = 2 * z * (D.m[0][1] - D.m[1][0]) + 2 * y * (D.m[2][0] - D.m[0][2]) + 2 * x * (D.m[1][2] - D.m[2][1]);
+    dL_drot->y = 2 * y * (D.m[1][0] + D.m[0][1]) + 2 * z * (D.m[2][0] + D.m[0][2]) + 2 * r * (D.m[1][2] - D.m[2][1]) - 4 * x * (D.m[2][2] + D.m[1][1]);
+    dL_drot->z = 2 * x * (D.m[1][0] + D.m[0][1]) + 2 * r * (D.m[2][0] - D.m[0][2]) + 2 * z * (D.m[1][2] + D.m[2][1]) - 4 * y * (D.m[2][2] + D.m[0][0]);
+    dL_drot->w = 2 * r * (D.m[0][1] - D.m[1][0]) + 2 * x * (D.m[2][0] + D.m[0][2]) + 2 * y * (D.m[1][2] + D.m[2][1]) - 4 * z * (D.m[1][1] + D.m[0][0]);
+}
+
+__global__ void __launch_bounds__(PB_THREADS)
+preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord* __restrict__ rec,
+                      const int32_t* __restrict__ radii, const float* __restrict__ acc,
+                      bool have_invdepth, GsrBackwardIO io) {
+    __shared__ float sh_smem[PB_WARPS][32 * PB_ROW_PAD];
+    __shared__ float s_view[16], s_proj[16], s_cam[3];
+    if (threadIdx.x < 16) {
+        s_view[threadIdx.x] = p.viewmatrix[threadIdx.x];
+        s_proj[threadIdx.x] = p.projmatrix[threadIdx.x];
+    }
+    if (threadIdx.x < 3) s_cam[threadIdx.x] = p.campos[threadIdx.x];
+    __syncthreads();
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int idx = blockIdx.x * PB_THREADS + threadIdx.x;
+    const int warp_base = blockIdx.x * PB_THREADS + warp * 32;
+    const bool in_range = idx < p.P;
+    const bool visible = in_range && radii[idx] > 0;
+
+    float3 dL_dmean = {0.f, 0.f, 0.f};
+    float2 dL_dmean2D = {0.f, 0.f};
+    float dL_dopacity = 0.f;
+    float dL_dcolor[3] = {0.f, 0.f, 0.f};
+    float dL_dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    float3 dL_dscale = {0.f, 0.f, 0.f};
+    float4 dL_drot = {0.f, 0.f, 0.f, 0.f};
+    float3 mean = {0.f, 0.f, 0.f};
+    int clamped_bits = 0;
+
+    if (visible) {
+        const float4* a4 = reinterpret_cast<const float4*>(acc + (size_t)idx * ACC_FLOATS);
+        const float4 a0 = a4[0], a1 = a4[1], a2 = a4[2];
+        dL_dcolor[0] = a0.x; dL_dcolor[1] = a0.y; dL_dcolor[2] = a0.z;
+        const float dL_dinvdepth = a0.w;
+        dL_dmean2D = make_float2(a1.x, a1.y);
+        const float3 dL_dconic = {a1.z, a1.w, a2.x};
+        const float dL_dopacity_v = a2.y;
+        clamped_bits = __float_as_int(rec[idx].q3.x);
+
+        mean = make_float3(p.means3D[3 * idx], p.means3D[3 * idx + 1], p.means3D[3 * idx + 2]);
+        float cov3D[6];
+        float3 sc = {0.f, 0.f, 0.f};
+        float4 rot = {0.f, 0.f, 0.f, 0.f};
+        if (p.cov3D_precomp != nullptr) {
+#pragma unroll
+            for (int k = 0; k < 6; k++) cov3D[k] = p.cov3D_precomp[6 * idx + k];
+        } else {
+            sc = make_float3(p.scales[3 * idx], p.scales[3 * idx + 1], p.scales[3 * idx + 2]);
+            rot = reinterpret_cast<const float4*>(p.rotations)[idx];
+            compute_cov3D(sc, p.scale_modifier, rot, cov3D);
+        }
+        Cov2DCtx ctx;
+        const float3 cov = compute_cov2D(mean, focal_x, focal_y, p.tanfovx, p.tanfovy, cov3D, s_view, &ctx);
+        const float3 t = ctx.t;
+        const float x_grad_mul = (ctx.txtz < -ctx.limx || ctx.txtz > ctx.limx) ? 0.f : 1.f;
+        const float y_grad_mul = (ctx.tytz < -ctx.limy || ctx.tytz > ctx.limy) ? 0.f : 1.f;
+
+        float c_xx = cov.x, c_xy = cov.y, c_yy = cov.z;
+        constexpr float h_var = 0.3f;
+        float d_inside_root = 0.f;
+        dL_dopacity = dL_dopacity_v;
+        if (p.antialiasing) {
+            const float det_cov = c_xx * c_yy - c_xy * c_xy;
+            c_xx += h_var;
+            c_yy += h_var;
+            const float det_cov_plus_h_cov = c_xx * c_yy - c_xy * c_xy;
+            const float h_convolution_scaling = sqrtf(fmaxf(0.000025f, det_cov / det_cov_plus_h_cov));
+            const float d_h_convolution_scaling = dL_dopacity_v * p.opacities[idx];
+            dL_dopacity = dL_dopacity_v * h_convolution_scaling;
+            d_inside_root = (det_cov / det_cov_plus_h_cov) <= 0.000025f
+                                ? 0.f
+                                : d_h_convolution_scaling / (2 * h_convolution_scaling);
+        } else {
+            c_xx += h_var;
+            c_yy += h_var;
+        }
+        float dL_dc_xx = 0, dL_dc_xy = 0, dL_dc_yy = 0;
+        if (p.antialiasing) {
+            const float x = c_xx, y = c_yy, z = c_xy, w = h_var;
+            const float denom_f = d_inside_root / sq(w * w + w * (x + y) + x * y - z * z);
+            dL_dc_xx = w * (w * y + y * y + z * z) * denom_f;
+            dL_dc_yy = w * (w * x + x * x + z * z) * denom_f;
+            dL_dc_xy = -2.f * w * z * (w + x + y) * denom_f;
+        }
+        const float denom = c_xx * c_yy - c_xy * c_xy;
+        const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+        if (denom2inv != 0) {
+            dL_dc_xx += denom2inv * (-c_yy * c_yy * dL_dconic.x + 2 * c_xy * c_yy * dL_dconic.y + (denom - c_xx * c_yy) * dL_dconic.z);
+            dL_dc_yy += denom2inv * (-c_xx * c_xx * dL_dconic.z + 2 * c_xx * c_xy * dL_dconic.y + (denom - c_xx * c_yy) * dL_dconic.x);
+            dL_dc_xy += denom2inv * 2 * (c_xy * c_yy * dL_dconic.x - (denom + 2 * c_xy * c_xy) * dL_dconic.y + c_xx * c_xy * dL_dconic.z);
+        }
+
+        // ---- restored tail (App. A.6): A = J*Rw, rows A0 = T.m[0][*], A1 = T.m[1][*] ----
+        const float dL_da = dL_dc_xx, dL_db = dL_dc_xy, dL_dc = dL_dc_yy;
+        const float A0[3] = {ctx.T.m[0][0], ctx.T.m[0][1], ctx.T.m[0][2]};
+        const float A1[3] = {ctx.T.m[1][0], ctx.T.m[1][1], ctx.T.m[1][2]};
+        dL_dcov[0] = A0[0] * A0[0] * dL_da + A0[0] * A1[0] * dL_db + A1[0] * A1[0] * dL_dc;
+        dL_dcov[3] = A0[1] * A0[1] * dL_da + A0[1] * A1[1] * dL_db + A1[1] * A1[1] * dL_dc;
+        dL_dcov[5] = A0[2] * A0[2] * dL_da + A0[2] * A1[2] * dL_db + A1[2] * A1[2] * dL_dc;
+        dL_dcov[1] = 2 * A0[0] * A0[1] * dL_da + (A0[0] * A1[1] + A0[1] * A1[0]) * dL_db + 2 * A1[0] * A1[1] * dL_dc;
+        dL_dcov[2] = 2 * A0[0] * A0[2] * dL_da + (A0[0] * A1[2] + A0[2] * A1[0]) * dL_db + 2 * A1[0] * A1[2] * dL_dc;
+        dL_dcov[4] = 2 * A0[2] * A0[1] * dL_da + (A0[1] * A1[2] + A0[2] * A1[1]) * dL_db + 2 * A1[1] * A1[2] * dL_dc;
+
+        const float V[3][3] = {{cov3D[0], cov3D[1], cov3D[2]},
+                               {cov3D[1], cov3D[3], cov3D[4]},
+                               {cov3D[2], cov3D[4], cov3D[5]}};
+        float dL_dA0[3], dL_dA1[3];
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            const float VA0 = V[k][0] * A0[0] + V[k][1] * A0[1] + V[k][2] * A0[2];
+            const float VA1 = V[k][0] * A1[0] + V[k][1] * A1[1] + V[k][2] * A1[2];
+            dL_dA0[k] = 2 * VA0 * dL_da + VA1 * dL_db;
+            dL_dA1[k] = 2 * VA1 * dL_dc + VA0 * dL_db;
+        }
+        // Rw(r,k) = view[4k + r]
+        const float dL_dJ00 = s_view[0] * dL_dA0[0] + s_view[4] * dL_dA0[1] + s_view[8] * dL_dA0[2];
+        const float dL_dJ02 = s_view[2] * dL_dA0[0] + s_view[6] * dL_dA0[1] + s_view[10] * dL_dA0[2];
+        const float dL_dJ11 = s_view[1] * dL_dA1[0] + s_view[5] * dL_dA1[1] + s_view[9] * dL_dA1[2];
+        const float dL_dJ12 = s_view[2] * dL_dA1[0] + s_view[6] * dL_dA1[1] + s_view[10] * dL_dA1[2];
+        const float tz = 1.f / t.z;
+        const float tz2 = tz * tz;
+        const float tz3 = tz2 * tz;
+        const float dL_dtx = x_grad_mul * -focal_x * tz2 * dL_dJ02;
+        const float dL_dty = y_grad_mul * -focal_y * tz2 * dL_dJ12;
+        float dL_dtz = -focal_x * tz2 * dL_dJ00 - focal_y * tz2 * dL_dJ11 +
+                       (2 * focal_x * t.x) * tz3 * dL_dJ02 + (2 * focal_y * t.y) * tz3 * dL_dJ12;
+        if (have_invdepth) dL_dtz -= dL_dinvdepth / (t.z * t.z);
+        dL_dmean = transform_vec_4x3_transpose(make_float3(dL_dtx, dL_dty, dL_dtz), s_view);
+
+        // ---- projection term (backward.cu:393-420) ----
+        const float* proj = s_proj;
+        const float3 m = mean;
+        const float4 m_hom = transform_point_4x4(m, proj);
+        const float m_w = 1.0f / (m_hom.w + 0.0000001f);
+        const float mul1 = (proj[0] * m.x + proj[4] * m.y + proj[8] * m.z + proj[12]) * m_w * m_w;
+        const float mul2 = (proj[1] * m.x + proj[5] * m.y + proj[9] * m.z + proj[13]) * m_w * m_w;
+        dL_dmean.x += (proj[0] * m_w - proj[3] * mul1) * dL_dmean2D.x + (proj[1] * m_w - proj[3] * mul2) * dL_dmean2D.y;
+        dL_dmean.y += (proj[4] * m_w - proj[7] * mul1) * dL_dmean2D.x + (proj[5] * m_w - proj[7] * mul2) * dL_dmean2D.y;
+        dL_dmean.z += (proj[8] * m_w - proj[11] * mul1) * dL_dmean2D.x + (proj[9] * m_w - proj[11] * mul2) * dL_dmean2D.y;
+
+        if (p.scales != nullptr) cov3D_backward(sc, p.scale_modifier, rot, dL_dcov, &dL_dscale, &dL_drot);
+    }
+
+    // ---- SH backward through the shared-memory transpose; dL_dsh rows written coalesced ----
+    if (p.shs != nullptr && io.dL_dsh != nullptr) {
+        const unsigned vis_mask = __ballot_sync(0xffffffffu, visible);
+        const int L = 3 * (p.D + 1) * (p.D + 1);
+        const int row = 3 * p.M;
+        float* ws = sh_smem[warp];
+        if (vis_mask != 0) {
+            const float* src = p.shs + (size_t)warp_base * row;
+            for (int i = lane; i < 32 * L; i += 32) {
+                int g = i / L, k = i - g * L;
+                if ((vis_mask >> g) & 1u) ws[g * PB_ROW_PAD + k] = __ldg(src + (size_t)g * row + k);
+            }
+        }
+        __syncwarp();
+        float* myrow = ws + lane * PB_ROW_PAD;
+        if (visible) {
+            float dL_dRGB[3];
+#pragma unroll
+            for (int c = 0; c < 3; c++) dL_dRGB[c] = ((clamped_bits >> c) & 1) ? 0.f : dL_dcolor[c];
+            float3 dir_orig = {mean.x - s_cam[0], mean.y - s_cam[1], mean.z - s_cam[2]};
+            float3 dm = sh_backward(myrow, row, p.D, dir_orig, dL_dRGB);
+            dL_dmean.x += dm.x; dL_dmean.y += dm.y; dL_dmean.z += dm.z;
+        } else {
+            for (int k = 0; k < row; k++) myrow[k] = 0.f;
+        }
+        __syncwarp();
+        const int nvalid = min(32, p.P - warp_base);
+        float* dst = io.dL_dsh + (size_t)warp_base * row;
+        for (int i = lane; i < nvalid * row; i += 32) {
+            int g = i / row, k = i - g * row;
+            dst[i] = ws[g * PB_ROW_PAD + k];
+        }
+    }
+
+    if (!in_range) return;
+    if (io.dL_dmeans3D) {
+        io.dL_dmeans3D[3 * idx] = dL_dmean.x; io.dL_dmeans3D[3 * idx + 1] = dL_dmean.y; io.dL_dmeans3D[3 * idx + 2] = dL_dmean.z;
+    }
+    if (io.dL_dmeans2D) {
+        io.dL_dmeans2D[3 * idx] = dL_dmean2D.x; io.dL_dmeans2D[3 * idx + 1] = dL_dmean2D.y; io.dL_dmeans2D[3 * idx + 2] = 0.f;
+    }
+    if (io.dL_dopacity) io.dL_dopacity[idx] = dL_dopacity;
+    if (io.dL_dcolors) {
+        io.dL_dcolors[3 * idx] = dL_dcolor[0]; io.dL_dcolors[3 * idx + 1] = dL_dcolor[1]; io.dL_dcolors[3 * idx + 2] = dL_dcolor[2];
+    }
+    if (io.dL_dcov3D) {
+#pragma unroll
+        for (int k = 0; k < 6; k++) io.dL_dcov3D[6 * idx + k] = dL_dcov[k];
+    }
+    if (io.dL_dscales) {
+        io.dL_dscales[3 * idx] = dL_dscale.x; io.dL_dscales[3 * idx + 1] = dL_dscale.y; io.dL_dscales[3 * idx + 2] = dL_dscale.z;
+    }
+    if (io.dL_drotations) reinterpret_cast<float4*>(io.dL_drotations)[idx] = dL_drot;
+}
+
+int launch_preprocess_backward(const GsrParams& p, GeomState g, Scratch s, const int32_t* radii,
+                               bool have_invdepth, const GsrBackwardIO& io, cudaStream_t st) {
+    const float focal_y = p.H / (2.0f * p.tanfovy);
+    const float focal_x = p.W / (2.0f * p.tanfovx);
+    const int blocks = (p.P + PB_THREADS - 1) / PB_THREADS;
+    preprocess_bwd_kernel<<<blocks, PB_THREADS, 0, st>>>(p, focal_x, focal_y, g.rec, radii, s.acc,
+                                                         have_invdepth, io);
+    return check_stage("preprocess backward", p.debug, st);
+}
+
+}  // namespace gsr

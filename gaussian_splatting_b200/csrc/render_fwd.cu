@@ -1,0 +1,136 @@
+// render_fwd.cu — kernel 3 of the path: per-tile front-to-back alpha blending.
+//
+// Replaces renderCUDA forward (DGR/cuda_rasterizer/forward.cu:367-513).  One CTA per
+// 16x16 tile, one thread per pixel.  The tile's depth-ordered Gaussian records are
+// gathered into shared memory by bulk async copies (one 48 B `cp.async.bulk` per entry,
+// completing on an mbarrier), double-buffered so batch k+1 lands while batch k is blended.
+// A warp leaves the inner loop as soon as all of its 32 pixels are saturated; the CTA
+// stops fetching when all 256 are (block vote at batch granularity, as the reference).
+//
+// The per-pixel arithmetic keeps the reference's expression order: the skip tests
+// (power > 0, alpha < 1/255, T*(1-alpha) < 1e-4) are discontinuities, so a 1-ulp
+// difference in alpha would change n_contrib and move the image by up to 4e-3.
+#include "common.cuh"
+#include "async_copy.cuh"
+
+namespace gsr {
+
+constexpr int RF_BATCH = TILE_PIX;         // entries per stage (one gather per thread)
+constexpr int RF_REC_BYTES = 48;           // q0,q1,q2 of GsRecord
+constexpr int RF_STAGES = 2;
+
+__global__ void __launch_bounds__(TILE_PIX)
+render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+                  int W, int H, const GsRecord* __restrict__ rec,
+                  const float* __restrict__ bg_color,
+                  float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
+                  uint32_t* __restrict__ tile_max_contrib,
+                  float* __restrict__ out_color, float* __restrict__ out_invdepth) {
+    __shared__ __align__(128) float4 s_rec[RF_STAGES][RF_BATCH * 3];
+    __shared__ __align__(8) uint64_t s_bar[RF_STAGES];
+    __shared__ uint32_t s_max;
+
+    const uint32_t tx = threadIdx.x, ty = threadIdx.y;
+    const uint32_t rank = ty * TILE_X + tx;
+    const uint32_t horizontal_blocks = (W + TILE_X - 1) / TILE_X;
+    const uint32_t tile = blockIdx.y * horizontal_blocks + blockIdx.x;
+    const uint2 pix = {blockIdx.x * TILE_X + tx, blockIdx.y * TILE_Y + ty};
+    const uint32_t pix_id = W * pix.y + pix.x;
+    const float2 pixf = {(float)pix.x, (float)pix.y};
+    const bool inside = pix.x < (uint32_t)W && pix.y < (uint32_t)H;
+    bool done = !inside;
+
+    const uint2 range = ranges[tile];
+    const int n = (int)(range.y - range.x);
+    const int rounds = (n + RF_BATCH - 1) / RF_BATCH;
+
+    if (rank == 0) {
+        mbar_init(smem_u32(&s_bar[0]), 1);
+        mbar_init(smem_u32(&s_bar[1]), 1);
+        mbar_fence_init();
+        s_max = 0;
+    }
+    __syncthreads();
+
+    // gather of batch k into stage k&1: every thread copies one record, thread 0 posts
+    // the expected byte count (the only arrival of the phase).
+    auto issue = [&](int k) {
+        const int stage = k & 1;
+        const int cnt = min(RF_BATCH, n - k * RF_BATCH);
+        const uint32_t bar = smem_u32(&s_bar[stage]);
+        if ((int)rank < cnt) {
+            const uint32_t id = point_list[range.x + k * RF_BATCH + rank];
+            bulk_g2s(smem_u32(&s_rec[stage][rank * 3]), rec + id, RF_REC_BYTES, bar);
+        }
+        if (rank == 0) mbar_arrive_expect_tx(bar, (uint32_t)cnt * RF_REC_BYTES);
+    };
+
+    float T = 1.0f;
+    uint32_t last_contributor = 0;
+    float C[3] = {0.f, 0.f, 0.f};
+    float expected_invdepth = 0.0f;
+
+    if (rounds > 0) issue(0);
+    for (int k = 0; k < rounds; k++) {
+        mbar_wait(smem_u32(&s_bar[k & 1]), (uint32_t)((k >> 1) & 1));   // batch k has landed
+        // all threads are past batch k-1 here, so its stage may be refilled; nothing is
+        // in flight when the CTA leaves through the break
+        const int num_done = __syncthreads_count(done);
+        if (num_done == TILE_PIX) break;
+        if (k + 1 < rounds) issue(k + 1);
+
+        const float4* sr = s_rec[k & 1];
+        const int cnt = min(RF_BATCH, n - k * RF_BATCH);
+        const uint32_t base = (uint32_t)k * RF_BATCH;
+        for (int j = 0; !done && j < cnt; j++) {
+            const float4 q0 = sr[j * 3 + 0];      // x, y, conic.x, conic.y
+            const float4 q1 = sr[j * 3 + 1];      // conic.z, opacity, r, g
+            const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
+            const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
+            if (power > 0.0f) continue;
+            const float alpha = fminf(0.99f, q1.y * expf(power));
+            if (alpha < 1.0f / 255.0f) continue;
+            const float test_T = T * (1 - alpha);
+            if (test_T < 0.0001f) {
+                done = true;
+                continue;
+            }
+            const float4 q2 = sr[j * 3 + 2];      // b, 1/depth, depth, radius
+            C[0] += q1.z * alpha * T;
+            C[1] += q1.w * alpha * T;
+            C[2] += q2.x * alpha * T;
+            expected_invdepth += q2.y * alpha * T;
+            T = test_T;
+            last_contributor = base + j + 1;
+        }
+    }
+
+    if (inside) {
+        final_T[pix_id] = T;
+        n_contrib[pix_id] = last_contributor;
+        const size_t HW = (size_t)H * W;
+        out_color[0 * HW + pix_id] = C[0] + T * bg_color[0];
+        out_color[1 * HW + pix_id] = C[1] + T * bg_color[1];
+        out_color[2 * HW + pix_id] = C[2] + T * bg_color[2];
+        out_invdepth[pix_id] = expected_invdepth;
+    }
+    // backward starts its reverse traversal at the deepest contributor of the tile
+    uint32_t m = last_contributor;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((rank & 31) == 0 && m > 0) atomicMax(&s_max, m);
+    __syncthreads();
+    if (rank == 0) tile_max_contrib[tile] = s_max;
+}
+
+int launch_render_forward(const GsrParams& p, GeomState g, ImgState im, BinState b,
+                          float* out_color, float* out_invdepth, cudaStream_t st) {
+    dim3 grid((p.W + TILE_X - 1) / TILE_X, (p.H + TILE_Y - 1) / TILE_Y, 1);
+    dim3 block(TILE_X, TILE_Y, 1);
+    render_fwd_kernel<<<grid, block, 0, st>>>(im.ranges, b.point_list, p.W, p.H, g.rec, p.background,
+                                              im.final_T, im.n_contrib, im.tile_max_contrib,
+                                              out_color, out_invdepth);
+    return check_stage("render forward", p.debug, st);
+}
+
+}  // namespace gsr

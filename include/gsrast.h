@@ -1,0 +1,175 @@
+/*
+ * gsrast.h — C-ABI of the B200-native differentiable Gaussian rasterizer.
+ *
+ * This is the drop-in boundary for the reference's native layer
+ * (submodules/diff-gaussian-rasterization, "DGR"):
+ *   gsr_forward_*      replaces RasterizeGaussiansCUDA          (DGR/rasterize_points.cu:45-146,
+ *                      CudaRasterizer::Rasterizer::forward, DGR/cuda_rasterizer/rasterizer_impl.cu:227-370)
+ *   gsr_backward       replaces RasterizeGaussiansBackwardCUDA  (DGR/rasterize_points.cu:149-248,
+ *                      Rasterizer::backward, rasterizer_impl.cu:374-479)
+ *   gsr_mark_visible   replaces markVisible                     (DGR/rasterize_points.cu:250-274,
+ *                      rasterizer_impl.cu:169-181)
+ *
+ * Conventions
+ *  - extern "C", plain pointers and sizes; no torch / C++ types.
+ *  - The library never allocates or frees device memory that outlives a call:
+ *    every output, state and scratch buffer is owned by the caller (Python:
+ *    torch tensors).  Sizes come from the gsr_*_bytes queries.
+ *  - All device pointers must be 16-byte aligned (torch allocations are 512 B).
+ *  - Every entry point takes the CUDA stream to enqueue on (a cudaStream_t
+ *    passed as void*; NULL = legacy default stream).  Nothing synchronises the
+ *    host except where stated.
+ *  - Return value: 0 on success, negative GSR_ERR_* otherwise; text through
+ *    gsr_last_error() (thread-local).  Never exit()/abort().
+ *  - Optional inputs follow the reference's "empty tensor == nullptr" rule
+ *    (rasterize_points.cu:120-139): NULL shs => colors_precomp mode, NULL
+ *    scales/rotations => cov3D_precomp mode, NULL dL_dout_invdepth => no depth
+ *    gradient.
+ */
+#ifndef GSRAST_H_INCLUDED
+#define GSRAST_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GSR_VERSION 100
+
+#define GSR_OK                 0
+#define GSR_ERR_INVALID_ARG   -1
+#define GSR_ERR_CUDA          -2
+#define GSR_ERR_CAPACITY      -3   /* a caller-provided buffer is too small */
+#define GSR_ERR_OVERFLOW      -4   /* num_rendered does not fit in int32 (reference: int num_rendered) */
+#define GSR_ERR_NO_DEVICE     -5
+
+#define GSR_TILE_X 16               /* DGR/cuda_rasterizer/config.h:16-17 */
+#define GSR_TILE_Y 16
+#define GSR_CHANNELS 3              /* config.h:15 */
+
+/* Per-call arguments shared by the forward stages and the backward pass.
+ * Field meaning follows GaussianRasterizationSettings
+ * (DGR/diff_gaussian_rasterization/__init__.py:151-180) and the argument list
+ * of Rasterizer::forward (rasterizer_impl.cu:227-254). */
+typedef struct GsrParams {
+    int32_t P;                 /* number of Gaussians */
+    int32_t D;                 /* active SH degree 0..3 */
+    int32_t M;                 /* SH coefficients stored per Gaussian (sh.size(1)); 0 if no shs */
+    int32_t W, H;              /* image size in pixels */
+    float tanfovx, tanfovy;
+    float scale_modifier;
+    int32_t prefiltered;
+    int32_t antialiasing;
+    int32_t debug;             /* 1: synchronise + check after every stage and name the stage */
+    int32_t reserved0;
+
+    /* device inputs (fp32) */
+    const float* background;     /* 3 */
+    const float* means3D;        /* P*3 */
+    const float* shs;            /* P*M*3 or NULL */
+    const float* colors_precomp; /* P*3 or NULL */
+    const float* opacities;      /* P */
+    const float* scales;         /* P*3 or NULL */
+    const float* rotations;      /* P*4 (w,x,y,z) or NULL */
+    const float* cov3D_precomp;  /* P*6 or NULL */
+    const float* viewmatrix;     /* 16, column-major W2V   (auxiliary.h:75-95) */
+    const float* projmatrix;     /* 16, column-major Proj*W2V */
+    const float* campos;         /* 3 */
+} GsrParams;
+
+/* Caller-owned state and scratch.  geom/img/bin are kept alive by the caller
+ * between forward and backward (the reference keeps geomBuffer/binningBuffer/
+ * imgBuffer on the autograd ctx, __init__.py:93).  scratch is only used inside
+ * a call and may be shared across calls on the same stream. */
+typedef struct GsrBuffers {
+    void*  geom;    size_t geom_bytes;     /* >= gsr_geom_bytes(P) */
+    void*  img;     size_t img_bytes;      /* >= gsr_img_bytes(W,H) */
+    void*  bin;     size_t bin_bytes;      /* >= gsr_bin_bytes(R) */
+    void*  scratch; size_t scratch_bytes;  /* >= gsr_scratch_bytes(P,W,H,R) */
+    int32_t* num_rendered_host;            /* pinned host int32[2]: {R, overflow flag} */
+} GsrBuffers;
+
+typedef struct GsrForwardOut {
+    float*   out_color;     /* 3*H*W */
+    float*   out_invdepth;  /* H*W   */
+    int32_t* radii;         /* P     */
+} GsrForwardOut;
+
+typedef struct GsrBackwardIO {
+    /* upstream gradients */
+    const float* dL_dout_color;     /* 3*H*W */
+    const float* dL_dout_invdepth;  /* H*W or NULL */
+    /* outputs; every one is fully written (zeros for culled Gaussians), so the
+     * caller may pass uninitialised memory.  NULL = not wanted. */
+    float* dL_dmeans3D;    /* P*3 */
+    float* dL_dmeans2D;    /* P*3 (z stays 0; x,y scaled by 0.5*W, 0.5*H as backward.cu:529-530) */
+    float* dL_dopacity;    /* P   */
+    float* dL_dcolors;     /* P*3   gradient of colors_precomp; NULL in SH mode */
+    float* dL_dcov3D;      /* P*6   gradient of cov3D_precomp;  NULL in scale/rot mode */
+    float* dL_dsh;         /* P*M*3 or NULL */
+    float* dL_dscales;     /* P*3 or NULL */
+    float* dL_drotations;  /* P*4 or NULL */
+} GsrBackwardIO;
+
+int         gsr_version(void);
+const char* gsr_last_error(void);
+
+/* Workspace sizing (bytes).  R = number of (Gaussian, tile) instances. */
+size_t gsr_geom_bytes(int32_t P);
+size_t gsr_img_bytes(int32_t W, int32_t H);
+size_t gsr_bin_bytes(int64_t R);
+size_t gsr_scratch_bytes(int32_t P, int32_t W, int32_t H, int64_t R);
+
+/* Forward, stage 1: preprocess (projection, EWA + antialiasing, SH->RGB, tile
+ * rects), stable depth ordering and the tile-count scan.  Enqueues an async
+ * copy of {num_rendered, overflow} into buf->num_rendered_host; the caller
+ * waits for the stream (or an event) before reading it and before stage 2.
+ * Replaces rasterizer_impl.cu:279-313. */
+int gsr_forward_stage1(const GsrParams* p, const GsrBuffers* buf,
+                       const GsrForwardOut* out, void* stream);
+
+/* Forward, stage 2: instance emission, stable tile ordering, tile ranges and
+ * alpha blending.  R must be the value produced by stage 1; buf->bin must hold
+ * gsr_bin_bytes(R).  Replaces rasterizer_impl.cu:315-368. */
+int gsr_forward_stage2(const GsrParams* p, const GsrBuffers* buf,
+                       const GsrForwardOut* out, int64_t R, void* stream);
+
+/* Convenience: stage 1, host wait on `stream`, stage 2.  *num_rendered gets R.
+ * If buf->bin is too small returns GSR_ERR_CAPACITY with *num_rendered set;
+ * the caller regrows bin and calls gsr_forward_stage2. */
+int gsr_forward(const GsrParams* p, const GsrBuffers* buf,
+                const GsrForwardOut* out, int64_t* num_rendered, void* stream);
+
+/* Backward of the whole path. R as returned by forward. */
+int gsr_backward(const GsrParams* p, const GsrBuffers* buf, int64_t R,
+                 const int32_t* radii, const GsrBackwardIO* io, void* stream);
+
+/* present[i] = (W2V * p_i).z > 0.2   (rasterizer_impl.cu:56-73). present is P bytes (bool). */
+int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,
+                     const float* projmatrix, uint8_t* present, void* stream);
+
+/* Test/inspection hooks (bit-exact parity of the binning stage):
+ * rebuild the reference's sorted 64-bit key list (tile<<32 | depth bits) and
+ * expose point_list / ranges held in the state buffers.  Device pointers. */
+int gsr_debug_sorted_keys(const GsrParams* p, const GsrBuffers* buf, int64_t R,
+                          uint64_t* keys_out /* R */, void* stream);
+int gsr_debug_state_ptrs(const GsrParams* p, const GsrBuffers* buf, int64_t R,
+                         const uint32_t** point_list /* R */,
+                         const uint32_t** ranges /* T*2 */,
+                         const float** final_T /* H*W */,
+                         const uint32_t** n_contrib /* H*W */,
+                         const float** records /* P*GSR_RECORD_FLOATS */);
+
+#define GSR_RECORD_FLOATS 16
+
+/* View-parallel helper: number of floats per Gaussian in the
+ * flat parameter-gradient buffer that is all-reduced (xyz 3, sh 3*M, opacity 1,
+ * scale 3, rotation 4). */
+int32_t gsr_flat_grad_floats(int32_t M);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GSRAST_H_INCLUDED */
