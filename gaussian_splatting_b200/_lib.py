@@ -1,0 +1,109 @@
+"""ctypes binding of libgsrast.so (the C-ABI declared in include/gsrast.h).
+
+There is no fallback: if the shared library is missing or a call fails, a RuntimeError is
+raised.  Build it with `python -m gaussian_splatting_b200.build` (nvcc, sm_100a).
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libgsrast.so")
+
+GSR_OK = 0
+GSR_ERR_INVALID_ARG = -1
+GSR_ERR_CUDA = -2
+GSR_ERR_CAPACITY = -3
+GSR_ERR_OVERFLOW = -4
+
+_fp = C.c_void_p   # device pointers are passed as integers
+
+
+class GsrParams(C.Structure):
+    _fields_ = [
+        ("P", C.c_int32), ("D", C.c_int32), ("M", C.c_int32), ("W", C.c_int32), ("H", C.c_int32),
+        ("tanfovx", C.c_float), ("tanfovy", C.c_float), ("scale_modifier", C.c_float),
+        ("prefiltered", C.c_int32), ("antialiasing", C.c_int32), ("debug", C.c_int32),
+        ("reserved0", C.c_int32),
+        ("background", _fp), ("means3D", _fp), ("shs", _fp), ("colors_precomp", _fp),
+        ("opacities", _fp), ("scales", _fp), ("rotations", _fp), ("cov3D_precomp", _fp),
+        ("viewmatrix", _fp), ("projmatrix", _fp), ("campos", _fp),
+    ]
+
+
+class GsrBuffers(C.Structure):
+    _fields_ = [
+        ("geom", _fp), ("geom_bytes", C.c_size_t),
+        ("img", _fp), ("img_bytes", C.c_size_t),
+        ("bin", _fp), ("bin_bytes", C.c_size_t),
+        ("scratch", _fp), ("scratch_bytes", C.c_size_t),
+        ("num_rendered_host", _fp),
+    ]
+
+
+class GsrForwardOut(C.Structure):
+    _fields_ = [("out_color", _fp), ("out_invdepth", _fp), ("radii", _fp)]
+
+
+class GsrBackwardIO(C.Structure):
+    _fields_ = [
+        ("dL_dout_color", _fp), ("dL_dout_invdepth", _fp),
+        ("dL_dmeans3D", _fp), ("dL_dmeans2D", _fp), ("dL_dopacity", _fp), ("dL_dcolors", _fp),
+        ("dL_dcov3D", _fp), ("dL_dsh", _fp), ("dL_dscales", _fp), ("dL_drotations", _fp),
+    ]
+
+
+# every symbol include/gsrast.h declares (tests check that the library exports all of them)
+EXPORTS = (
+    "gsr_version", "gsr_last_error", "gsr_geom_bytes", "gsr_img_bytes", "gsr_bin_bytes",
+    "gsr_scratch_bytes", "gsr_forward_stage1", "gsr_forward_stage2", "gsr_forward", "gsr_backward",
+    "gsr_mark_visible", "gsr_debug_sorted_keys", "gsr_debug_state_ptrs", "gsr_flat_grad_floats",
+)
+
+_lib = None
+
+
+def load():
+    """Load libgsrast.so once; raises RuntimeError (never falls back) if it is unavailable."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} not found: the CUDA extension is required (no CPU fallback). "
+            "Build it with `python -m gaussian_splatting_b200.build`.")
+    lib = C.CDLL(LIB_PATH)
+    lib.gsr_version.restype = C.c_int
+    lib.gsr_last_error.restype = C.c_char_p
+    lib.gsr_geom_bytes.restype = C.c_size_t
+    lib.gsr_geom_bytes.argtypes = [C.c_int32]
+    lib.gsr_img_bytes.restype = C.c_size_t
+    lib.gsr_img_bytes.argtypes = [C.c_int32, C.c_int32]
+    lib.gsr_bin_bytes.restype = C.c_size_t
+    lib.gsr_bin_bytes.argtypes = [C.c_int64]
+    lib.gsr_scratch_bytes.restype = C.c_size_t
+    lib.gsr_scratch_bytes.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int64]
+    lib.gsr_flat_grad_floats.restype = C.c_int32
+    lib.gsr_flat_grad_floats.argtypes = [C.c_int32]
+    PP, PB, PO = C.POINTER(GsrParams), C.POINTER(GsrBuffers), C.POINTER(GsrForwardOut)
+    lib.gsr_forward_stage1.restype = C.c_int
+    lib.gsr_forward_stage1.argtypes = [PP, PB, PO, C.c_void_p]
+    lib.gsr_forward_stage2.restype = C.c_int
+    lib.gsr_forward_stage2.argtypes = [PP, PB, PO, C.c_int64, C.c_void_p]
+    lib.gsr_forward.restype = C.c_int
+    lib.gsr_forward.argtypes = [PP, PB, PO, C.POINTER(C.c_int64), C.c_void_p]
+    lib.gsr_backward.restype = C.c_int
+    lib.gsr_backward.argtypes = [PP, PB, C.c_int64, C.c_void_p, C.POINTER(GsrBackwardIO), C.c_void_p]
+    lib.gsr_mark_visible.restype = C.c_int
+    lib.gsr_mark_visible.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.gsr_debug_sorted_keys.restype = C.c_int
+    lib.gsr_debug_sorted_keys.argtypes = [PP, PB, C.c_int64, C.c_void_p, C.c_void_p]
+    lib.gsr_debug_state_ptrs.restype = C.c_int
+    lib.gsr_debug_state_ptrs.argtypes = [PP, PB, C.c_int64] + [C.POINTER(C.c_void_p)] * 5
+    _lib = lib
+    return lib
+
+
+def check(rc):
+    if rc != GSR_OK:
+        msg = load().gsr_last_error().decode("utf-8", "replace")
+        raise RuntimeError(msg or f"libgsrast error {rc}")
