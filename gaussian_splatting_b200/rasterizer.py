@@ -1,0 +1,345 @@
+"""Host-side mirror of the reference's autograd boundary over the C-ABI of libgsrast.so.
+
+Same names, argument order, defaults, exception messages, output tuple and gradient tuple as
+submodules/diff-gaussian-rasterization/diff_gaussian_rasterization/__init__.py
+(GaussianRasterizationSettings :151-180, GaussianRasterizer :183-274, _RasterizeGaussians
+:48-148, rasterize_gaussians :24-46, cpu_deep_copy_tuple :18-21), so that
+gaussian_renderer/__init__.py:render() and train.py run unmodified.
+
+PyTorch is plumbing only (device memory, streams, autograd registration): every kernel on the
+path lives in libgsrast.so.  There is no CPU or eager fallback: non-CUDA tensors or a missing
+library raise.
+"""
+import ctypes as C
+from typing import NamedTuple
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+from ._lib import GsrBackwardIO, GsrBuffers, GsrForwardOut, GsrParams
+
+
+def cpu_deep_copy_tuple(input_tuple):
+    copied_tensors = [item.cpu().clone() if isinstance(item, torch.Tensor) else item for item in input_tuple]
+    return tuple(copied_tensors)
+
+
+class GaussianRasterizationSettings(NamedTuple):
+    image_height: int
+    image_width: int
+    tanfovx: float
+    tanfovy: float
+    bg: torch.Tensor
+    scale_modifier: float
+    viewmatrix: torch.Tensor
+    projmatrix: torch.Tensor
+    sh_degree: int
+    campos: torch.Tensor
+    prefiltered: bool
+    debug: bool
+    antialiasing: bool
+
+
+# ---------------------------------------------------------------------------------------
+# Workspace: the C layer never allocates.  Per device we keep one scratch arena (grown
+# geometrically, reused by every call on that device's current stream) and a pinned
+# int32[2] that receives {num_rendered, overflow}.  State that backward needs (geom/img/bin)
+# is allocated per call and kept alive by the autograd ctx, as the reference does with
+# geomBuffer/binningBuffer/imgBuffer (__init__.py:93).
+# ---------------------------------------------------------------------------------------
+class _DeviceWorkspace:
+    def __init__(self, device):
+        self.device = device
+        self.scratch = torch.empty(0, dtype=torch.uint8, device=device)
+        self.pinned = torch.zeros(2, dtype=torch.int32).pin_memory()
+        self.last_R = 0
+        self.regrows = 0
+
+    def ensure(self, nbytes, keep_prefix=0):
+        """Grow the scratch arena to >= nbytes, preserving its first keep_prefix bytes."""
+        if self.scratch.numel() >= nbytes:
+            return
+        new = torch.empty(int(nbytes * 1.25) + 4096, dtype=torch.uint8, device=self.device)
+        if keep_prefix:
+            new[:keep_prefix].copy_(self.scratch[:keep_prefix])
+        self.scratch = new
+        self.regrows += 1
+
+
+_workspaces = {}
+
+
+def _workspace(device):
+    key = (device.type, device.index if device.index is not None else torch.cuda.current_device())
+    ws = _workspaces.get(key)
+    if ws is None:
+        ws = _workspaces[key] = _DeviceWorkspace(device)
+    return ws
+
+
+def workspace_stats(device=None):
+    """{'scratch_bytes', 'regrows', 'last_num_rendered'} for a device (config C5 reporting)."""
+    device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    ws = _workspace(device)
+    return dict(scratch_bytes=ws.scratch.numel(), regrows=ws.regrows, last_num_rendered=ws.last_R)
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def _f32c(t, name):
+    """fp32 contiguous CUDA tensor or None for an empty tensor (the reference's nullptr rule)."""
+    if t is None or t.numel() == 0:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor (this rasterizer has no CPU path)")
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+def _params(P, M, rs, bg, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+            viewmatrix, projmatrix, campos):
+    p = GsrParams()
+    p.P, p.D, p.M = P, int(rs.sh_degree), M
+    p.W, p.H = int(rs.image_width), int(rs.image_height)
+    p.tanfovx, p.tanfovy = float(rs.tanfovx), float(rs.tanfovy)
+    p.scale_modifier = float(rs.scale_modifier)
+    p.prefiltered, p.antialiasing, p.debug = int(bool(rs.prefiltered)), int(bool(rs.antialiasing)), int(bool(rs.debug))
+    p.background, p.means3D, p.shs = _ptr(bg), _ptr(means3D), _ptr(sh)
+    p.colors_precomp, p.opacities = _ptr(colors_precomp), _ptr(opacities)
+    p.scales, p.rotations, p.cov3D_precomp = _ptr(scales), _ptr(rotations), _ptr(cov3Ds_precomp)
+    p.viewmatrix, p.projmatrix, p.campos = _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos)
+    return p
+
+
+def _forward_native(rs, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp):
+    """Role of _C.rasterize_gaussians (ext.cpp:16 -> rasterize_points.cu:45-146).
+
+    Returns (num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, invdepths)."""
+    lib = _lib.load()
+    if means3D.ndim != 2 or means3D.shape[1] != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    if not means3D.is_cuda:
+        raise RuntimeError("means3D must be a CUDA tensor (this rasterizer has no CPU path)")
+    device = means3D.device
+    P = means3D.shape[0]
+    H, W = int(rs.image_height), int(rs.image_width)
+    with torch.cuda.device(device):
+        color = torch.empty((3, H, W), dtype=torch.float32, device=device)
+        invdepth = torch.empty((1, H, W), dtype=torch.float32, device=device)
+        radii = torch.empty((P,), dtype=torch.int32, device=device)
+        empty = torch.empty(0, dtype=torch.uint8, device=device)
+        if P == 0:                                   # rasterize_points.cu:107: no launch, zeros
+            return 0, color.zero_(), radii, empty, empty, empty, invdepth.zero_()
+
+        means3D = _f32c(means3D, "means3D")
+        sh = _f32c(sh, "sh")
+        colors_precomp = _f32c(colors_precomp, "colors_precomp")
+        opacities = _f32c(opacities, "opacities")
+        scales = _f32c(scales, "scales")
+        rotations = _f32c(rotations, "rotations")
+        cov3Ds_precomp = _f32c(cov3Ds_precomp, "cov3Ds_precomp")
+        bg = _f32c(rs.bg, "bg")
+        viewmatrix = _f32c(rs.viewmatrix, "viewmatrix")
+        projmatrix = _f32c(rs.projmatrix, "projmatrix")
+        campos = _f32c(rs.campos, "campos")
+        M = sh.shape[1] if sh is not None else 0
+        p = _params(P, M, rs, bg, means3D, sh, colors_precomp, opacities, scales, rotations,
+                    cov3Ds_precomp, viewmatrix, projmatrix, campos)
+
+        ws = _workspace(device)
+        stream = torch.cuda.current_stream(device)
+        geom = torch.empty(lib.gsr_geom_bytes(P), dtype=torch.uint8, device=device)
+        img = torch.empty(lib.gsr_img_bytes(W, H), dtype=torch.uint8, device=device)
+        # speculate the instance count from the previous frame so the arena rarely regrows
+        R_guess = max(int(ws.last_R * 1.1), 4 * P)
+        ws.ensure(lib.gsr_scratch_bytes(P, W, H, R_guess))
+
+        buf = GsrBuffers()
+        buf.geom, buf.geom_bytes = geom.data_ptr(), geom.numel()
+        buf.img, buf.img_bytes = img.data_ptr(), img.numel()
+        buf.scratch, buf.scratch_bytes = ws.scratch.data_ptr(), ws.scratch.numel()
+        buf.num_rendered_host = ws.pinned.data_ptr()
+        out = GsrForwardOut(color.data_ptr(), invdepth.data_ptr(), radii.data_ptr())
+
+        _lib.check(lib.gsr_forward_stage1(C.byref(p), C.byref(buf), C.byref(out), stream.cuda_stream))
+        stream.synchronize()                         # the one host sync of the path (rasterizer_impl.cu:313)
+        R, overflow = int(ws.pinned[0]), int(ws.pinned[1])
+        if overflow:
+            raise RuntimeError("num_rendered exceeds int32 (the reference stores it in an int)")
+        ws.last_R = R
+        need = lib.gsr_scratch_bytes(P, W, H, R)
+        if ws.scratch.numel() < need:
+            ws.ensure(need, keep_prefix=lib.gsr_scratch_bytes(P, W, H, 0))
+            buf.scratch, buf.scratch_bytes = ws.scratch.data_ptr(), ws.scratch.numel()
+        binb = torch.empty(lib.gsr_bin_bytes(R), dtype=torch.uint8, device=device)
+        buf.bin, buf.bin_bytes = binb.data_ptr(), binb.numel()
+        _lib.check(lib.gsr_forward_stage2(C.byref(p), C.byref(buf), C.byref(out), R, stream.cuda_stream))
+    return R, color, radii, geom, binb, img, invdepth
+
+
+def _backward_native(rs, means3D, radii, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                     grad_out_color, grad_out_depth, sh, geom, R, binb, img):
+    """Role of _C.rasterize_gaussians_backward (rasterize_points.cu:149-248).
+
+    Returns (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales,
+    dL_drotations); entries for absent inputs are None."""
+    lib = _lib.load()
+    device = means3D.device
+    P = means3D.shape[0]
+    H, W = int(rs.image_height), int(rs.image_width)
+    f32 = dict(dtype=torch.float32, device=device)
+    with torch.cuda.device(device):
+        sh_c = _f32c(sh, "sh")
+        M = sh_c.shape[1] if sh_c is not None else 0
+        if P == 0:
+            z = lambda *s: torch.zeros(*s, **f32)
+            return z(0, 3), z(0, 3), z(0, 1), z(0, 3), z(0, 6), z(0, M, 3), z(0, 3), z(0, 4)
+        means3D = _f32c(means3D, "means3D")
+        colors_precomp = _f32c(colors_precomp, "colors_precomp")
+        opacities = _f32c(opacities, "opacities")
+        scales = _f32c(scales, "scales")
+        rotations = _f32c(rotations, "rotations")
+        cov3Ds_precomp = _f32c(cov3Ds_precomp, "cov3Ds_precomp")
+        bg = _f32c(rs.bg, "bg")
+        viewmatrix = _f32c(rs.viewmatrix, "viewmatrix")
+        projmatrix = _f32c(rs.projmatrix, "projmatrix")
+        campos = _f32c(rs.campos, "campos")
+        grad_out_color = _f32c(grad_out_color, "grad_out_color")
+        grad_out_depth = _f32c(grad_out_depth, "grad_out_depth")
+        if grad_out_color is None:
+            grad_out_color = torch.zeros((3, H, W), **f32)
+        p = _params(P, M, rs, bg, means3D, sh_c, colors_precomp, opacities, scales, rotations,
+                    cov3Ds_precomp, viewmatrix, projmatrix, campos)
+
+        ws = _workspace(device)
+        stream = torch.cuda.current_stream(device)
+        ws.ensure(lib.gsr_scratch_bytes(P, W, H, R))
+        buf = GsrBuffers()
+        buf.geom, buf.geom_bytes = geom.data_ptr(), geom.numel()
+        buf.img, buf.img_bytes = img.data_ptr(), img.numel()
+        buf.bin, buf.bin_bytes = binb.data_ptr(), binb.numel()
+        buf.scratch, buf.scratch_bytes = ws.scratch.data_ptr(), ws.scratch.numel()
+        buf.num_rendered_host = ws.pinned.data_ptr()
+
+        # every output is fully written by the fused backward kernel: no zero fills
+        dL_dmeans3D = torch.empty((P, 3), **f32)
+        dL_dmeans2D = torch.empty((P, 3), **f32)
+        dL_dopacity = torch.empty((P, 1), **f32)
+        dL_dcolors = torch.empty((P, 3), **f32) if colors_precomp is not None else None
+        dL_dcov3D = torch.empty((P, 6), **f32) if cov3Ds_precomp is not None else None
+        dL_dsh = torch.empty((P, M, 3), **f32) if sh_c is not None else None
+        dL_dscales = torch.empty((P, 3), **f32) if scales is not None else None
+        dL_drotations = torch.empty((P, 4), **f32) if rotations is not None else None
+        io = GsrBackwardIO(grad_out_color.data_ptr(), _ptr(grad_out_depth), dL_dmeans3D.data_ptr(),
+                           dL_dmeans2D.data_ptr(), dL_dopacity.data_ptr(), _ptr(dL_dcolors), _ptr(dL_dcov3D),
+                           _ptr(dL_dsh), _ptr(dL_dscales), _ptr(dL_drotations))
+        _lib.check(lib.gsr_backward(C.byref(p), C.byref(buf), R, radii.data_ptr(), C.byref(io),
+                                    stream.cuda_stream))
+    return dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations
+
+
+def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                        raster_settings):
+    return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
+                                     cov3Ds_precomp, raster_settings)
+
+
+class _RasterizeGaussians(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                raster_settings):
+        num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, invdepths = _forward_native(
+            raster_settings, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp)
+        ctx.raster_settings = raster_settings
+        ctx.num_rendered = num_rendered
+        ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, opacities,
+                              geomBuffer, binningBuffer, imgBuffer)
+        ctx.mark_non_differentiable(radii)
+        return color, radii, invdepths
+
+    @staticmethod
+    def backward(ctx, grad_out_color, _, grad_out_depth):
+        num_rendered = ctx.num_rendered
+        raster_settings = ctx.raster_settings
+        (colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, opacities,
+         geomBuffer, binningBuffer, imgBuffer) = ctx.saved_tensors
+        (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh,
+         grad_scales, grad_rotations) = _backward_native(
+            raster_settings, means3D, radii, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+            grad_out_color, grad_out_depth, sh, geomBuffer, num_rendered, binningBuffer, imgBuffer)
+        grads = (
+            grad_means3D,
+            grad_means2D,
+            grad_sh,
+            grad_colors_precomp,
+            grad_opacities,
+            grad_scales,
+            grad_rotations,
+            grad_cov3Ds_precomp,
+            None,
+        )
+        return grads
+
+
+class GaussianRasterizer(nn.Module):
+    def __init__(self, raster_settings):
+        super().__init__()
+        self.raster_settings = raster_settings
+
+    def markVisible(self, positions):
+        # Mark visible points (based on frustum culling for camera) with a boolean
+        with torch.no_grad():
+            raster_settings = self.raster_settings
+            lib = _lib.load()
+            if not positions.is_cuda:
+                raise RuntimeError("positions must be a CUDA tensor (this rasterizer has no CPU path)")
+            P = positions.shape[0]
+            visible = torch.zeros((P,), dtype=torch.bool, device=positions.device)
+            if P:
+                with torch.cuda.device(positions.device):
+                    pos = _f32c(positions, "positions")
+                    view = _f32c(raster_settings.viewmatrix, "viewmatrix")
+                    proj = _f32c(raster_settings.projmatrix, "projmatrix")
+                    _lib.check(lib.gsr_mark_visible(P, pos.data_ptr(), view.data_ptr(), proj.data_ptr(),
+                                                    visible.data_ptr(),
+                                                    torch.cuda.current_stream(positions.device).cuda_stream))
+        return visible
+
+    def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
+                cov3D_precomp=None):
+        raster_settings = self.raster_settings
+
+        if (shs is None and colors_precomp is None) or (shs is not None and colors_precomp is not None):
+            raise Exception('Please provide exactly one of either SHs or precomputed colors!')
+
+        if ((scales is None or rotations is None) and cov3D_precomp is None) or \
+                ((scales is not None or rotations is not None) and cov3D_precomp is not None):
+            raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
+
+        if shs is None:
+            shs = torch.Tensor([])
+        if colors_precomp is None:
+            colors_precomp = torch.Tensor([])
+        if scales is None:
+            scales = torch.Tensor([])
+        if rotations is None:
+            rotations = torch.Tensor([])
+        if cov3D_precomp is None:
+            cov3D_precomp = torch.Tensor([])
+
+        # Invoke C++/CUDA rasterization routine
+        return rasterize_gaussians(
+            means3D,
+            means2D,
+            shs,
+            colors_precomp,
+            opacities,
+            scales,
+            rotations,
+            cov3D_precomp,
+            raster_settings,
+        )
