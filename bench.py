@@ -1,0 +1,479 @@
+#!/usr/bin/env python
+"""Benchmark of the hot path: fwd+bwd Gaussian rasterization (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload C3]
+
+One "step" = one forward + backward pass of the rasterizer over one camera of the synthetic
+workload (default C3 = 3M Gaussians, 1920x1080, SH degree 3, antialiasing on,
+dense upstream gradients for colour and inverse depth).  With N > 1 (torchrun, one rank per
+GPU) every rank rasterizes its own camera of a ring and the per-Gaussian parameter gradients
+are summed with one NCCL all-reduce per step (view-parallel, weak scaling).
+
+Prints ONE JSON line on rank 0.  Keys beyond the base contract:
+  roofline      dominant stage of the step, timed live with CUDA events on the launching stream
+  stages        every stage: ms, algorithmic bytes / flops, achieved, peak, fraction
+  work          measured work descriptors P, V, R, T, N, Wf, Wb, Bp (independent counting pass)
+  cpu_baseline  the CPU oracle (port of the reference kernels) on the host cores
+  e2e           same metric through the public API with host-side step inputs (camera + targets
+                copied from pinned memory every step, loss read back every step)
+  fwd_fps       forward-only render FPS (second half of BASELINE.json's metric)
+`--impl reference` times the reference's own CUDA rasterizer (oracle/_ref, built from
+/root/reference by oracle/build_ref.py) with the same protocol; if that build is absent it
+falls back to the CPU oracle port and says so.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+METRIC = "fwd+bwd rasterize iters/sec at 3M Gaussians 1080p"
+UNIT = "iter/s"
+SM_COUNT_B200 = 148
+FP32_LANES_PER_SM = 128
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="C3", help="C1|C2|C3|C4 (SURVEY.md §8d) or C3 with --P override")
+    ap.add_argument("--P", type=int, default=None, help="override the Gaussian count")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--ref-variant", default="restored", choices=["restored", "asis"])
+    return ap.parse_args()
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        d = json.load(open(path))
+        return dict(hbm_gbs=float(d["hbm_gbs"]), sm_max_mhz=float(d.get("sm_max_mhz", 1965.0)), source="measured")
+    return dict(hbm_gbs=6650.0, sm_max_mhz=1965.0, source="fallback")
+
+
+# ------------------------------------------------------------------ clocks during the timed region
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0=None, t1=None):
+        if self.proc is None:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons, power = [], [], set(), []
+        for ts, line in self.rows:
+            if t0 is not None and not (t0 - 0.05 <= ts <= t1 + 0.15):
+                continue
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); smax.append(float(f[2])); power.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["no samples"])
+        sm.sort()
+        return dict(sm_mhz=sm[len(sm) // 2], sm_max_mhz=max(smax), reasons=sorted(reasons),
+                    samples=len(sm), power_w_max=max(power))
+
+
+# ------------------------------------------------------------------ workload
+def build_workload(args, rank, device):
+    """Synthetic Gaussians (identical on every rank) + this rank's camera + upstream gradients."""
+    from gaussian_splatting_b200 import synthetic
+    cfg = synthetic.CONFIGS[args.workload]
+    P = args.P or cfg.P
+    gs, cam = synthetic.make_scene(cfg, P=P, yaw_deg=45.0 * rank)
+    W, H = cfg.W, cfg.H
+    g = torch.Generator().manual_seed(1000 + cfg.seed)
+    target, target_d = synthetic.make_targets(W, H, cfg.seed)
+    dc = (torch.rand(3, H, W, generator=g) - 0.5) / (3 * H * W)
+    dd = (torch.rand(1, H, W, generator=g) - 0.5) * 0.1 / (H * W)
+    s = dict(cam)
+    s.update(bg=torch.zeros(3), scale_modifier=1.0, sh_degree=3, prefiltered=False, debug=False)
+    wl = dict(cfg=cfg, P=P, W=W, H=H, gs=gs, s=s, dc=dc, dd=dd, target=target, target_d=target_d)
+    if device is not None:
+        wl["params"] = {k: v.to(device).requires_grad_(True) for k, v in gs.items()}
+        wl["means2D"] = torch.zeros(P, 3, device=device, requires_grad=True)
+        wl["dc_dev"], wl["dd_dev"] = dc.to(device), dd.to(device)
+    return wl
+
+
+def settings_of(module, s, device, cam_dev=None):
+    cam_dev = cam_dev or {}
+    return module.GaussianRasterizationSettings(
+        image_height=int(s["image_height"]), image_width=int(s["image_width"]),
+        tanfovx=float(s["tanfovx"]), tanfovy=float(s["tanfovy"]), bg=cam_dev.get("bg", s["bg"].to(device)),
+        scale_modifier=1.0, viewmatrix=cam_dev.get("viewmatrix", s["viewmatrix"].to(device)),
+        projmatrix=cam_dev.get("projmatrix", s["projmatrix"].to(device)), sh_degree=3,
+        campos=cam_dev.get("campos", s["campos"].to(device)), prefiltered=False, debug=False,
+        antialiasing=bool(s["antialiasing"]))
+
+
+def make_steps(module, wl, device, flat=None):
+    """Returns (step_resident, step_forward_only, step_e2e, e2e_bytes)."""
+    params, means2D = wl["params"], wl["means2D"]
+    leaves = list(params.values()) + [means2D]
+    rs = settings_of(module, wl["s"], device)
+    rast = module.GaussianRasterizer(rs)
+    dc, dd = wl["dc_dev"], wl["dd_dev"]
+
+    def clear():
+        for t in leaves:
+            t.grad = None
+
+    def step_resident():
+        clear()
+        color, radii, invd = rast(means3D=params["means3D"], means2D=means2D, opacities=params["opacities"],
+                                  shs=params["shs"], scales=params["scales"], rotations=params["rotations"])
+        torch.autograd.backward([color, invd], [dc, dd])
+        if flat is not None:
+            flat.all_reduce()
+
+    def step_forward_only():
+        with torch.no_grad():
+            rast(means3D=params["means3D"], means2D=means2D, opacities=params["opacities"],
+                 shs=params["shs"], scales=params["scales"], rotations=params["rotations"])
+
+    # ---- end to end: this step's camera and targets come from pinned host memory, loss goes back
+    H, W = wl["H"], wl["W"]
+    cam_host = torch.cat([wl["s"]["viewmatrix"].reshape(-1), wl["s"]["projmatrix"].reshape(-1),
+                          wl["s"]["campos"].reshape(-1)]).pin_memory()
+    tgt_host = torch.cat([wl["target"].reshape(-1), wl["target_d"].reshape(-1)]).pin_memory()
+    cam_dev = torch.empty_like(cam_host, device=device)
+    tgt_dev = torch.empty_like(tgt_host, device=device)
+    loss_host = torch.zeros(1).pin_memory()
+    bg_dev = wl["s"]["bg"].to(device)
+    h2d = cam_host.numel() * 4 + tgt_host.numel() * 4
+    d2h = 4
+
+    def step_e2e():
+        clear()
+        cam_dev.copy_(cam_host, non_blocking=True)
+        tgt_dev.copy_(tgt_host, non_blocking=True)
+        cd = dict(viewmatrix=cam_dev[:16].view(4, 4), projmatrix=cam_dev[16:32].view(4, 4), campos=cam_dev[32:35],
+                  bg=bg_dev)
+        r = module.GaussianRasterizer(settings_of(module, wl["s"], device, cd))
+        color, radii, invd = r(means3D=params["means3D"], means2D=means2D, opacities=params["opacities"],
+                               shs=params["shs"], scales=params["scales"], rotations=params["rotations"])
+        tgt = tgt_dev[:3 * H * W].view(3, H, W)
+        tgt_d = tgt_dev[3 * H * W:].view(1, H, W)
+        loss = (color - tgt).abs().mean() + 0.1 * (invd - tgt_d).abs().mean()
+        loss.backward()
+        if flat is not None:
+            flat.all_reduce()
+        loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return float(loss_host[0])
+
+    return step_resident, step_forward_only, step_e2e, (h2d, d2h)
+
+
+def timed_loop(step, steps, warmup, world, device, on_start=None):
+    """W untimed steps, then exactly K steps between barrier + synchronize; device time by CUDA
+    events on the launching stream, max over ranks.  Returns (ms_total_max, wall t0, wall t1)."""
+    for _ in range(warmup):
+        step()
+    torch.cuda.synchronize(device)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(device)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if on_start is not None:
+        on_start()
+    t0 = time.time()
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize(device)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(device)
+    t1 = time.time()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], device=device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t[0])
+    return ms, t0, t1
+
+
+# ------------------------------------------------------------------ roofline bookkeeping
+def stage_model(work):
+    """Algorithmic bytes / flops of each stage of OUR path for one step.
+    HBM stages: minimum bytes the stage must move; render stages: FLOP model of SURVEY.md §8d."""
+    P, V, R, T, N = work["P"], work["V"], work["R"], work["T"], work["N"]
+    Wf, Wb, Bp = work["Wf"], work["Wb"], work["Bp"]
+    tile_passes = max(1, (max(T, 1).bit_length() + 7) // 8)
+    return {
+        # means 12 + radii 4 + depth key 8 + rect 8 for all; scales/rot/opacity/SH 224 read + record 64 written for visible
+        "preprocess": ("hbm", 32 * P + 288 * V),
+        # 4 LSD passes over P 8-byte items: histogram read + scatter read + scatter write
+        "depth_sort": ("hbm", 4 * 24 * P),
+        # sorted keys 8 + rect gather 8 + counts write 4, then read 4 + write 4
+        "scan": ("hbm", 28 * P),
+        # key 8 + rect 8 + offset 4 per Gaussian, 8 per instance written
+        "emit": ("hbm", 20 * P + 8 * R),
+        # per pass: histogram read 8 + scatter read 8 + write 8 (last pass writes 4 + 4)
+        "tile_sort": ("hbm", tile_passes * 24 * R),
+        "tile_ranges": ("hbm", 4 * R + 8 * T),
+        "render_fwd": ("fp32", 14 * Wf + 11 * Bp),
+        "render_bwd": ("fp32", 14 * Wb + 75 * Bp),
+        # dense outputs for every Gaussian + visible reads (+ 48 B accumulator)
+        "preprocess_bwd": ("hbm", 236 * P + 287 * V + 48 * V),
+    }
+
+
+def rooflines(stage_ms, work, peaks, sm_mhz):
+    model = stage_model(work)
+    fp32_peak = SM_COUNT_B200 * FP32_LANES_PER_SM * 2 * peaks["sm_max_mhz"] * 1e6 / 1e12   # TFLOP/s at max clock
+    out = []
+    for name, (ms_total, calls) in stage_ms.items():
+        if not calls or name not in model:
+            continue
+        ms = ms_total / calls
+        bound, amount = model[name]
+        if bound == "hbm":
+            achieved = amount / (ms * 1e-3) / 1e9
+            peak, unit = peaks["hbm_gbs"], "GB/s"
+        else:
+            achieved = amount / (ms * 1e-3) / 1e12
+            peak, unit = fp32_peak, "TFLOP/s"
+        out.append(dict(stage=name, ms=round(ms, 4), bound=bound, algorithmic=int(amount), achieved=round(achieved, 3),
+                        peak=round(peak, 1), unit=unit, frac=round(achieved / peak, 4)))
+    out.sort(key=lambda d: -d["ms"])
+    return out
+
+
+def measure_work(wl, device):
+    """Work descriptors of this rank's view from the state of one forward (independent counting pass)."""
+    from gaussian_splatting_b200 import rasterizer
+    import diff_gaussian_rasterization as dgr
+    rs = settings_of(dgr, wl["s"], device)
+    p = wl["params"]
+    e = torch.Tensor([])
+    st = {}
+    with torch.no_grad():
+        R, color, radii, *_ = rasterizer._forward_native(rs, p["means3D"], p["shs"], e, p["opacities"], p["scales"],
+                                                         p["rotations"], e, state_out=st)
+    c = st["work_counts"].cpu().tolist()
+    W, H = wl["W"], wl["H"]
+    return dict(P=wl["P"], V=int((radii > 0).sum()), R=int(R), T=((W + 15) // 16) * ((H + 15) // 16), N=W * H,
+                Wf=int(c[0]), Bp=int(c[1]), Wb=int(c[2]))
+
+
+# ------------------------------------------------------------------ CPU baseline (oracle port)
+def cpu_oracle_iteration(wl, threads, reps=1):
+    """One full fwd+bwd of the CPU oracle (C restatement of the reference kernels) on the host.
+    Returns (seconds per iteration, description)."""
+    from oracle import cpu_ref
+    cpu_ref.build()
+    cpu_ref.set_threads(threads)
+    gs = {k: v.numpy() for k, v in wl["gs"].items()}
+    s = {k: (v.numpy() if isinstance(v, torch.Tensor) else v) for k, v in wl["s"].items()}
+    dc, dd = wl["dc"].numpy(), wl["dd"].numpy().reshape(-1)
+    best = None
+    for _ in range(reps):
+        t0 = time.time()
+        fw = cpu_ref.forward(gs, s)
+        cpu_ref.backward(fw, s, dc, dd, restored=True)
+        dt = time.time() - t0
+        best = dt if best is None else min(best, dt)
+    return best, f"full workload ({wl['cfg'].name}: P={wl['P']}, {wl['W']}x{wl['H']}), fwd+bwd, best of {reps}"
+
+
+# ------------------------------------------------------------------ arms
+def init_dist(args):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def base_line(args, wl, world, impl):
+    return {
+        "metric": METRIC, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "impl": impl,
+        "config": {"workload": f"{wl['cfg'].name}: {wl['P']} Gaussians, {wl['W']}x{wl['H']}, SH degree 3, "
+                               f"antialiasing={bool(wl['s']['antialiasing'])}, fwd+bwd with colour and "
+                               "inverse-depth gradients, one camera per GPU per step",
+                   "parallelism": f"view-parallel x{world}" if world > 1 else "single GPU",
+                   "l2_policy": f"inputs larger than L2 ({wl['P'] * 236 / 1e6:.0f} MB of Gaussian parameters read per step "
+                                "vs 126 MB L2); no explicit flush",
+                   "seed": wl["cfg"].seed},
+    }
+
+
+def run_gpu_arm(args, module, impl, rank, world, local):
+    device = torch.device("cuda", local)
+    torch.cuda.set_device(device)
+    if world > 1 and not dist.is_initialized():
+        dist.init_process_group("nccl", device_id=device)
+    wl = build_workload(args, rank, device)
+    flat = None
+    if world > 1:
+        from gaussian_splatting_b200.view_parallel import FlatGradients
+        flat = FlatGradients(list(wl["params"].values()))
+    step, step_fwd, step_e2e, (h2d, d2h) = make_steps(module, wl, device, flat)
+    ours = impl == "ours"
+    if ours:
+        from gaussian_splatting_b200 import _lib
+        work = measure_work(wl, device)
+
+    sampler = ClockSampler(local)
+    sampler.start()
+    mark = {}
+
+    def on_start():
+        if ours:
+            _lib.profile_enable(True)
+            mark["l0"] = _lib.launch_count()
+
+    ms, t0, t1 = timed_loop(step, args.steps, args.warmup, world, device, on_start)
+    clocks = sampler.stop(t0, t1)
+    line = base_line(args, wl, world, impl)
+    if ours:
+        launches = _lib.launch_count() - mark["l0"]
+        stage_ms = _lib.profile_collect()
+        _lib.profile_enable(False)
+    ms_step = ms / args.steps
+    line.update(value=round(world * 1000.0 / ms_step, 3), ms_per_step=round(ms_step, 4), clocks=clocks)
+
+    # forward-only FPS
+    ms_f, _, _ = timed_loop(step_fwd, args.steps, 3, world, device)
+    line["fwd_fps"] = round(world * 1000.0 * args.steps / ms_f, 2)
+
+    if not args.no_e2e:
+        ms_e, _, _ = timed_loop(step_e2e, args.steps, 3, world, device)
+        line["e2e"] = {"value": round(world * 1000.0 * args.steps / ms_e, 3), "unit": UNIT,
+                       "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                       "what": "camera + target image/depth from pinned host memory, L1 losses in torch, "
+                               "backward, loss scalar read back; Gaussian parameters stay resident (they "
+                               "are the model)"}
+    if ours:
+        peaks = load_peaks()
+        stages = rooflines(stage_ms, work, peaks, clocks.get("sm_mhz"))
+        line["gpu_launches"] = int(launches)
+        line["work"] = work
+        line["stages"] = stages
+        top = stages[0]
+        line["roofline"] = {"kernel": top["stage"], "bound": top["bound"], "achieved": top["achieved"],
+                            "peak": top["peak"], "unit": top["unit"], "frac": top["frac"], "traffic": None,
+                            "ms": top["ms"],
+                            "peak_source": (f"{peaks['source']} copy bandwidth (MEASURED_PEAKS.json)" if top["bound"] == "hbm"
+                                            else "FP32 CUDA-core peak = 148 SMs x 128 lanes x 2 x max SM clock")}
+        hbm = [s for s in stages if s["bound"] == "hbm"]
+        if hbm:
+            line["roofline_hbm"] = hbm[0]
+    else:
+        line["gpu_launches"] = 0          # none of this repo's kernels run in the reference arm
+    return line, wl
+
+
+def run_cpu_port_arm(args, why):
+    """Fallback of --impl reference when the reference CUDA build is absent: CPU oracle port."""
+    wl = build_workload(args, 0, None)
+    threads = min(os.cpu_count() or 1, 256)
+    for _ in range(min(args.warmup, 1)):
+        cpu_oracle_iteration(wl, threads)
+    t = [cpu_oracle_iteration(wl, threads)[0] for _ in range(min(args.steps, 3))]
+    sec = sum(t) / len(t)
+    line = base_line(args, wl, 1, "reference")
+    line.update(value=round(1.0 / sec, 4), ms_per_step=round(sec * 1e3, 2), steps=len(t), gpu_launches=0,
+                cpu_baseline={"value": round(1.0 / sec, 4), "unit": UNIT, "cores": threads, "kind": "port",
+                              "sample": f"full workload, mean of {len(t)} iterations", "why": why},
+                e2e={"value": round(1.0 / sec, 4), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0})
+    return line
+
+
+def main():
+    args = parse_args()
+    rank, world, local = init_dist(args)
+    if args.impl == "reference":
+        if rank != 0:
+            return 0                     # the reference is single-GPU: rank 0 alone runs it
+        from oracle import ref_loader
+        why = None
+        if not torch.cuda.is_available():
+            why = "no CUDA device"
+        elif not ref_loader.available(args.ref_variant):
+            why = f"oracle/_ref/{args.ref_variant} not built"
+        if why is None:
+            try:
+                ref = ref_loader.load(args.ref_variant)
+            except Exception as ex:      # noqa: BLE001
+                why = f"reference build failed to load: {ex}"
+        if why is not None:
+            print(json.dumps(run_cpu_port_arm(args, why)))
+            return 0
+        line, wl = run_gpu_arm(args, ref, "reference", 0, 1, local)
+        line["n_gpus"] = 1
+        line["reference"] = {"kind": "reference", "what": "the reference's own CUDA rasterizer "
+                             "(submodules/diff-gaussian-rasterization) compiled for sm_100 by oracle/build_ref.py; "
+                             f"variant '{args.ref_variant}' (SURVEY.md F1-F3 repairs)"}
+        print(json.dumps(line))
+        return 0
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (the product has no CPU path)")
+    import diff_gaussian_rasterization as dgr
+    line, wl = run_gpu_arm(args, dgr, "ours", rank, world, local)
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        threads = min(os.cpu_count() or 1, 256)
+        sec, sample = cpu_oracle_iteration(wl, threads)
+        line["cpu_baseline"] = {"value": round(1.0 / sec, 4), "unit": UNIT, "cores": threads, "kind": "port",
+                                "sample": sample}
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1 and dist.is_initialized():
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -57,7 +57,10 @@ EXPORTS = (
     "gsr_version", "gsr_last_error", "gsr_geom_bytes", "gsr_img_bytes", "gsr_bin_bytes",
     "gsr_scratch_bytes", "gsr_forward_stage1", "gsr_forward_stage2", "gsr_forward", "gsr_backward",
     "gsr_mark_visible", "gsr_debug_sorted_keys", "gsr_debug_state_ptrs", "gsr_flat_grad_floats",
+    "gsr_debug_count_work",
+    "gsr_profile_enable", "gsr_profile_collect", "gsr_stage_name", "gsr_launch_count",
 )
+STAGE_COUNT = 9
 
 _lib = None
 
@@ -99,8 +102,34 @@ def load():
     lib.gsr_debug_sorted_keys.argtypes = [PP, PB, C.c_int64, C.c_void_p, C.c_void_p]
     lib.gsr_debug_state_ptrs.restype = C.c_int
     lib.gsr_debug_state_ptrs.argtypes = [PP, PB, C.c_int64] + [C.POINTER(C.c_void_p)] * 5
+    lib.gsr_debug_count_work.restype = C.c_int
+    lib.gsr_debug_count_work.argtypes = [PP, PB, C.c_int64, C.c_void_p, C.c_void_p]
+    lib.gsr_profile_enable.restype = C.c_int
+    lib.gsr_profile_enable.argtypes = [C.c_int]
+    lib.gsr_profile_collect.restype = C.c_int
+    lib.gsr_profile_collect.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_int64)]
+    lib.gsr_stage_name.restype = C.c_char_p
+    lib.gsr_stage_name.argtypes = [C.c_int]
+    lib.gsr_launch_count.restype = C.c_uint64
     _lib = lib
     return lib
+
+
+def profile_enable(on=True):
+    check(load().gsr_profile_enable(int(bool(on))))
+
+
+def profile_collect():
+    """{stage name: (total ms, calls)} of the spans recorded since the last collect."""
+    lib = load()
+    ms = (C.c_double * STAGE_COUNT)()
+    n = (C.c_int64 * STAGE_COUNT)()
+    check(lib.gsr_profile_collect(ms, n))
+    return {lib.gsr_stage_name(i).decode(): (ms[i], n[i]) for i in range(STAGE_COUNT)}
+
+
+def launch_count():
+    return int(load().gsr_launch_count())
 
 
 def check(rc):

@@ -3,6 +3,7 @@
 #include <stdarg.h>
 #include <stdio.h>
 #include <string.h>
+#include <vector>
 #include "common.cuh"
 
 namespace gsr {
@@ -26,6 +27,33 @@ int check_stage(const char* stage, bool debug, cudaStream_t stream) {
         return GSR_ERR_CUDA;
     }
     return GSR_OK;
+}
+
+// ---- measurement hooks ----------------------------------------------------
+unsigned long long g_launches = 0;
+static bool g_profile = false;
+struct ProfSpan { int stage; cudaEvent_t a, b; };
+static std::vector<ProfSpan> g_spans;       // recorded, not yet collected
+static std::vector<cudaEvent_t> g_free;     // event pool
+static cudaEvent_t g_open[GSR_STAGE_COUNT];
+
+static cudaEvent_t take_event() {
+    cudaEvent_t e = nullptr;
+    if (!g_free.empty()) { e = g_free.back(); g_free.pop_back(); }
+    else cudaEventCreate(&e);
+    return e;
+}
+void profile_begin(int stage, cudaStream_t st) {
+    if (!g_profile) return;
+    g_open[stage] = take_event();
+    cudaEventRecord(g_open[stage], st);
+}
+void profile_end(int stage, cudaStream_t st) {
+    if (!g_profile || !g_open[stage]) return;
+    cudaEvent_t b = take_event();
+    cudaEventRecord(b, st);
+    g_spans.push_back({stage, g_open[stage], b});
+    g_open[stage] = nullptr;
 }
 
 static int validate(const GsrParams* p, const GsrBuffers* buf) {
@@ -106,6 +134,36 @@ size_t gsr_scratch_bytes(int32_t P, int32_t W, int32_t H, int64_t R) {
     (void)W; (void)H;
     size_t b; Scratch::carve(nullptr, (size_t)(P > 0 ? P : 1), (size_t)(R > 0 ? R : 0), &b); return b;
 }
+
+int gsr_profile_enable(int on) {
+    g_profile = on != 0;
+    if (!g_profile) {
+        for (auto& sp : g_spans) { g_free.push_back(sp.a); g_free.push_back(sp.b); }
+        g_spans.clear();
+    }
+    return GSR_OK;
+}
+
+int gsr_profile_collect(double* ms_sum, int64_t* calls) {
+    for (auto& sp : g_spans) {
+        GSR_CUDA_TRY(cudaEventSynchronize(sp.b));
+        float ms = 0.f;
+        GSR_CUDA_TRY(cudaEventElapsedTime(&ms, sp.a, sp.b));
+        if (ms_sum) ms_sum[sp.stage] += ms;
+        if (calls) calls[sp.stage] += 1;
+        g_free.push_back(sp.a); g_free.push_back(sp.b);
+    }
+    g_spans.clear();
+    return GSR_OK;
+}
+
+const char* gsr_stage_name(int stage) {
+    static const char* names[GSR_STAGE_COUNT] = {"preprocess", "depth_sort", "scan", "emit", "tile_sort",
+                                                 "tile_ranges", "render_fwd", "render_bwd", "preprocess_bwd"};
+    return stage >= 0 && stage < GSR_STAGE_COUNT ? names[stage] : "?";
+}
+
+uint64_t gsr_launch_count(void) { return g_launches; }
 
 int32_t gsr_flat_grad_floats(int32_t M) { return 3 + 3 * M + 1 + 3 + 4; }
 
@@ -190,6 +248,16 @@ int gsr_debug_sorted_keys(const GsrParams* p, const GsrBuffers* buf, int64_t R, 
     ImgState im = ImgState::carve(buf->img, (size_t)p->W * p->H, tiles_of(p->W, p->H), nullptr);
     BinState b = BinState::carve(buf->bin, (size_t)R, nullptr);
     return launch_rebuild_keys(*p, g, im, b, R, keys_out, (cudaStream_t)stream);
+}
+
+int gsr_debug_count_work(const GsrParams* p, const GsrBuffers* buf, int64_t R, uint64_t* counts, void* stream) {
+    int rc = validate(p, buf);
+    if (rc) return rc;
+    if (!counts) { set_error("counts is required"); return GSR_ERR_INVALID_ARG; }
+    GeomState g = GeomState::carve(buf->geom, p->P, nullptr);
+    ImgState im = ImgState::carve(buf->img, (size_t)p->W * p->H, tiles_of(p->W, p->H), nullptr);
+    BinState b = BinState::carve(buf->bin, (size_t)R, nullptr);
+    return launch_count_work(*p, g, im, b, reinterpret_cast<unsigned long long*>(counts), (cudaStream_t)stream);
 }
 
 int gsr_debug_state_ptrs(const GsrParams* p, const GsrBuffers* buf, int64_t R, const uint32_t** point_list,

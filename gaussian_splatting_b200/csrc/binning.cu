@@ -174,13 +174,13 @@ radix_scatter_kernel(const uint64_t* __restrict__ in, uint32_t n, int shift,
 static int radix_pass(const uint64_t* src, uint64_t* dst, uint32_t n, int shift, Scratch s,
                       bool split, uint32_t* out_lo, uint32_t* out_hi, cudaStream_t st) {
     const uint32_t nb = div_up(n, SORT_CHUNK);
-    radix_hist_kernel<<<nb, SORT_THREADS, 0, st>>>(src, n, shift, s.hist, nb);
-    radix_rowscan_kernel<<<256, 256, 0, st>>>(s.hist, nb, s.digit_tot);
+    GSR_LAUNCH(radix_hist_kernel, nb, SORT_THREADS, 0, st, src, n, shift, s.hist, nb);
+    GSR_LAUNCH(radix_rowscan_kernel, 256, 256, 0, st, s.hist, nb, s.digit_tot);
     if (split)
-        radix_scatter_kernel<true><<<nb, SORT_THREADS, 0, st>>>(src, n, shift, s.hist, nb, s.digit_tot,
+        GSR_LAUNCH(radix_scatter_kernel<true>, nb, SORT_THREADS, 0, st, src, n, shift, s.hist, nb, s.digit_tot,
                                                                 nullptr, out_lo, out_hi);
     else
-        radix_scatter_kernel<false><<<nb, SORT_THREADS, 0, st>>>(src, n, shift, s.hist, nb, s.digit_tot,
+        GSR_LAUNCH(radix_scatter_kernel<false>, nb, SORT_THREADS, 0, st, src, n, shift, s.hist, nb, s.digit_tot,
                                                                  dst, nullptr, nullptr);
     return GSR_OK;
 }
@@ -308,17 +308,23 @@ int launch_depth_order_and_scan(const GsrParams& p, GeomState g, Scratch s, int3
     // depth_a holds depth_bits<<32 | id (written by preprocess). 4 stable LSD passes.
     uint64_t* a = s.depth_a;
     uint64_t* b = s.depth_b;
-    for (int pass = 0; pass < 4; pass++) {
-        radix_pass(a, b, P, 32 + 8 * pass, s, false, nullptr, nullptr, st);
-        uint64_t* tmp = a; a = b; b = tmp;
+    {
+        StageTimer tm(GSR_STAGE_DEPTH_SORT, st);
+        for (int pass = 0; pass < 4; pass++) {
+            radix_pass(a, b, P, 32 + 8 * pass, s, false, nullptr, nullptr, st);
+            uint64_t* tmp = a; a = b; b = tmp;
+        }
     }
     int rc = check_stage("depth sort", p.debug, st);
     if (rc) return rc;
     // a == s.depth_a again (even number of passes)
-    const uint32_t nb = div_up(P, SCAN_CHUNK);
-    scan_count_kernel<<<nb, SCAN_THREADS, 0, st>>>(a, s.rects, P, s.offsets, s.scan_blocks);
-    scan_blocksums_kernel<<<1, 256, 0, st>>>(s.scan_blocks, nb, s.counters);
-    scan_apply_kernel<<<nb, SCAN_THREADS, 0, st>>>(s.offsets, P, s.scan_blocks);
+    {
+        StageTimer tm(GSR_STAGE_SCAN, st);
+        const uint32_t nb = div_up(P, SCAN_CHUNK);
+        GSR_LAUNCH(scan_count_kernel, nb, SCAN_THREADS, 0, st, a, s.rects, P, s.offsets, s.scan_blocks);
+        GSR_LAUNCH(scan_blocksums_kernel, 1, 256, 0, st, s.scan_blocks, nb, s.counters);
+        GSR_LAUNCH(scan_apply_kernel, nb, SCAN_THREADS, 0, st, s.offsets, P, s.scan_blocks);
+    }
     rc = check_stage("tile-count scan", p.debug, st);
     if (rc) return rc;
     if (num_rendered_host)
@@ -335,7 +341,10 @@ int launch_binning(const GsrParams& p, GeomState g, ImgState im, BinState b, Scr
     GSR_CUDA_TRY(cudaMemsetAsync(im.ranges, 0, (size_t)T * sizeof(uint2), st));   // rasterizer_impl.cu:342
     if (R <= 0) return GSR_OK;
     const uint32_t n = (uint32_t)R;
-    emit_instances_kernel<<<div_up(P, 256), 256, 0, st>>>(s.depth_a, s.rects, s.offsets, P, gx, s.inst_a);
+    {
+        StageTimer tm(GSR_STAGE_EMIT, st);
+        GSR_LAUNCH(emit_instances_kernel, div_up(P, 256), 256, 0, st, s.depth_a, s.rects, s.offsets, P, gx, s.inst_a);
+    }
     int rc = check_stage("emit instances", p.debug, st);
     if (rc) return rc;
     // reference sorts bits [0, 32+getHigherMsb(T)) (rasterizer_impl.cu:332-340); the low 32
@@ -344,14 +353,20 @@ int launch_binning(const GsrParams& p, GeomState g, ImgState im, BinState b, Scr
     const int passes = (bits + 7) / 8;
     uint64_t* a = s.inst_a;
     uint64_t* c = s.inst_b;
-    for (int pass = 0; pass < passes; pass++) {
-        const bool last = pass == passes - 1;
-        radix_pass(a, c, n, 32 + 8 * pass, s, last, b.point_list, s.tile_ids, st);
-        uint64_t* tmp = a; a = c; c = tmp;
+    {
+        StageTimer tm(GSR_STAGE_TILE_SORT, st);
+        for (int pass = 0; pass < passes; pass++) {
+            const bool last = pass == passes - 1;
+            radix_pass(a, c, n, 32 + 8 * pass, s, last, b.point_list, s.tile_ids, st);
+            uint64_t* tmp = a; a = c; c = tmp;
+        }
     }
     rc = check_stage("tile sort", p.debug, st);
     if (rc) return rc;
-    tile_ranges_kernel<<<div_up(n, 256), 256, 0, st>>>(s.tile_ids, n, im.ranges);
+    {
+        StageTimer tm(GSR_STAGE_TILE_RANGES, st);
+        GSR_LAUNCH(tile_ranges_kernel, div_up(n, 256), 256, 0, st, s.tile_ids, n, im.ranges);
+    }
     return check_stage("tile ranges", p.debug, st);
 }
 
@@ -359,7 +374,7 @@ int launch_rebuild_keys(const GsrParams& p, GeomState g, ImgState im, BinState b
                         uint64_t* keys_out, cudaStream_t st) {
     const uint32_t gx = div_up(p.W, TILE_X), gy = div_up(p.H, TILE_Y);
     if (R <= 0) return GSR_OK;
-    rebuild_keys_kernel<<<gx * gy, 128, 0, st>>>(im.ranges, gx * gy, b.point_list, g.rec, keys_out);
+    GSR_LAUNCH(rebuild_keys_kernel, gx * gy, 128, 0, st, im.ranges, gx * gy, b.point_list, g.rec, keys_out);
     return check_stage("rebuild keys", true, st);
 }
 

@@ -157,6 +157,22 @@ int  check_stage(const char* stage, bool debug, cudaStream_t stream);
         }                                                                         \
     } while (0)
 
+// ---- measurement hooks (api.cu) ---------------------------------------------
+extern unsigned long long g_launches;
+#define GSR_LAUNCH(kernel, grid, block, smem, st, ...)              \
+    do {                                                            \
+        kernel<<<(grid), (block), (smem), (st)>>>(__VA_ARGS__);     \
+        ++gsr::g_launches;                                          \
+    } while (0)
+
+void profile_begin(int stage, cudaStream_t st);
+void profile_end(int stage, cudaStream_t st);
+struct StageTimer {     // brackets a launcher's work with events when profiling is enabled
+    int stage; cudaStream_t st;
+    StageTimer(int s, cudaStream_t t) : stage(s), st(t) { profile_begin(stage, st); }
+    ~StageTimer() { profile_end(stage, st); }
+};
+
 // ---- stage launchers (defined in the per-stage .cu files) ------------------
 int launch_preprocess(const GsrParams& p, GeomState g, Scratch s, int32_t* radii, cudaStream_t st);
 int launch_mark_visible(int P, const float* means, const float* view, uint8_t* present, cudaStream_t st);
@@ -168,6 +184,8 @@ int launch_render_backward(const GsrParams& p, GeomState g, ImgState im, BinStat
                            const float* dL_dpix, const float* dL_dinvdepth, cudaStream_t st);
 int launch_preprocess_backward(const GsrParams& p, GeomState g, Scratch s, const int32_t* radii,
                                bool have_invdepth, const GsrBackwardIO& io, cudaStream_t st);
+int launch_count_work(const GsrParams& p, GeomState g, ImgState im, BinState b, unsigned long long* counts,
+                      cudaStream_t st);
 int launch_rebuild_keys(const GsrParams& p, GeomState g, ImgState im, BinState b, int64_t R,
                         uint64_t* keys_out, cudaStream_t st);
 

@@ -201,13 +201,14 @@ int launch_preprocess(const GsrParams& p, GeomState g, Scratch s, int32_t* radii
     const float focal_x = p.W / (2.0f * p.tanfovx);
     const int gx = (p.W + TILE_X - 1) / TILE_X, gy = (p.H + TILE_Y - 1) / TILE_Y;
     const int blocks = (p.P + PRE_THREADS - 1) / PRE_THREADS;
-    preprocess_fwd_kernel<<<blocks, PRE_THREADS, 0, st>>>(p, focal_x, focal_y, gx, gy, g.rec, s.rects,
+    StageTimer tm(GSR_STAGE_PREPROCESS, st);
+    GSR_LAUNCH(preprocess_fwd_kernel, blocks, PRE_THREADS, 0, st, p, focal_x, focal_y, gx, gy, g.rec, s.rects,
                                                           s.depth_a, radii);
     return check_stage("preprocess", p.debug, st);
 }
 
 int launch_mark_visible(int P, const float* means, const float* view, uint8_t* present, cudaStream_t st) {
-    mark_visible_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, means, view, present);
+    GSR_LAUNCH(mark_visible_kernel, (P + 255) / 256, 256, 0, st, P, means, view, present);
     return check_stage("markVisible", false, st);
 }
 

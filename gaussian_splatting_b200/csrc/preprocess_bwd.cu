@@ -363,7 +363,8 @@ int launch_preprocess_backward(const GsrParams& p, GeomState g, Scratch s, const
     const float focal_y = p.H / (2.0f * p.tanfovy);
     const float focal_x = p.W / (2.0f * p.tanfovx);
     const int blocks = (p.P + PB_THREADS - 1) / PB_THREADS;
-    preprocess_bwd_kernel<<<blocks, PB_THREADS, 0, st>>>(p, focal_x, focal_y, g.rec, radii, s.acc,
+    StageTimer tm(GSR_STAGE_PREPROCESS_BWD, st);
+    GSR_LAUNCH(preprocess_bwd_kernel, blocks, PB_THREADS, 0, st, p, focal_x, focal_y, g.rec, radii, s.acc,
                                                          have_invdepth, io);
     return check_stage("preprocess backward", p.debug, st);
 }

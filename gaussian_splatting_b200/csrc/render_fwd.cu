@@ -123,11 +123,65 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     if (rank == 0) tile_max_contrib[tile] = s_max;
 }
 
-int launch_render_forward(const GsrParams& p, GeomState g, ImgState im, BinState b,
-                          float* out_color, float* out_invdepth, cudaStream_t st) {
+// Work-descriptor counting pass: independent of the kernel under test, one
+// thread per pixel reading the records straight from global memory.  counts[0] += entries
+// visited by the forward blend (Wf), counts[1] += blended (pixel, Gaussian) pairs (Bp),
+// counts[2] += sum of n_contrib (Wb).
+__global__ void __launch_bounds__(TILE_PIX)
+count_work_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
+                  const GsRecord* __restrict__ rec, unsigned long long* __restrict__ counts) {
+    const uint32_t horizontal_blocks = (W + TILE_X - 1) / TILE_X;
+    const uint32_t tile = blockIdx.y * horizontal_blocks + blockIdx.x;
+    const uint2 pix = {blockIdx.x * TILE_X + threadIdx.x, blockIdx.y * TILE_Y + threadIdx.y};
+    const float2 pixf = {(float)pix.x, (float)pix.y};
+    const bool inside = pix.x < (uint32_t)W && pix.y < (uint32_t)H;
+    const uint2 range = ranges[tile];
+    unsigned long long visited = 0, blended = 0, last = 0;
+    float T = 1.0f;
+    if (inside) {
+        for (uint32_t i = range.x; i < range.y; i++) {
+            visited++;
+            const GsRecord r = rec[point_list[i]];
+            const float2 d = {r.q0.x - pixf.x, r.q0.y - pixf.y};
+            const float power = -0.5f * (r.q0.z * d.x * d.x + r.q1.x * d.y * d.y) - r.q0.w * d.x * d.y;
+            if (power > 0.0f) continue;
+            const float alpha = fminf(0.99f, r.q1.y * expf(power));
+            if (alpha < 1.0f / 255.0f) continue;
+            const float test_T = T * (1 - alpha);
+            if (test_T < 0.0001f) break;
+            T = test_T;
+            blended++;
+            last = visited;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        visited += __shfl_xor_sync(0xffffffffu, visited, o);
+        blended += __shfl_xor_sync(0xffffffffu, blended, o);
+        last += __shfl_xor_sync(0xffffffffu, last, o);
+    }
+    if (((threadIdx.y * TILE_X + threadIdx.x) & 31) == 0) {
+        atomicAdd(&counts[0], visited);
+        atomicAdd(&counts[1], blended);
+        atomicAdd(&counts[2], last);
+    }
+}
+
+int launch_count_work(const GsrParams& p, GeomState g, ImgState im, BinState b, unsigned long long* counts,
+                      cudaStream_t st) {
+    GSR_CUDA_TRY(cudaMemsetAsync(counts, 0, 3 * sizeof(unsigned long long), st));
     dim3 grid((p.W + TILE_X - 1) / TILE_X, (p.H + TILE_Y - 1) / TILE_Y, 1);
     dim3 block(TILE_X, TILE_Y, 1);
-    render_fwd_kernel<<<grid, block, 0, st>>>(im.ranges, b.point_list, p.W, p.H, g.rec, p.background,
+    count_work_kernel<<<grid, block, 0, st>>>(im.ranges, b.point_list, p.W, p.H, g.rec, counts);
+    return check_stage("count work", true, st);
+}
+
+int launch_render_forward(const GsrParams& p, GeomState g, ImgState im, BinState b,
+                          float* out_color, float* out_invdepth, cudaStream_t st) {
+    StageTimer tm(GSR_STAGE_RENDER_FWD, st);
+    dim3 grid((p.W + TILE_X - 1) / TILE_X, (p.H + TILE_Y - 1) / TILE_Y, 1);
+    dim3 block(TILE_X, TILE_Y, 1);
+    GSR_LAUNCH(render_fwd_kernel, grid, block, 0, st, im.ranges, b.point_list, p.W, p.H, g.rec, p.background,
                                               im.final_T, im.n_contrib, im.tile_max_contrib,
                                               out_color, out_invdepth);
     return check_stage("render forward", p.debug, st);

@@ -115,10 +115,12 @@ def _params(P, M, rs, bg, means3D, sh, colors_precomp, opacities, scales, rotati
     return p
 
 
-def _forward_native(rs, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp):
+def _forward_native(rs, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                    state_out=None):
     """Role of _C.rasterize_gaussians (ext.cpp:16 -> rasterize_points.cu:45-146).
 
-    Returns (num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, invdepths)."""
+    Returns (num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, invdepths).
+    state_out: optional dict that receives views of the binning / image state (parity tests)."""
     lib = _lib.load()
     if means3D.ndim != 2 or means3D.shape[1] != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
@@ -178,7 +180,33 @@ def _forward_native(rs, means3D, sh, colors_precomp, opacities, scales, rotation
         binb = torch.empty(lib.gsr_bin_bytes(R), dtype=torch.uint8, device=device)
         buf.bin, buf.bin_bytes = binb.data_ptr(), binb.numel()
         _lib.check(lib.gsr_forward_stage2(C.byref(p), C.byref(buf), C.byref(out), R, stream.cuda_stream))
+        if state_out is not None:
+            state_out.update(_inspect_state(lib, p, buf, R, geom, binb, img, stream))
     return R, color, radii, geom, binb, img, invdepth
+
+
+def _inspect_state(lib, p, buf, R, geom, binb, img, stream):
+    """Views of the forward state through the gsr_debug_* hooks: the reference's sorted key list
+    (tile<<32 | depth bits), point_list, ranges, final_T, n_contrib and the 16-float records."""
+    ptrs = [C.c_void_p() for _ in range(5)]
+    _lib.check(lib.gsr_debug_state_ptrs(C.byref(p), C.byref(buf), R, *[C.byref(x) for x in ptrs]))
+
+    def view(t, ptr, dtype, count):
+        off = ptr.value - t.data_ptr()
+        return t[off:off + count * torch.empty(0, dtype=dtype).element_size()].view(dtype)
+
+    N = p.W * p.H
+    T = ((p.W + 15) // 16) * ((p.H + 15) // 16)
+    counts = torch.zeros(3, dtype=torch.int64, device=geom.device)
+    if R > 0:
+        _lib.check(lib.gsr_debug_count_work(C.byref(p), C.byref(buf), R, counts.data_ptr(), stream.cuda_stream))
+    keys = torch.empty(max(R, 1), dtype=torch.int64, device=geom.device)
+    if R > 0:
+        _lib.check(lib.gsr_debug_sorted_keys(C.byref(p), C.byref(buf), R, keys.data_ptr(), stream.cuda_stream))
+    return dict(point_list=view(binb, ptrs[0], torch.int32, R), ranges=view(img, ptrs[1], torch.int32, 2 * T).view(T, 2),
+                final_T=view(img, ptrs[2], torch.float32, N), n_contrib=view(img, ptrs[3], torch.int32, N),
+                records=view(geom, ptrs[4], torch.float32, 16 * p.P).view(p.P, 16), point_list_keys=keys[:R],
+                work_counts=counts)
 
 
 def _backward_native(rs, means3D, radii, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,

@@ -155,6 +155,11 @@ int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,
  * expose point_list / ranges held in the state buffers.  Device pointers. */
 int gsr_debug_sorted_keys(const GsrParams* p, const GsrBuffers* buf, int64_t R,
                           uint64_t* keys_out /* R */, void* stream);
+/* Work descriptors of the last forward, by an independent counting pass:
+ * counts[0] = entries visited by the forward blend (Wf), counts[1] = blended (pixel, Gaussian)
+ * pairs (Bp), counts[2] = sum of n_contrib (Wb).  counts: device uint64[3]. Synchronises. */
+int gsr_debug_count_work(const GsrParams* p, const GsrBuffers* buf, int64_t R,
+                         uint64_t* counts, void* stream);
 int gsr_debug_state_ptrs(const GsrParams* p, const GsrBuffers* buf, int64_t R,
                          const uint32_t** point_list /* R */,
                          const uint32_t** ranges /* T*2 */,
@@ -163,6 +168,27 @@ int gsr_debug_state_ptrs(const GsrParams* p, const GsrBuffers* buf, int64_t R,
                          const float** records /* P*GSR_RECORD_FLOATS */);
 
 #define GSR_RECORD_FLOATS 16
+
+/* Measurement hooks used by bench.py (no effect on results).
+ * gsr_profile_enable(1): every stage launcher brackets its launches with CUDA events recorded
+ * on the launching stream (cudaEventRecord only; no synchronisation).  gsr_profile_collect
+ * waits for the recorded events, adds each stage's elapsed milliseconds / call counts into the
+ * two GSR_STAGE_COUNT-sized arrays (either may be NULL) and clears the record.
+ * gsr_launch_count: kernels launched by this library in this process so far. */
+#define GSR_STAGE_PREPROCESS      0
+#define GSR_STAGE_DEPTH_SORT      1
+#define GSR_STAGE_SCAN            2
+#define GSR_STAGE_EMIT            3
+#define GSR_STAGE_TILE_SORT       4
+#define GSR_STAGE_TILE_RANGES     5
+#define GSR_STAGE_RENDER_FWD      6
+#define GSR_STAGE_RENDER_BWD      7
+#define GSR_STAGE_PREPROCESS_BWD  8
+#define GSR_STAGE_COUNT           9
+int         gsr_profile_enable(int on);
+int         gsr_profile_collect(double* ms_sum, int64_t* calls);
+const char* gsr_stage_name(int stage);
+uint64_t    gsr_launch_count(void);
 
 /* View-parallel helper: number of floats per Gaussian in the
  * flat parameter-gradient buffer that is all-reduced (xyz 3, sh 3*M, opacity 1,

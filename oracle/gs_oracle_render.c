@@ -96,19 +96,40 @@ typedef struct {
     int P, W, H, gx;
     const uint32_t *ranges, *point_list, *n_contrib;
     const float *bg_color, *means2D, *conic_opacity, *colors, *depths, *final_Ts, *dL_dpixels, *dL_invdepths;
-    double* acc[GSO_MAX_THREADS];
+    double* acc;                       /* P x 10 global sums (fp64) */
+    double* local[GSO_MAX_THREADS];    /* per-thread scratch: one tile's range x 10 */
+    size_t local_cap[GSO_MAX_THREADS];
 } bwd_ctx;
+
+/* fp64 atomic add (CAS loop): tiles processed by different threads share Gaussians. */
+static inline void atomic_add_f64(double* addr, double v) {
+    uint64_t* p = (uint64_t*)addr;
+    uint64_t old = __atomic_load_n(p, __ATOMIC_RELAXED), nw;
+    do {
+        double d;
+        memcpy(&d, &old, 8);
+        d += v;
+        memcpy(&nw, &d, 8);
+    } while (!__atomic_compare_exchange_n(p, &old, nw, 1, __ATOMIC_RELAXED, __ATOMIC_RELAXED));
+}
 
 static void bwd_tiles(int lo, int hi, int tid, void* vp) {
     bwd_ctx* c = (bwd_ctx*)vp;
     const int W = c->W, H = c->H;
-    if (!c->acc[tid]) c->acc[tid] = (double*)calloc((size_t)c->P * 10, sizeof(double));
-    double* loc = c->acc[tid];
     const float ddelx_dx = 0.5 * W; /* backward.cu:529-530 */
     const float ddely_dy = 0.5 * H;
     for (int tile = lo; tile < hi; tile++) {
         const int bx = tile % c->gx, by = tile / c->gx;
         const uint32_t r0 = c->ranges[2 * tile], r1 = c->ranges[2 * tile + 1];
+        /* per-tile sums indexed by position in the tile's list, flushed once per tile */
+        const size_t need = (size_t)(r1 - r0) * 10;
+        if (need > c->local_cap[tid]) {
+            free(c->local[tid]);
+            c->local_cap[tid] = need * 2;
+            c->local[tid] = (double*)malloc(c->local_cap[tid] * sizeof(double));
+        }
+        double* loc = c->local[tid];
+        if (need) memset(loc, 0, need * sizeof(double));
         for (int ty = 0; ty < BLOCK_Y; ty++)
             for (int tx = 0; tx < BLOCK_X; tx++) {
                 const uint32_t px = bx * BLOCK_X + tx, py = by * BLOCK_Y + ty;
@@ -142,7 +163,7 @@ static void bwd_tiles(int lo, int hi, int tid, void* vp) {
                     T = T / (1.f - alpha);
                     const float dchannel_dcolor = alpha * T;
                     float dL_dalpha = 0.0f;
-                    double* a = loc + (size_t)id * 10;
+                    double* a = loc + (size_t)(r1 - r0 - k - 1) * 10;
                     for (int ch = 0; ch < 3; ch++) {
                         const float col = c->colors[id * 3 + ch];
                         accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
@@ -176,6 +197,12 @@ static void bwd_tiles(int lo, int hi, int tid, void* vp) {
                     a[9] += (double)(G * dL_dalpha);
                 }
             }
+        for (uint32_t k = 0; k < r1 - r0; k++) {
+            const double* a = loc + (size_t)k * 10;
+            double* g = c->acc + (size_t)c->point_list[r0 + k] * 10;
+            for (int j = 0; j < 10; j++)
+                if (a[j] != 0.0) atomic_add_f64(g + j, a[j]);
+        }
     }
 }
 
@@ -199,14 +226,10 @@ void gso_render_backward(int P, int W, int H, const uint32_t* ranges, const uint
     c->ranges = ranges; c->point_list = point_list; c->n_contrib = n_contrib; c->bg_color = bg_color;
     c->means2D = means2D; c->conic_opacity = conic_opacity; c->colors = colors; c->depths = depths;
     c->final_Ts = final_Ts; c->dL_dpixels = dL_dpixels; c->dL_invdepths = dL_invdepths;
+    c->acc = (double*)calloc((size_t)(P > 0 ? P : 1) * 10, sizeof(double));
     gso_parallel_for(tile_lo, tile_hi, 4, bwd_tiles, c);
-    double* acc = NULL;
-    for (int t = 0; t < GSO_MAX_THREADS; t++) {
-        if (!c->acc[t]) continue;
-        if (!acc) { acc = c->acc[t]; continue; }
-        for (size_t i = 0; i < (size_t)P * 10; i++) acc[i] += c->acc[t][i];
-        free(c->acc[t]);
-    }
+    double* acc = c->acc;
+    for (int t = 0; t < GSO_MAX_THREADS; t++) free(c->local[t]);
     for (int id = 0; id < P; id++) {
         static const double zero[10] = {0};
         const double* a = acc ? acc + (size_t)id * 10 : zero;
