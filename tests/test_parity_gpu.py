@@ -172,7 +172,7 @@ def test_mark_visible(dgr, oracle, ref_restored):
     assert (got.cpu().numpy() != cpu).sum() <= 2
 
 
-def test_three_pass_tile_sort(dgr, oracle):
+def test_three_pass_tile_sort(dgr, oracle, ref_restored):
     """T = 257*257 = 66049 tiles > 2^16: the tile ordering needs 3 radix passes (17 key bits)."""
     W = H = 4112
     gs, s = small_scene(P=3000, W=W, H=H, scale_mult=2.0, seed=12)
@@ -183,7 +183,16 @@ def test_three_pass_tile_sort(dgr, oracle):
     assert np.array_equal(got["point_list_keys"].view(np.uint64), want["keys"])
     assert np.array_equal(got["point_list"].view(np.uint32), want["point_list"])
     assert np.array_equal(got["ranges"].view(np.uint32), want["ranges"])
-    assert np.abs(got["color"] - want["color"]).max() <= IMG_TOL
+    # 17M pixels: the host libm expf and the device expf differ by an ulp on a few pairs, which
+    # flips the alpha < 1/255 skip test there (a 4e-3 step).  Against the CPU oracle the image is
+    # therefore checked up to a handful of such pixels; against the reference's CUDA build exactly.
+    bad = np.abs(got["color"] - want["color"]).max(axis=0) > IMG_TOL
+    assert bad.mean() < 1e-5 and np.abs(got["color"] - want["color"]).max() < 5e-3
+    ref = ref_forward_state(ref_restored, gs, s)
+    assert np.array_equal(got["point_list"], ref["point_list"])
+    assert np.array_equal(got["ranges"], ref["ranges"])
+    assert np.abs(got["color"] - ref["color"]).max() <= IMG_TOL
+    assert np.array_equal(got["n_contrib"], ref["n_contrib"])
 
 
 # ---------------------------------------------------------------- vs the reference's CUDA build
