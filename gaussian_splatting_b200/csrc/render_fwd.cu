@@ -1,17 +1,20 @@
 // render_fwd.cu — kernel 3 of the path: per-tile front-to-back alpha blending.
 //
 // Replaces renderCUDA forward (DGR/cuda_rasterizer/forward.cu:367-513).  One CTA per
-// 16x16 tile, one thread per pixel.  The tile's depth-ordered Gaussian records are
-// gathered into shared memory by bulk async copies (one 48 B `cp.async.bulk` per entry,
-// completing on an mbarrier), double-buffered so batch k+1 lands while batch k is blended.
-// A warp leaves the inner loop as soon as all of its 32 pixels are saturated; the CTA
-// stops fetching when all 256 are (block vote at batch granularity, as the reference).
+// 16x16 tile, one thread per pixel, warps laid out as 8x4-pixel sub-rectangles.  The tile's
+// depth-ordered Gaussian records are gathered into shared memory by bulk async copies (one
+// 48 B `cp.async.bulk` per entry, completing on an mbarrier), double-buffered so batch k+1
+// lands while batch k is blended.  Each landed batch is culled per sub-rectangle
+// (render_common.cuh) and every warp walks only its own compacted entry list.  A warp leaves
+// the inner loop as soon as all of its 32 pixels are saturated; the CTA stops fetching when
+// all 256 are (block vote at batch granularity, as the reference).
 //
 // The per-pixel arithmetic keeps the reference's expression order: the skip tests
 // (power > 0, alpha < 1/255, T*(1-alpha) < 1e-4) are discontinuities, so a 1-ulp
 // difference in alpha would change n_contrib and move the image by up to 4e-3.
 #include "common.cuh"
 #include "async_copy.cuh"
+#include "render_common.cuh"
 
 namespace gsr {
 
@@ -28,15 +31,18 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   float* __restrict__ out_color, float* __restrict__ out_invdepth) {
     __shared__ __align__(128) float4 s_rec[RF_STAGES][RF_BATCH * 3];
     __shared__ __align__(8) uint64_t s_bar[RF_STAGES];
+    __shared__ uint8_t s_mask[RF_STAGES][RF_BATCH];
+    __shared__ __align__(4) uint8_t s_list[TILE_PIX / 32][RF_BATCH];
     __shared__ uint32_t s_max;
 
-    const uint32_t tx = threadIdx.x, ty = threadIdx.y;
-    const uint32_t rank = ty * TILE_X + tx;
+    const uint32_t rank = threadIdx.x;
+    const uint32_t lane = rank & 31u, warp = rank >> 5;
     const uint32_t horizontal_blocks = (W + TILE_X - 1) / TILE_X;
     const uint32_t tile = blockIdx.y * horizontal_blocks + blockIdx.x;
-    const uint2 pix = {blockIdx.x * TILE_X + tx, blockIdx.y * TILE_Y + ty};
+    const uint2 pix = {blockIdx.x * TILE_X + sub_px(rank), blockIdx.y * TILE_Y + sub_py(rank)};
     const uint32_t pix_id = W * pix.y + pix.x;
     const float2 pixf = {(float)pix.x, (float)pix.y};
+    const float tx0 = (float)(blockIdx.x * TILE_X), ty0 = (float)(blockIdx.y * TILE_Y);
     const bool inside = pix.x < (uint32_t)W && pix.y < (uint32_t)H;
     bool done = !inside;
 
@@ -72,17 +78,32 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
 
     if (rounds > 0) issue(0);
     for (int k = 0; k < rounds; k++) {
-        mbar_wait(smem_u32(&s_bar[k & 1]), (uint32_t)((k >> 1) & 1));   // batch k has landed
+        const int stage = k & 1;
+        const int cnt = min(RF_BATCH, n - k * RF_BATCH);
+        const float4* sr = s_rec[stage];
+        mbar_wait(smem_u32(&s_bar[stage]), (uint32_t)((k >> 1) & 1));   // batch k has landed
+        if ((int)rank < cnt) s_mask[stage][rank] = (uint8_t)cull_mask(sr[rank * 3], sr[rank * 3 + 1], tx0, ty0);
         // all threads are past batch k-1 here, so its stage may be refilled; nothing is
         // in flight when the CTA leaves through the break
         const int num_done = __syncthreads_count(done);
         if (num_done == TILE_PIX) break;
         if (k + 1 < rounds) issue(k + 1);
 
-        const float4* sr = s_rec[k & 1];
-        const int cnt = min(RF_BATCH, n - k * RF_BATCH);
+        // this warp's entries, in list order
+        int cntw = 0;
+        for (int i = 0; i * 32 < cnt; i++) {
+            const int slot = i * 32 + (int)lane;
+            const bool hit = slot < cnt && ((s_mask[stage][slot] >> warp) & 1u);
+            const uint32_t b = __ballot_sync(0xffffffffu, hit);
+            if (hit) s_list[warp][cntw + __popc(b & ((1u << lane) - 1u))] = (uint8_t)slot;
+            cntw += __popc(b);
+        }
+        __syncwarp();
+
+        const uint8_t* sl = s_list[warp];
         const uint32_t base = (uint32_t)k * RF_BATCH;
-        for (int j = 0; !done && j < cnt; j++) {
+        for (int jj = 0; !done && jj < cntw; jj++) {
+            const int j = sl[jj];
             const float4 q0 = sr[j * 3 + 0];      // x, y, conic.x, conic.y
             const float4 q1 = sr[j * 3 + 1];      // conic.z, opacity, r, g
             const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
@@ -103,6 +124,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
             T = test_T;
             last_contributor = base + j + 1;
         }
+        __syncwarp();                              // s_list is rebuilt next round
     }
 
     if (inside) {
@@ -118,7 +140,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     uint32_t m = last_contributor;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
-    if ((rank & 31) == 0 && m > 0) atomicMax(&s_max, m);
+    if (lane == 0 && m > 0) atomicMax(&s_max, m);
     __syncthreads();
     if (rank == 0) tile_max_contrib[tile] = s_max;
 }
@@ -180,7 +202,7 @@ int launch_render_forward(const GsrParams& p, GeomState g, ImgState im, BinState
                           float* out_color, float* out_invdepth, cudaStream_t st) {
     StageTimer tm(GSR_STAGE_RENDER_FWD, st);
     dim3 grid((p.W + TILE_X - 1) / TILE_X, (p.H + TILE_Y - 1) / TILE_Y, 1);
-    dim3 block(TILE_X, TILE_Y, 1);
+    dim3 block(TILE_PIX, 1, 1);
     GSR_LAUNCH(render_fwd_kernel, grid, block, 0, st, im.ranges, b.point_list, p.W, p.H, g.rec, p.background,
                                               im.final_T, im.n_contrib, im.tile_max_contrib,
                                               out_color, out_invdepth);
