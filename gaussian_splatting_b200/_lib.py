@@ -7,7 +7,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libgsrast.so")
+# GSR_LIB: alternative build of the same library (A/B measurements of kernel variants)
+LIB_PATH = os.environ.get("GSR_LIB") or os.path.join(_HERE, "libgsrast.so")
 
 GSR_OK = 0
 GSR_ERR_INVALID_ARG = -1

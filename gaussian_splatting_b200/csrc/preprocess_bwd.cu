@@ -12,13 +12,21 @@
 // dL/dt.x, dL/dt.y (x_grad_mul / y_grad_mul).
 #include "common.cuh"
 #include "gs_math.cuh"
+#include "async_copy.cuh"
 
 namespace gsr {
 
 constexpr int PB_THREADS = 128;
+#ifndef PB_MIN_BLOCKS
+#define PB_MIN_BLOCKS 5
+#endif
 constexpr int PB_WARPS = PB_THREADS / 32;
 constexpr int PB_ROW = 48;
-constexpr int PB_ROW_PAD = PB_ROW + 1;
+// Shared-memory rows per Gaussian.  Bulk path (3*M % 4 == 0, 16 B aligned pointers): a warp's 32 SH
+// rows are contiguous in global memory, so they arrive with ONE cp.async.bulk (TMA engine, no
+// register staging) issued before the covariance math and leave with ONE bulk store; rows are dense
+// (stride 3*M floats, LDS.128 / STS.128 per lane).  Scalar path: 49-float padded rows.
+constexpr int PB_STRIDE_SCALAR = PB_ROW + 1;
 
 __device__ __forceinline__ float sq(float x) { return x * x; }
 
@@ -124,6 +132,24 @@ __device__ __forceinline__ float3 sh_backward(float* row, int rowlen, int deg, f
     return dnormvdv(dir_orig, dL_ddir);
 }
 
+// Vector path: the row is pulled into registers with LDS.128, the gradients go back with STS.128.
+__device__ __forceinline__ float3 sh_backward_vec(float* row, int rowlen, int deg, float3 dir_orig,
+                                                  const float dL_dRGB[3]) {
+    float sh[PB_ROW];
+    float4* row4 = reinterpret_cast<float4*>(row);
+#pragma unroll
+    for (int m = 0; m < PB_ROW / 4; m++) {
+        const float4 v = row4[m];
+        sh[4 * m] = v.x; sh[4 * m + 1] = v.y; sh[4 * m + 2] = v.z; sh[4 * m + 3] = v.w;
+    }
+    const float3 r = sh_backward(sh, rowlen, deg, dir_orig, dL_dRGB);
+    const int n4 = rowlen >> 2;
+#pragma unroll
+    for (int m = 0; m < PB_ROW / 4; m++)
+        if (m < n4) row4[m] = make_float4(sh[4 * m], sh[4 * m + 1], sh[4 * m + 2], sh[4 * m + 3]);
+    return r;
+}
+
 // cov3D backward (backward.cu:296-365) with GLM indexing m[c][r].
 __device__ __forceinline__ void cov3D_backward(float3 scale, float mod, float4 rot, const float* dL_dcov3D,
                                                float3* dL_dscale, float4* dL_drot) {
@@ -160,12 +186,18 @@ __device__ __forceinline__ void cov3D_backward(float3 scale, float mod, float4 r
     dL_drot->w = 2 * r * (D.m[0][1] - D.m[1][0]) + 2 * x * (D.m[2][0] + D.m[0][2]) + 2 * y * (D.m[1][2] + D.m[2][1]) - 4 * z * (D.m[1][1] + D.m[0][0]);
 }
 
-__global__ void __launch_bounds__(PB_THREADS)
+template <bool VEC>
+__global__ void __launch_bounds__(PB_THREADS, PB_MIN_BLOCKS)
 preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord* __restrict__ rec,
                       const int32_t* __restrict__ radii, const float* __restrict__ acc,
                       bool have_invdepth, GsrBackwardIO io) {
-    __shared__ float sh_smem[PB_WARPS][32 * PB_ROW_PAD];
+    __shared__ __align__(128) float sh_smem[PB_WARPS][32 * PB_STRIDE_SCALAR];
+    __shared__ __align__(8) uint64_t s_bar[PB_WARPS];
     __shared__ float s_view[16], s_proj[16], s_cam[3];
+    if (VEC && (threadIdx.x & 31) == 0) {
+        mbar_init(smem_u32(&s_bar[threadIdx.x >> 5]), 1);
+        mbar_fence_init();
+    }
     if (threadIdx.x < 16) {
         s_view[threadIdx.x] = p.viewmatrix[threadIdx.x];
         s_proj[threadIdx.x] = p.projmatrix[threadIdx.x];
@@ -178,6 +210,14 @@ preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord*
     const int warp_base = blockIdx.x * PB_THREADS + warp * 32;
     const bool in_range = idx < p.P;
     const bool visible = in_range && radii[idx] > 0;
+    const unsigned vis_mask = __ballot_sync(0xffffffffu, visible);
+    const int sh_row = 3 * p.M;                                   // floats per Gaussian
+    const uint32_t sh_bytes = (uint32_t)(max(0, min(32, p.P - warp_base)) * sh_row) * 4u;
+    if (VEC && vis_mask != 0 && lane == 0) {                      // prefetch this warp's SH rows
+        const uint32_t bar = smem_u32(&s_bar[warp]);
+        mbar_arrive_expect_tx(bar, sh_bytes);
+        bulk_g2s(smem_u32(sh_smem[warp]), p.shs + (size_t)warp_base * sh_row, sh_bytes, bar);
+    }
 
     float3 dL_dmean = {0.f, 0.f, 0.f};
     float2 dL_dmean2D = {0.f, 0.f};
@@ -303,37 +343,53 @@ preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord*
         if (p.scales != nullptr) cov3D_backward(sc, p.scale_modifier, rot, dL_dcov, &dL_dscale, &dL_drot);
     }
 
-    // ---- SH backward through the shared-memory transpose; dL_dsh rows written coalesced ----
+    // ---- SH backward; dL_dsh rows leave coalesced (bulk store or transposed scalar stores) ----
     if (p.shs != nullptr && io.dL_dsh != nullptr) {
-        const unsigned vis_mask = __ballot_sync(0xffffffffu, visible);
         const int L = 3 * (p.D + 1) * (p.D + 1);
-        const int row = 3 * p.M;
+        const int row = sh_row;
         float* ws = sh_smem[warp];
-        if (vis_mask != 0) {
-            const float* src = p.shs + (size_t)warp_base * row;
-            for (int i = lane; i < 32 * L; i += 32) {
-                int g = i / L, k = i - g * L;
-                if ((vis_mask >> g) & 1u) ws[g * PB_ROW_PAD + k] = __ldg(src + (size_t)g * row + k);
-            }
-        }
-        __syncwarp();
-        float* myrow = ws + lane * PB_ROW_PAD;
-        if (visible) {
-            float dL_dRGB[3];
+        float dL_dRGB[3];
 #pragma unroll
-            for (int c = 0; c < 3; c++) dL_dRGB[c] = ((clamped_bits >> c) & 1) ? 0.f : dL_dcolor[c];
-            float3 dir_orig = {mean.x - s_cam[0], mean.y - s_cam[1], mean.z - s_cam[2]};
-            float3 dm = sh_backward(myrow, row, p.D, dir_orig, dL_dRGB);
-            dL_dmean.x += dm.x; dL_dmean.y += dm.y; dL_dmean.z += dm.z;
-        } else {
-            for (int k = 0; k < row; k++) myrow[k] = 0.f;
-        }
-        __syncwarp();
-        const int nvalid = min(32, p.P - warp_base);
+        for (int c = 0; c < 3; c++) dL_dRGB[c] = ((clamped_bits >> c) & 1) ? 0.f : dL_dcolor[c];
+        const float3 dir_orig = {mean.x - s_cam[0], mean.y - s_cam[1], mean.z - s_cam[2]};
         float* dst = io.dL_dsh + (size_t)warp_base * row;
-        for (int i = lane; i < nvalid * row; i += 32) {
-            int g = i / row, k = i - g * row;
-            dst[i] = ws[g * PB_ROW_PAD + k];
+        if (VEC) {
+            if (vis_mask != 0) mbar_wait(smem_u32(&s_bar[warp]), 0);
+            float* myrow = ws + lane * row;
+            if (visible) {
+                const float3 dm = sh_backward_vec(myrow, row, p.D, dir_orig, dL_dRGB);
+                dL_dmean.x += dm.x; dL_dmean.y += dm.y; dL_dmean.z += dm.z;
+            } else {
+                for (int k = 0; k < (row >> 2); k++) reinterpret_cast<float4*>(myrow)[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0 && sh_bytes != 0) {
+                bulk_s2g(dst, smem_u32(ws), sh_bytes);
+                bulk_commit();
+            }
+        } else {
+            if (vis_mask != 0) {
+                const float* src = p.shs + (size_t)warp_base * row;
+                for (int i = lane; i < 32 * L; i += 32) {
+                    int g = i / L, k = i - g * L;
+                    if ((vis_mask >> g) & 1u) ws[g * PB_STRIDE_SCALAR + k] = __ldg(src + (size_t)g * row + k);
+                }
+            }
+            __syncwarp();
+            float* myrow = ws + lane * PB_STRIDE_SCALAR;
+            if (visible) {
+                const float3 dm = sh_backward(myrow, row, p.D, dir_orig, dL_dRGB);
+                dL_dmean.x += dm.x; dL_dmean.y += dm.y; dL_dmean.z += dm.z;
+            } else {
+                for (int k = 0; k < row; k++) myrow[k] = 0.f;
+            }
+            __syncwarp();
+            const int nvalid = min(32, p.P - warp_base);
+            for (int i = lane; i < nvalid * row; i += 32) {
+                int g = i / row, k = i - g * row;
+                dst[i] = ws[g * PB_STRIDE_SCALAR + k];
+            }
         }
     }
 
@@ -356,6 +412,7 @@ preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord*
         io.dL_dscales[3 * idx] = dL_dscale.x; io.dL_dscales[3 * idx + 1] = dL_dscale.y; io.dL_dscales[3 * idx + 2] = dL_dscale.z;
     }
     if (io.dL_drotations) reinterpret_cast<float4*>(io.dL_drotations)[idx] = dL_drot;
+    if (VEC && lane == 0) bulk_wait_read0();      // shared memory must outlive the bulk store's reads
 }
 
 int launch_preprocess_backward(const GsrParams& p, GeomState g, Scratch s, const int32_t* radii,
@@ -364,8 +421,15 @@ int launch_preprocess_backward(const GsrParams& p, GeomState g, Scratch s, const
     const float focal_x = p.W / (2.0f * p.tanfovx);
     const int blocks = (p.P + PB_THREADS - 1) / PB_THREADS;
     StageTimer tm(GSR_STAGE_PREPROCESS_BWD, st);
-    GSR_LAUNCH(preprocess_bwd_kernel, blocks, PB_THREADS, 0, st, p, focal_x, focal_y, g.rec, radii, s.acc,
-                                                         have_invdepth, io);
+    // vector path: SH rows are whole float4s (M in {4, 8, 12, 16}) and 16 B aligned
+    const bool vec = p.shs != nullptr && io.dL_dsh != nullptr && (p.M & 3) == 0 &&
+                     (reinterpret_cast<uintptr_t>(p.shs) & 15) == 0 && (reinterpret_cast<uintptr_t>(io.dL_dsh) & 15) == 0;
+    if (vec)
+        GSR_LAUNCH(preprocess_bwd_kernel<true>, blocks, PB_THREADS, 0, st, p, focal_x, focal_y, g.rec, radii, s.acc,
+                                                                   have_invdepth, io);
+    else
+        GSR_LAUNCH(preprocess_bwd_kernel<false>, blocks, PB_THREADS, 0, st, p, focal_x, focal_y, g.rec, radii, s.acc,
+                                                                    have_invdepth, io);
     return check_stage("preprocess backward", p.debug, st);
 }
 
