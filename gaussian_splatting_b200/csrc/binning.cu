@@ -170,6 +170,214 @@ radix_scatter_kernel(const uint64_t* __restrict__ in, uint32_t n, int shift,
     }
 }
 
+// ---------------------------------------------------------------- onesweep radix sort
+// One read + one write of the items per digit pass: digit histograms of ALL passes come from a
+// single read of the input, and each pass is one kernel whose CTAs (4096-item tiles, taken in
+// ticket order) rank their items, publish their per-digit counts and obtain the count of all
+// earlier tiles by decoupled look-back over `status` (aggregate / inclusive-prefix flags in the
+// two top bits of each word) instead of a separate histogram + scan pass.  Stable.
+constexpr int OS_THREADS = 512;
+constexpr int OS_WARPS = OS_THREADS / 32;
+constexpr int OS_ITEMS = 8;
+constexpr int OS_TILE = OS_THREADS * OS_ITEMS;          // 4096 == SORT_CHUNK
+static_assert(OS_TILE == SORT_CHUNK, "scratch sizing assumes 4096-item tiles");
+constexpr uint32_t OS_FLAG_AGG = 1u << 30, OS_FLAG_PREFIX = 1u << 31, OS_COUNT_MASK = (1u << 30) - 1u;
+constexpr uint32_t OS_MAX_N = 1u << 30;                 // counts must fit in 30 bits
+
+// Histograms of `passes` consecutive 8-bit digits starting at bit `shift`, one read of the input.
+template <int PASSES>
+__global__ void __launch_bounds__(256)
+radix_hist_multi_kernel(const uint64_t* __restrict__ in, uint32_t n, int shift, uint32_t* __restrict__ ghist) {
+    __shared__ uint32_t h[PASSES][256];
+#pragma unroll
+    for (int p = 0; p < PASSES; p++) h[p][threadIdx.x] = 0;
+    __syncthreads();
+    const uint32_t stride = gridDim.x * blockDim.x * 2;
+    for (uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) * 2; i < n; i += stride) {
+        uint64_t a, b = 0;
+        const bool two = i + 1 < n;
+        if (two) {
+            const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(in + i);
+            a = v.x; b = v.y;
+        } else {
+            a = in[i];
+        }
+#pragma unroll
+        for (int p = 0; p < PASSES; p++) {
+            atomicAdd(&h[p][(uint32_t)(a >> (shift + 8 * p)) & 255u], 1u);
+            if (two) atomicAdd(&h[p][(uint32_t)(b >> (shift + 8 * p)) & 255u], 1u);
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int p = 0; p < PASSES; p++) {
+        const uint32_t c = h[p][threadIdx.x];
+        if (c) atomicAdd(&ghist[p * 256 + threadIdx.x], c);
+    }
+}
+
+// Exclusive scan of each pass's 256 digit counts (block p = pass p).
+__global__ void __launch_bounds__(256)
+radix_bases_kernel(const uint32_t* __restrict__ ghist, uint32_t* __restrict__ gbase) {
+    __shared__ uint32_t s_w[8];
+    const uint32_t c = ghist[blockIdx.x * 256 + threadIdx.x];
+    gbase[blockIdx.x * 256 + threadIdx.x] = block_excl_scan_256(c, s_w, nullptr);
+}
+
+template <bool SPLIT>
+__global__ void __launch_bounds__(OS_THREADS, 2)
+onesweep_kernel(const uint64_t* __restrict__ in, uint32_t n, int shift, const uint32_t* __restrict__ gbase,
+                uint32_t* status, uint32_t* ticket,
+                uint64_t* __restrict__ out, uint32_t* __restrict__ out_lo, uint32_t* __restrict__ out_hi) {
+    __shared__ uint16_t wh[OS_WARPS][256];           // per-warp digit counts (<= 256), then prefixes (<= 4096)
+    __shared__ uint64_t stage[OS_TILE];
+    __shared__ uint32_t s_gbase[256];
+    __shared__ uint32_t s_dstart[256];
+    __shared__ uint32_t s_w[8];
+    __shared__ uint32_t s_tile;
+
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    if (t == 0) s_tile = atomicAdd(ticket, 1u);     // tiles start in ticket order: look-back never waits on an unscheduled CTA
+#pragma unroll
+    for (int w = 0; w < OS_WARPS / 2; w++) wh[w * 2 + (t >> 8)][t & 255] = 0;
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const uint32_t block_base = tile * OS_TILE;
+    const uint32_t n_block = min((uint32_t)OS_TILE, n - block_base);
+
+    uint64_t items[OS_ITEMS];
+    uint32_t ranks[OS_ITEMS];
+#pragma unroll
+    for (int i = 0; i < OS_ITEMS; i++) {
+        const uint32_t idx = warp * (32 * OS_ITEMS) + i * 32 + lane;
+        items[i] = idx < n_block ? in[block_base + idx] : ~0ull;
+    }
+#pragma unroll
+    for (int i = 0; i < OS_ITEMS; i++) {
+        const uint32_t idx = warp * (32 * OS_ITEMS) + i * 32 + lane;
+        const bool valid = idx < n_block;
+        const uint32_t d = valid ? ((uint32_t)(items[i] >> shift) & 255u) : 256u;
+        const uint32_t mask = __match_any_sync(0xffffffffu, d);
+        const int leader = __ffs(mask) - 1;
+        const uint32_t r = __popc(mask & ((1u << lane) - 1u));
+        uint32_t old = 0;
+        if (lane == leader && valid) {
+            old = wh[warp][d];
+            wh[warp][d] = (uint16_t)(old + __popc(mask));
+        }
+        old = __shfl_sync(0xffffffffu, old, leader);
+        ranks[i] = old + r;
+        __syncwarp();
+    }
+    __syncthreads();
+
+    // thread d < 256 owns digit d: exclusive prefix over warps, tile count, publish, look back
+    uint32_t cnt = 0;
+    volatile uint32_t* vstatus = status;
+    if (t < 256) {
+#pragma unroll
+        for (int w = 0; w < OS_WARPS; w++) {
+            const uint32_t c = wh[w][t];
+            wh[w][t] = (uint16_t)cnt;
+            cnt += c;
+        }
+        vstatus[(size_t)tile * 256 + t] = cnt | (tile == 0 ? OS_FLAG_PREFIX : OS_FLAG_AGG);
+    }
+    // start of each digit's run inside the tile (all threads take part in the barriers)
+    uint32_t dstart = 0;
+    {
+        const int w8 = t >> 5;
+        uint32_t inc = warp_incl_scan(cnt, lane);
+        if (t < 256 && lane == 31) s_w[w8] = inc;
+        __syncthreads();
+        if (t < 256) {
+            uint32_t wp = 0;
+#pragma unroll
+            for (int w = 0; w < 8; w++) if (w < w8) wp += s_w[w];
+            dstart = wp + inc - cnt;
+        }
+    }
+    if (t < 256) {
+        uint32_t excl = 0;
+        if (tile > 0) {
+            int look = (int)tile - 1;
+            uint32_t spins = 0;
+            while (true) {
+                const uint32_t v = vstatus[(size_t)look * 256 + t];
+                if ((v >> 30) == 0) {
+                    if (++spins > (1u << 24)) __trap();       // a lost predecessor must not hang the GPU
+                    continue;
+                }
+                excl += v & OS_COUNT_MASK;
+                if (v & OS_FLAG_PREFIX) break;
+                --look;
+            }
+            vstatus[(size_t)tile * 256 + t] = ((excl + cnt) & OS_COUNT_MASK) | OS_FLAG_PREFIX;
+        }
+        s_dstart[t] = dstart;
+        s_gbase[t] = gbase[t] + excl - dstart;
+    }
+    __syncthreads();
+
+#pragma unroll
+    for (int i = 0; i < OS_ITEMS; i++) {
+        const uint32_t idx = warp * (32 * OS_ITEMS) + i * 32 + lane;
+        if (idx < n_block) {
+            const uint32_t d = (uint32_t)(items[i] >> shift) & 255u;
+            stage[s_dstart[d] + wh[warp][d] + ranks[i]] = items[i];
+        }
+    }
+    __syncthreads();
+
+#pragma unroll
+    for (int i = 0; i < OS_ITEMS; i++) {
+        const uint32_t idx = i * OS_THREADS + t;
+        if (idx < n_block) {
+            const uint64_t it = stage[idx];
+            const uint32_t d = (uint32_t)(it >> shift) & 255u;
+            const uint32_t pos = s_gbase[d] + idx;
+            if (SPLIT) {
+                out_lo[pos] = (uint32_t)it;
+                out_hi[pos] = (uint32_t)(it >> 32);
+            } else {
+                out[pos] = it;
+            }
+        }
+    }
+}
+
+// Stable LSD sort of n u64 items on `passes` 8-bit digits from bit `shift` (a -> b -> a ...).
+// split_last: the final pass writes low words to out_lo and high words to out_hi instead.
+// Returns through *result the buffer holding the sorted items (unused with split_last).
+static int radix_sort_onesweep(uint64_t* a, uint64_t* b, uint32_t n, int shift, int passes, Scratch s,
+                               bool split_last, uint32_t* out_lo, uint32_t* out_hi, uint64_t** result,
+                               cudaStream_t st) {
+    const uint32_t nb = div_up(n, OS_TILE);
+    uint32_t* ctl = s.sort_ctl;
+    GSR_CUDA_TRY(cudaMemsetAsync(ctl, 0, (SORT_CTL_STATUS + (size_t)passes * 256 * nb) * sizeof(uint32_t), st));
+    const uint32_t hist_blocks = min(div_up(n, 512u), 148u * 8u);
+    switch (passes) {
+        case 1: GSR_LAUNCH(radix_hist_multi_kernel<1>, hist_blocks, 256, 0, st, a, n, shift, ctl + SORT_CTL_HIST); break;
+        case 2: GSR_LAUNCH(radix_hist_multi_kernel<2>, hist_blocks, 256, 0, st, a, n, shift, ctl + SORT_CTL_HIST); break;
+        case 3: GSR_LAUNCH(radix_hist_multi_kernel<3>, hist_blocks, 256, 0, st, a, n, shift, ctl + SORT_CTL_HIST); break;
+        default: GSR_LAUNCH(radix_hist_multi_kernel<4>, hist_blocks, 256, 0, st, a, n, shift, ctl + SORT_CTL_HIST); break;
+    }
+    GSR_LAUNCH(radix_bases_kernel, passes, 256, 0, st, ctl + SORT_CTL_HIST, ctl + SORT_CTL_BASE);
+    for (int pass = 0; pass < passes; pass++) {
+        uint32_t* status = ctl + SORT_CTL_STATUS + (size_t)pass * 256 * nb;
+        const bool split = split_last && pass == passes - 1;
+        if (split)
+            GSR_LAUNCH(onesweep_kernel<true>, nb, OS_THREADS, 0, st, a, n, shift + 8 * pass, ctl + SORT_CTL_BASE + pass * 256,
+                                                            status, ctl + SORT_CTL_TICKET + pass, nullptr, out_lo, out_hi);
+        else
+            GSR_LAUNCH(onesweep_kernel<false>, nb, OS_THREADS, 0, st, a, n, shift + 8 * pass, ctl + SORT_CTL_BASE + pass * 256,
+                                                             status, ctl + SORT_CTL_TICKET + pass, b, nullptr, nullptr);
+        uint64_t* tmp = a; a = b; b = tmp;
+    }
+    if (result) *result = a;
+    return GSR_OK;
+}
+
 // One LSD pass src -> dst on digit `shift`. split => final pass with split outputs.
 static int radix_pass(const uint64_t* src, uint64_t* dst, uint32_t n, int shift, Scratch s,
                       bool split, uint32_t* out_lo, uint32_t* out_hi, cudaStream_t st) {
@@ -272,22 +480,34 @@ emit_instances_kernel(const uint64_t* __restrict__ sorted, const uint2* __restri
             inst[off++] = ((uint64_t)(y * grid_x + x) << 32) | g;
 }
 
-// identifyTileRanges (rasterizer_impl.cu:132-164) on the sorted tile ids.
+// identifyTileRanges (rasterizer_impl.cu:132-164) on the sorted tile ids; 4 instances per thread.
 __global__ void __launch_bounds__(256)
 tile_ranges_kernel(const uint32_t* __restrict__ tile_ids, uint32_t L, uint2* __restrict__ ranges) {
-    uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= L) return;
-    uint32_t cur = tile_ids[idx];
-    if (idx == 0)
-        ranges[cur].x = 0;
-    else {
-        uint32_t prev = tile_ids[idx - 1];
-        if (cur != prev) {
+    const uint32_t i0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (i0 >= L) return;
+    uint32_t v[4];
+    if (i0 + 3 < L) {
+        const uint4 q = *reinterpret_cast<const uint4*>(tile_ids + i0);
+        v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
+    } else {
+#pragma unroll
+        for (int k = 0; k < 4; k++) v[k] = i0 + k < L ? tile_ids[i0 + k] : 0u;
+    }
+    uint32_t prev = i0 > 0 ? tile_ids[i0 - 1] : 0u;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const uint32_t idx = i0 + k;
+        if (idx >= L) break;
+        const uint32_t cur = v[k];
+        if (idx == 0)
+            ranges[cur].x = 0;
+        else if (cur != prev) {
             ranges[prev].y = idx;
             ranges[cur].x = idx;
         }
+        if (idx == L - 1) ranges[cur].y = L;
+        prev = cur;
     }
-    if (idx == L - 1) ranges[cur].y = L;
 }
 
 // Test hook: rebuild the reference's sorted keys  tile<<32 | depth bits.
@@ -310,9 +530,14 @@ int launch_depth_order_and_scan(const GsrParams& p, GeomState g, Scratch s, int3
     uint64_t* b = s.depth_b;
     {
         StageTimer tm(GSR_STAGE_DEPTH_SORT, st);
-        for (int pass = 0; pass < 4; pass++) {
-            radix_pass(a, b, P, 32 + 8 * pass, s, false, nullptr, nullptr, st);
-            uint64_t* tmp = a; a = b; b = tmp;
+        if (P < OS_MAX_N) {
+            int rc = radix_sort_onesweep(a, b, P, 32, 4, s, false, nullptr, nullptr, nullptr, st);
+            if (rc) return rc;
+        } else {
+            for (int pass = 0; pass < 4; pass++) {
+                radix_pass(a, b, P, 32 + 8 * pass, s, false, nullptr, nullptr, st);
+                uint64_t* tmp = a; a = b; b = tmp;
+            }
         }
     }
     int rc = check_stage("depth sort", p.debug, st);
@@ -355,6 +580,10 @@ int launch_binning(const GsrParams& p, GeomState g, ImgState im, BinState b, Scr
     uint64_t* c = s.inst_b;
     {
         StageTimer tm(GSR_STAGE_TILE_SORT, st);
+        if (n < OS_MAX_N) {
+            rc = radix_sort_onesweep(a, c, n, 32, passes, s, true, b.point_list, s.tile_ids, nullptr, st);
+            if (rc) return rc;
+        } else
         for (int pass = 0; pass < passes; pass++) {
             const bool last = pass == passes - 1;
             radix_pass(a, c, n, 32 + 8 * pass, s, last, b.point_list, s.tile_ids, st);
@@ -365,7 +594,7 @@ int launch_binning(const GsrParams& p, GeomState g, ImgState im, BinState b, Scr
     if (rc) return rc;
     {
         StageTimer tm(GSR_STAGE_TILE_RANGES, st);
-        GSR_LAUNCH(tile_ranges_kernel, div_up(n, 256), 256, 0, st, s.tile_ids, n, im.ranges);
+        GSR_LAUNCH(tile_ranges_kernel, div_up(n, 1024), 256, 0, st, s.tile_ids, n, im.ranges);
     }
     return check_stage("tile ranges", p.debug, st);
 }

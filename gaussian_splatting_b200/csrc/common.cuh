@@ -106,6 +106,15 @@ constexpr int SCAN_THREADS = 256;
 constexpr int SCAN_ITEMS = 8;
 constexpr int SCAN_CHUNK = SCAN_THREADS * SCAN_ITEMS;   // 2048 items per block
 
+// Control block of one radix sort (up to 4 digit passes):
+//   [0, 1024)            digit histograms of all passes (256 each)
+//   [1024, 2048)         exclusive digit bases of all passes
+//   [2048, 2048+64)      tile tickets, one per pass (padded)
+//   [2112, ...)          look-back status words, pass-major: pass * 256 * nb + tile * 256 + digit
+constexpr int SORT_MAX_PASSES = 4;
+constexpr size_t SORT_CTL_HIST = 0, SORT_CTL_BASE = 1024, SORT_CTL_TICKET = 2048, SORT_CTL_STATUS = 2112;
+inline size_t sort_ctl_words(size_t nb) { return SORT_CTL_STATUS + (size_t)SORT_MAX_PASSES * 256 * nb; }
+
 struct Scratch {            // only live inside one forward or backward call
     // forward
     uint2*    rects;        // P   packed rect {min.x | min.y<<16, max.x | max.y<<16}
@@ -113,7 +122,8 @@ struct Scratch {            // only live inside one forward or backward call
     uint64_t* depth_b;      // P   (pong)
     uint32_t* offsets;      // P   inclusive scan of tiles_touched in depth order
     uint32_t* scan_blocks;  // ceil(P / SCAN_CHUNK) + 1
-    uint32_t* hist;         // 256 * max(blocks(P), blocks(R))
+    uint32_t* sort_ctl;     // onesweep control words, see SORT_CTL_* (zeroed per sort)
+    uint32_t* hist;         // 256 * max(blocks(P), blocks(R))   (legacy 3-kernel pass, n >= 2^30)
     uint32_t* digit_tot;    // 256
     uint64_t* inst_a;       // R   tile<<32 | id (ping)
     uint64_t* inst_b;       // R   (pong)
@@ -132,6 +142,7 @@ struct Scratch {            // only live inside one forward or backward call
         s.depth_b = c.take<uint64_t>(Pn);
         s.offsets = c.take<uint32_t>(Pn);
         s.scan_blocks = c.take<uint32_t>(Pn / SCAN_CHUNK + 2);
+        s.sort_ctl = c.take<uint32_t>(sort_ctl_words(nb));
         s.hist = c.take<uint32_t>(256 * nb);
         s.digit_tot = c.take<uint32_t>(256);
         s.inst_a = c.take<uint64_t>(Rn);
