@@ -252,22 +252,34 @@ onesweep_kernel(const uint64_t* __restrict__ in, uint32_t n, int shift, const ui
         const uint32_t idx = warp * (32 * OS_ITEMS) + i * 32 + lane;
         items[i] = idx < n_block ? in[block_base + idx] : ~0ull;
     }
+    // Lanes holding the same digit, by 8 ballots per item.  (MATCH.ANY costs one round per distinct
+    // value in the warp -- ~30 with random 8-bit digits -- and was the bottleneck of this kernel.)
+    uint32_t masks[OS_ITEMS];
+#pragma unroll
+    for (int i = 0; i < OS_ITEMS; i++) {
+        const uint32_t idx = warp * (32 * OS_ITEMS) + i * 32 + lane;
+        const uint32_t d = (uint32_t)(items[i] >> shift) & 255u;
+        uint32_t m = __ballot_sync(0xffffffffu, idx < n_block);
+#pragma unroll
+        for (int b = 0; b < 8; b++) {
+            const bool bit = (d >> b) & 1u;
+            const uint32_t v = __ballot_sync(0xffffffffu, bit);
+            m &= bit ? v : ~v;
+        }
+        masks[i] = m;
+    }
 #pragma unroll
     for (int i = 0; i < OS_ITEMS; i++) {
         const uint32_t idx = warp * (32 * OS_ITEMS) + i * 32 + lane;
         const bool valid = idx < n_block;
-        const uint32_t d = valid ? ((uint32_t)(items[i] >> shift) & 255u) : 256u;
-        const uint32_t mask = __match_any_sync(0xffffffffu, d);
-        const int leader = __ffs(mask) - 1;
-        const uint32_t r = __popc(mask & ((1u << lane) - 1u));
-        uint32_t old = 0;
-        if (lane == leader && valid) {
-            old = wh[warp][d];
-            wh[warp][d] = (uint16_t)(old + __popc(mask));
-        }
-        old = __shfl_sync(0xffffffffu, old, leader);
-        ranks[i] = old + r;
+        const uint32_t d = (uint32_t)(items[i] >> shift) & 255u;
+        const uint32_t mask = masks[i];
+        const uint32_t lower = mask & ((1u << lane) - 1u);
+        const uint32_t old = valid ? wh[warp][d] : 0u;     // every lane of the group reads the same counter
         __syncwarp();
+        if (valid && lower == 0) wh[warp][d] = (uint16_t)(old + __popc(mask));   // group leader
+        __syncwarp();
+        ranks[i] = old + __popc(lower);
     }
     __syncthreads();
 
