@@ -189,15 +189,25 @@ def make_steps(module, wl, device, flat=None):
     h2d = cam_host.numel() * 4 + tgt_host.numel() * 4
     d2h = 4
 
+    copy_stream = torch.cuda.Stream(device=device)
+    copied = torch.cuda.Event()
+
     def step_e2e():
         clear()
-        cam_dev.copy_(cam_host, non_blocking=True)
-        tgt_dev.copy_(tgt_host, non_blocking=True)
+        main = torch.cuda.current_stream(device)
+        cam_dev.copy_(cam_host, non_blocking=True)          # 140 B: needed before the first kernel
+        # the 33 MB of target image / depth are only needed by the loss: copy them on a side stream
+        # while the forward pass runs
+        copy_stream.wait_stream(main)                        # previous step's loss has consumed tgt_dev
+        with torch.cuda.stream(copy_stream):
+            tgt_dev.copy_(tgt_host, non_blocking=True)
+            copied.record(copy_stream)
         cd = dict(viewmatrix=cam_dev[:16].view(4, 4), projmatrix=cam_dev[16:32].view(4, 4), campos=cam_dev[32:35],
                   bg=bg_dev)
         r = module.GaussianRasterizer(settings_of(module, wl["s"], device, cd))
         color, radii, invd = r(means3D=params["means3D"], means2D=means2D, opacities=params["opacities"],
                                shs=params["shs"], scales=params["scales"], rotations=params["rotations"])
+        main.wait_event(copied)
         tgt = tgt_dev[:3 * H * W].view(3, H, W)
         tgt_d = tgt_dev[3 * H * W:].view(1, H, W)
         loss = (color - tgt).abs().mean() + 0.1 * (invd - tgt_d).abs().mean()
@@ -391,7 +401,7 @@ def run_gpu_arm(args, module, impl, rank, world, local):
         ms_e, _, _ = timed_loop(step_e2e, args.steps, 3, world, device)
         line["e2e"] = {"value": round(world * 1000.0 * args.steps / ms_e, 3), "unit": UNIT,
                        "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                       "what": "camera + target image/depth from pinned host memory, L1 losses in torch, "
+                       "what": "camera + target image/depth from pinned host memory (targets on a copy stream, overlapped with the forward), L1 losses in torch, "
                                "backward, loss scalar read back; Gaussian parameters stay resident (they "
                                "are the model)"}
     if ours:
