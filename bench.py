@@ -53,6 +53,9 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--ref-variant", default="restored", choices=["restored", "asis"])
+    ap.add_argument("--reduce", default="fused", choices=["fused", "nccl"],
+                    help="N > 1: gradient reduction inside the backward kernel over NVLink multicast (fused) "
+                         "or a separate NCCL all-reduce of the packed gradients (nccl)")
     return ap.parse_args()
 
 
@@ -365,9 +368,18 @@ def run_gpu_arm(args, module, impl, rank, world, local):
         dist.init_process_group("nccl", device_id=device)
     wl = build_workload(args, rank, device)
     flat = None
+    reduce_mode = None
     if world > 1:
-        from gaussian_splatting_b200.view_parallel import FlatGradients
-        flat = FlatGradients(list(wl["params"].values()))
+        from gaussian_splatting_b200.view_parallel import FlatGradients, FusedGradientReducer
+        reduce_mode = "nccl all-reduce of the packed gradients"
+        if impl == "ours" and args.reduce == "fused" and FusedGradientReducer.available():
+            try:
+                FusedGradientReducer().install()
+                reduce_mode = "fused: multimem.red into NVLink-multicast buffers inside the backward kernel"
+            except Exception as ex:      # noqa: BLE001
+                reduce_mode += f" (fused unavailable: {ex})"
+        if not reduce_mode.startswith("fused"):
+            flat = FlatGradients(list(wl["params"].values()))
     step, step_fwd, step_e2e, (h2d, d2h) = make_steps(module, wl, device, flat)
     ours = impl == "ours"
     if ours:
@@ -386,6 +398,8 @@ def run_gpu_arm(args, module, impl, rank, world, local):
     ms, t0, t1 = timed_loop(step, args.steps, args.warmup, world, device, on_start)
     clocks = sampler.stop(t0, t1)
     line = base_line(args, wl, world, impl)
+    if reduce_mode:
+        line["config"]["gradient_reduction"] = reduce_mode
     if ours:
         launches = _lib.launch_count() - mark["l0"]
         stage_ms = _lib.profile_collect()

@@ -50,6 +50,7 @@ class GsrBackwardIO(C.Structure):
         ("dL_dout_color", _fp), ("dL_dout_invdepth", _fp),
         ("dL_dmeans3D", _fp), ("dL_dmeans2D", _fp), ("dL_dopacity", _fp), ("dL_dcolors", _fp),
         ("dL_dcov3D", _fp), ("dL_dsh", _fp), ("dL_dscales", _fp), ("dL_drotations", _fp),
+        ("multimem_reduce", C.c_int32), ("reserved1", C.c_int32),
     ]
 
 

@@ -30,6 +30,29 @@ constexpr int PB_STRIDE_SCALAR = PB_ROW + 1;
 
 __device__ __forceinline__ float sq(float x) { return x * x; }
 
+// Output of one gradient value.  MM = false: plain store.  MM = true: `p` is an NVLink multicast
+// address; the value is ADDED to every rank's replica in the switch (multimem.red), zeros are
+// skipped (the replicas start zeroed), so the all-reduce of the view-parallel step happens inside
+// this kernel's stores.
+template <bool MM>
+__device__ __forceinline__ void out1(float* p, float v) {
+    if (MM) {
+        if (v != 0.f) asm volatile("multimem.red.relaxed.sys.global.add.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+    } else {
+        *p = v;
+    }
+}
+template <bool MM>
+__device__ __forceinline__ void out4(float* p, float4 v) {
+    if (MM) {
+        if (v.x != 0.f || v.y != 0.f || v.z != 0.f || v.w != 0.f)
+            asm volatile("multimem.red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};"
+                         ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+    } else {
+        *reinterpret_cast<float4*>(p) = v;
+    }
+}
+
 // auxiliary.h:128-139
 __device__ __forceinline__ float3 dnormvdv(float3 v, float3 dv) {
     float sum2 = v.x * v.x + v.y * v.y + v.z * v.z;
@@ -186,7 +209,7 @@ __device__ __forceinline__ void cov3D_backward(float3 scale, float mod, float4 r
     dL_drot->w = 2 * r * (D.m[0][1] - D.m[1][0]) + 2 * x * (D.m[2][0] + D.m[0][2]) + 2 * y * (D.m[1][2] + D.m[2][1]) - 4 * z * (D.m[1][1] + D.m[0][0]);
 }
 
-template <bool VEC>
+template <bool VEC, bool MM>
 __global__ void __launch_bounds__(PB_THREADS, PB_MIN_BLOCKS)
 preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord* __restrict__ rec,
                       const int32_t* __restrict__ radii, const float* __restrict__ acc,
@@ -362,11 +385,19 @@ preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord*
             } else {
                 for (int k = 0; k < (row >> 2); k++) reinterpret_cast<float4*>(myrow)[k] = make_float4(0.f, 0.f, 0.f, 0.f);
             }
-            fence_proxy_async_smem();
-            __syncwarp();
-            if (lane == 0 && sh_bytes != 0) {
-                bulk_s2g(dst, smem_u32(ws), sh_bytes);
-                bulk_commit();
+            if (MM) {
+                // rows of this warp are contiguous: 16 B multimem reductions, coalesced across lanes
+                __syncwarp();
+                const int n4 = (int)(sh_bytes >> 4);
+                for (int f = lane; f < n4; f += 32)
+                    out4<true>(dst + 4 * f, reinterpret_cast<const float4*>(ws)[f]);
+            } else {
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0 && sh_bytes != 0) {
+                    bulk_s2g(dst, smem_u32(ws), sh_bytes);
+                    bulk_commit();
+                }
             }
         } else {
             if (vis_mask != 0) {
@@ -388,31 +419,34 @@ preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord*
             const int nvalid = min(32, p.P - warp_base);
             for (int i = lane; i < nvalid * row; i += 32) {
                 int g = i / row, k = i - g * row;
-                dst[i] = ws[g * PB_STRIDE_SCALAR + k];
+                out1<MM>(dst + i, ws[g * PB_STRIDE_SCALAR + k]);
             }
         }
     }
 
     if (!in_range) return;
     if (io.dL_dmeans3D) {
-        io.dL_dmeans3D[3 * idx] = dL_dmean.x; io.dL_dmeans3D[3 * idx + 1] = dL_dmean.y; io.dL_dmeans3D[3 * idx + 2] = dL_dmean.z;
+        out1<MM>(io.dL_dmeans3D + 3 * idx, dL_dmean.x); out1<MM>(io.dL_dmeans3D + 3 * idx + 1, dL_dmean.y);
+        out1<MM>(io.dL_dmeans3D + 3 * idx + 2, dL_dmean.z);
     }
-    if (io.dL_dmeans2D) {
+    if (io.dL_dmeans2D) {       // per-view densification statistic: always local
         io.dL_dmeans2D[3 * idx] = dL_dmean2D.x; io.dL_dmeans2D[3 * idx + 1] = dL_dmean2D.y; io.dL_dmeans2D[3 * idx + 2] = 0.f;
     }
-    if (io.dL_dopacity) io.dL_dopacity[idx] = dL_dopacity;
+    if (io.dL_dopacity) out1<MM>(io.dL_dopacity + idx, dL_dopacity);
     if (io.dL_dcolors) {
-        io.dL_dcolors[3 * idx] = dL_dcolor[0]; io.dL_dcolors[3 * idx + 1] = dL_dcolor[1]; io.dL_dcolors[3 * idx + 2] = dL_dcolor[2];
+#pragma unroll
+        for (int k = 0; k < 3; k++) out1<MM>(io.dL_dcolors + 3 * idx + k, dL_dcolor[k]);
     }
     if (io.dL_dcov3D) {
 #pragma unroll
-        for (int k = 0; k < 6; k++) io.dL_dcov3D[6 * idx + k] = dL_dcov[k];
+        for (int k = 0; k < 6; k++) out1<MM>(io.dL_dcov3D + 6 * idx + k, dL_dcov[k]);
     }
     if (io.dL_dscales) {
-        io.dL_dscales[3 * idx] = dL_dscale.x; io.dL_dscales[3 * idx + 1] = dL_dscale.y; io.dL_dscales[3 * idx + 2] = dL_dscale.z;
+        out1<MM>(io.dL_dscales + 3 * idx, dL_dscale.x); out1<MM>(io.dL_dscales + 3 * idx + 1, dL_dscale.y);
+        out1<MM>(io.dL_dscales + 3 * idx + 2, dL_dscale.z);
     }
-    if (io.dL_drotations) reinterpret_cast<float4*>(io.dL_drotations)[idx] = dL_drot;
-    if (VEC && lane == 0) bulk_wait_read0();      // shared memory must outlive the bulk store's reads
+    if (io.dL_drotations) out4<MM>(io.dL_drotations + 4 * (size_t)idx, dL_drot);
+    if (VEC && !MM && lane == 0) bulk_wait_read0();      // shared memory must outlive the bulk store's reads
 }
 
 int launch_preprocess_backward(const GsrParams& p, GeomState g, Scratch s, const int32_t* radii,
@@ -424,12 +458,14 @@ int launch_preprocess_backward(const GsrParams& p, GeomState g, Scratch s, const
     // vector path: SH rows are whole float4s (M in {4, 8, 12, 16}) and 16 B aligned
     const bool vec = p.shs != nullptr && io.dL_dsh != nullptr && (p.M & 3) == 0 &&
                      (reinterpret_cast<uintptr_t>(p.shs) & 15) == 0 && (reinterpret_cast<uintptr_t>(io.dL_dsh) & 15) == 0;
-    if (vec)
-        GSR_LAUNCH(preprocess_bwd_kernel<true>, blocks, PB_THREADS, 0, st, p, focal_x, focal_y, g.rec, radii, s.acc,
-                                                                   have_invdepth, io);
-    else
-        GSR_LAUNCH(preprocess_bwd_kernel<false>, blocks, PB_THREADS, 0, st, p, focal_x, focal_y, g.rec, radii, s.acc,
-                                                                    have_invdepth, io);
+    const bool mm = io.multimem_reduce != 0;
+#define PB_LAUNCH(V, M) GSR_LAUNCH((preprocess_bwd_kernel<V, M>), blocks, PB_THREADS, 0, st, p, focal_x, focal_y, g.rec, \
+                                   radii, s.acc, have_invdepth, io)
+    if (vec && mm) PB_LAUNCH(true, true);
+    else if (vec) PB_LAUNCH(true, false);
+    else if (mm) PB_LAUNCH(false, true);
+    else PB_LAUNCH(false, false);
+#undef PB_LAUNCH
     return check_stage("preprocess backward", p.debug, st);
 }
 

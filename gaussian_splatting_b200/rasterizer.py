@@ -89,6 +89,16 @@ def _ptr(t):
     return None if t is None else t.data_ptr()
 
 
+# View-parallel fused reduction (view_parallel.FusedGradientReducer): when set, the backward kernel
+# adds its gradients into NVLink-multicast buffers instead of storing them locally.
+_gradient_reducer = None
+
+
+def set_gradient_reducer(reducer):
+    global _gradient_reducer
+    _gradient_reducer = reducer
+
+
 def _f32c(t, name):
     """fp32 contiguous CUDA tensor or None for an empty tensor (the reference's nullptr rule)."""
     if t is None or t.numel() == 0:
@@ -253,20 +263,36 @@ def _backward_native(rs, means3D, radii, colors_precomp, opacities, scales, rota
         buf.scratch, buf.scratch_bytes = ws.scratch.data_ptr(), ws.scratch.numel()
         buf.num_rendered_host = ws.pinned.data_ptr()
 
-        # every output is fully written by the fused backward kernel: no zero fills
-        dL_dmeans3D = torch.empty((P, 3), **f32)
         dL_dmeans2D = torch.empty((P, 3), **f32)
-        dL_dopacity = torch.empty((P, 1), **f32)
-        dL_dcolors = torch.empty((P, 3), **f32) if colors_precomp is not None else None
-        dL_dcov3D = torch.empty((P, 6), **f32) if cov3Ds_precomp is not None else None
-        dL_dsh = torch.empty((P, M, 3), **f32) if sh_c is not None else None
-        dL_dscales = torch.empty((P, 3), **f32) if scales is not None else None
-        dL_drotations = torch.empty((P, 4), **f32) if rotations is not None else None
-        io = GsrBackwardIO(grad_out_color.data_ptr(), _ptr(grad_out_depth), dL_dmeans3D.data_ptr(),
-                           dL_dmeans2D.data_ptr(), dL_dopacity.data_ptr(), _ptr(dL_dcolors), _ptr(dL_dcov3D),
-                           _ptr(dL_dsh), _ptr(dL_dscales), _ptr(dL_drotations))
+        want = [("means3D", (P, 3), True), ("opacity", (P, 1), True),
+                ("colors", (P, 3), colors_precomp is not None), ("cov3D", (P, 6), cov3Ds_precomp is not None),
+                ("sh", (P, M, 3), sh_c is not None), ("scales", (P, 3), scales is not None),
+                ("rotations", (P, 4), rotations is not None)]
+        names = [n for n, _, on in want if on]
+        shapes = [shp for _, shp, on in want if on]
+        red = _gradient_reducer
+        if red is None:
+            # every output is fully written by the fused backward kernel: no zero fills
+            outs = {n: torch.empty(shp, **f32) for n, shp in zip(names, shapes)}
+            addr = {n: t.data_ptr() for n, t in outs.items()}
+        else:
+            # outputs are views of this rank's replica of a symmetric buffer; the kernel reduces into
+            # all replicas through the multicast address
+            views, addrs = red.buffers(shapes, device)
+            outs = dict(zip(names, views))
+            addr = dict(zip(names, addrs))
+            red.begin()
+        io = GsrBackwardIO(grad_out_color.data_ptr(), _ptr(grad_out_depth), addr["means3D"],
+                           dL_dmeans2D.data_ptr(), addr["opacity"], addr.get("colors"), addr.get("cov3D"),
+                           addr.get("sh"), addr.get("scales"), addr.get("rotations"),
+                           0 if red is None else 1, 0)
         _lib.check(lib.gsr_backward(C.byref(p), C.byref(buf), R, radii.data_ptr(), C.byref(io),
                                     stream.cuda_stream))
+        if red is not None:
+            red.end()
+        dL_dmeans3D, dL_dopacity = outs["means3D"], outs["opacity"]
+        dL_dcolors, dL_dcov3D, dL_dsh = outs.get("colors"), outs.get("cov3D"), outs.get("sh")
+        dL_dscales, dL_drotations = outs.get("scales"), outs.get("rotations")
     return dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations
 
 

@@ -85,3 +85,94 @@ def reduce_densification_stats(viewspace_grad: torch.Tensor, radii: torch.Tensor
         dist.all_reduce(stats, op=dist.ReduceOp.SUM, group=group)
         dist.all_reduce(mx, op=dist.ReduceOp.MAX, group=group)
     return stats[:, 0:1], stats[:, 1:2], mx
+
+
+class FusedGradientReducer:
+    """All-reduce of the rasterizer's input gradients INSIDE the backward kernel (NVLS multicast).
+
+    The fused per-Gaussian backward kernel (csrc/preprocess_bwd.cu) writes every gradient exactly
+    once.  With this reducer installed (`install()`), those writes become `multimem.red.add.f32` on
+    the NVLink multicast address of a symmetric buffer replicated on all ranks, so the NVSwitch adds
+    the ranks' contributions while the kernel is still computing; no separate NCCL all-reduce pass
+    and no pack copy.  The gradients the autograd Function returns are views of this rank's replica
+    and already hold the SUM over ranks.  Because the activation / concat backward that follows in
+    autograd is linear in the incoming gradient and the parameters are replicated, reducing here is
+    equivalent to reducing the leaf gradients (up to fp32 rounding).
+
+    Contract (same as any gradient bucket that is reused): every rank calls backward the same number
+    of times, and the gradients returned by one backward are consumed (optimizer step / copy /
+    `grad = None`) before the next backward on this device.  dL_dmeans2D (per-view densification
+    statistic) is never reduced.
+
+    PyTorch is plumbing here: symmetric allocation + rendezvous + stream barriers come from
+    torch.distributed._symmetric_memory; the reduction itself is in our kernel.
+    """
+
+    ALIGN = 32   # floats (128 B) between segments
+
+    def __init__(self, group: Optional[dist.ProcessGroup] = None):
+        import torch.distributed._symmetric_memory as symm_mem
+        self._symm_mem = symm_mem
+        self.group = group if group is not None else dist.group.WORLD
+        self.world = dist.get_world_size(self.group)
+        self.flat = None
+        self.hdl = None
+        self.key = None
+        self.bytes_reduced = 0
+
+    @staticmethod
+    def available() -> bool:
+        try:
+            import torch.distributed._symmetric_memory  # noqa: F401
+        except Exception:   # noqa: BLE001
+            return False
+        return dist.is_available() and dist.is_initialized() and torch.cuda.is_available()
+
+    def _layout(self, shapes):
+        offs, off = [], 0
+        for shp in shapes:
+            n = 1
+            for d in shp:
+                n *= d
+            offs.append(off)
+            off += (n + self.ALIGN - 1) // self.ALIGN * self.ALIGN
+        return offs, off
+
+    def buffers(self, shapes, device):
+        """Returns (local views, multicast addresses) for gradient tensors of the given shapes.
+        (Re)allocates + rendezvous (a collective) when the shapes change, e.g. after densification."""
+        key = (tuple(tuple(s) for s in shapes), str(device))
+        if key != self.key:
+            offs, total = self._layout(shapes)
+            self.flat = self._symm_mem.empty(max(total, self.ALIGN), dtype=torch.float32, device=device)
+            self.hdl = self._symm_mem.rendezvous(self.flat, self.group.group_name)
+            if not self.hdl.multicast_ptr:
+                raise RuntimeError("NVLink multicast (NVLS) is not available for this group: use FlatGradients")
+            self.key, self.offs, self.total = key, offs, total
+        views, addrs = [], []
+        for shp, off in zip(shapes, self.offs):
+            n = 1
+            for d in shp:
+                n *= d
+            views.append(self.flat[off:off + n].view(*shp))
+            addrs.append(self.hdl.multicast_ptr + 4 * off)
+        return views, addrs
+
+    def begin(self):
+        """Zero this rank's replica and wait until every rank has done so (on the current stream)."""
+        self.flat.zero_()
+        self.hdl.barrier(channel=0)
+
+    def end(self):
+        """Wait until every rank's reductions have landed (on the current stream)."""
+        self.hdl.barrier(channel=1)
+        self.bytes_reduced = self.total * 4
+
+    def install(self):
+        from . import rasterizer
+        rasterizer.set_gradient_reducer(self)
+        return self
+
+    def uninstall(self):
+        from . import rasterizer
+        rasterizer.set_gradient_reducer(None)

@@ -111,6 +111,13 @@ typedef struct GsrBackwardIO {
     float* dL_dsh;         /* P*M*3 or NULL */
     float* dL_dscales;     /* P*3 or NULL */
     float* dL_drotations;  /* P*4 or NULL */
+    /* View-parallel fused reduction.  0: plain stores.  1: every output above except
+     * dL_dmeans2D is an NVLink MULTICAST address (NVLS) of a buffer replicated on all ranks; the
+     * kernel adds its non-zero values with multimem.red.add.f32, so after all ranks have run, every
+     * replica holds the sum over ranks.  The caller zeroes its replica and synchronises the ranks
+     * before and after (no NCCL all-reduce pass).  Pointers must be 16 B aligned. */
+    int32_t multimem_reduce;
+    int32_t reserved1;
 } GsrBackwardIO;
 
 int         gsr_version(void);

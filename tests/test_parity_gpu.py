@@ -283,3 +283,21 @@ def test_workspace_regrowth_keeps_results(dgr):
         outs[P] = o
     st = rasterizer.workspace_stats()
     assert st["scratch_bytes"] > 0 and st["regrows"] >= 1
+
+
+# ---------------------------------------------------------------- multi-GPU (only where >= 2 GPUs are visible)
+def test_fused_multicast_reduction_matches_nccl():
+    """tests/multi_gpu_check.py under torchrun: in-kernel NVLink-multicast gradient reduction vs NCCL."""
+    import os
+    import subprocess
+    import sys
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs (run tests/multi_gpu_check.py under torchrun on a multi-GPU box)")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29541",
+                        os.path.join(root, "tests", "multi_gpu_check.py")],
+                       capture_output=True, text=True, timeout=600, cwd=root)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "fused multimem reduction == NCCL all-reduce" in r.stdout
