@@ -108,6 +108,26 @@ static int validate_R(const GsrParams* p, const GsrBuffers* buf, int64_t R) {
     return GSR_OK;
 }
 
+// Host-side resources for the banded backward: one non-blocking side stream and a few events per
+// device, created on first use and kept for the life of the process (no device memory).
+struct SideStream {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t band_done[MAX_BANDS] = {};
+    cudaEvent_t joined = nullptr;
+};
+static SideStream g_side[64];
+static SideStream* side_stream() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    SideStream* s = &g_side[dev];
+    if (s->stream == nullptr) {
+        if (cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+        for (int i = 0; i < MAX_BANDS; i++) cudaEventCreateWithFlags(&s->band_done[i], cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&s->joined, cudaEventDisableTiming);
+    }
+    return s;
+}
+
 static inline size_t tiles_of(int W, int H) {
     return (size_t)((W + TILE_X - 1) / TILE_X) * (size_t)((H + TILE_Y - 1) / TILE_Y);
 }
@@ -228,9 +248,43 @@ int gsr_backward(const GsrParams* p, const GsrBuffers* buf, int64_t R, const int
     ImgState im = ImgState::carve(buf->img, (size_t)p->W * p->H, tiles_of(p->W, p->H), nullptr);
     BinState b = BinState::carve(buf->bin, (size_t)R, nullptr);
     Scratch s = Scratch::carve(buf->scratch, p->P, (size_t)R, nullptr);
-    rc = launch_render_backward(*p, g, im, b, s, io->dL_dout_color, io->dL_dout_invdepth, st);
+    const int gy = (p->H + TILE_Y - 1) / TILE_Y;
+    const bool have_invdepth = io->dL_dout_invdepth != nullptr;
+    int bands = io->multimem_reduce ? (io->reserved1 > 0 ? io->reserved1 : 1) : 1;
+    if (bands > gy) bands = gy;
+    if (bands > MAX_BANDS) bands = MAX_BANDS;
+    SideStream* side = bands > 1 ? side_stream() : nullptr;
+    // list mode needs whole-float4, 16 B aligned SH rows (same condition as the bulk-copy path)
+    const bool list_ok = p->shs == nullptr || io->dL_dsh == nullptr ||
+                         ((p->M & 3) == 0 && (reinterpret_cast<uintptr_t>(p->shs) & 15) == 0 &&
+                          (reinterpret_cast<uintptr_t>(io->dL_dsh) & 15) == 0);
+    if (bands <= 1 || side == nullptr || !list_ok) {
+        rc = launch_render_backward(*p, g, im, b, s, io->dL_dout_color, io->dL_dout_invdepth, 0, gy, true, st);
+        if (rc) return rc;
+        return launch_preprocess_backward(*p, g, s, radii, have_invdepth, *io, -1, st);
+    }
+    // Multicast-reduce mode with bands: run the blend backward band by band (tile rows, top to
+    // bottom) and hand every finished band's Gaussians (those whose last tile row lies in it) to the
+    // per-Gaussian kernel on a side stream, so that the gradient traffic of band k crosses NVLink
+    // while band k+1 is blended.
+    int band_hi[MAX_BANDS];
+    for (int k = 0; k < bands; k++) band_hi[k] = (int)((long long)gy * (k + 1) / bands);
+    GSR_CUDA_TRY(cudaEventRecord(side->joined, st));                       // order the side stream after the caller's work
+    GSR_CUDA_TRY(cudaStreamWaitEvent(side->stream, side->joined, 0));
+    rc = launch_band_lists(*p, g, s, radii, io->dL_dmeans2D, bands, band_hi, side->stream);
     if (rc) return rc;
-    return launch_preprocess_backward(*p, g, s, radii, io->dL_dout_invdepth != nullptr, *io, st);
+    for (int k = 0; k < bands; k++) {
+        const int lo = k == 0 ? 0 : band_hi[k - 1];
+        rc = launch_render_backward(*p, g, im, b, s, io->dL_dout_color, io->dL_dout_invdepth, lo, band_hi[k], k == 0, st);
+        if (rc) return rc;
+        GSR_CUDA_TRY(cudaEventRecord(side->band_done[k], st));
+        GSR_CUDA_TRY(cudaStreamWaitEvent(side->stream, side->band_done[k], 0));
+        rc = launch_preprocess_backward(*p, g, s, radii, have_invdepth, *io, k, side->stream);
+        if (rc) return rc;
+    }
+    GSR_CUDA_TRY(cudaEventRecord(side->joined, side->stream));
+    GSR_CUDA_TRY(cudaStreamWaitEvent(st, side->joined, 0));
+    return GSR_OK;
 }
 
 int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,

@@ -115,6 +115,10 @@ constexpr int SORT_MAX_PASSES = 4;
 constexpr size_t SORT_CTL_HIST = 0, SORT_CTL_BASE = 1024, SORT_CTL_TICKET = 2048, SORT_CTL_STATUS = 2112;
 inline size_t sort_ctl_words(size_t nb) { return SORT_CTL_STATUS + (size_t)SORT_MAX_PASSES * 256 * nb; }
 
+// band_ctl layout (u32 words): per-band counts, exclusive offsets, fill cursors, exclusive upper tile row
+constexpr int MAX_BANDS = 16;
+constexpr int BAND_CNT = 0, BAND_OFF = 16, BAND_CUR = 32, BAND_HI = 48, BAND_CTL_WORDS = 64;
+
 struct Scratch {            // only live inside one forward or backward call
     // forward
     uint2*    rects;        // P   packed rect {min.x | min.y<<16, max.x | max.y<<16}
@@ -131,6 +135,8 @@ struct Scratch {            // only live inside one forward or backward call
     int32_t*  counters;     // 8   device-side {R, overflow, ...}
     // backward
     float*    acc;          // P * ACC_FLOATS
+    uint32_t* band_list;    // P   visible Gaussian ids grouped by tile-row band (multimem mode)
+    uint32_t* band_ctl;     // BAND_CTL_WORDS: counts, offsets, cursors, band limits
     static Scratch carve(void* chunk, size_t P, size_t R, size_t* bytes) {
         Carver c(chunk); Scratch s;
         size_t Rn = R > 0 ? R : 1;
@@ -150,6 +156,8 @@ struct Scratch {            // only live inside one forward or backward call
         s.tile_ids = c.take<uint32_t>(Rn);
         // the backward accumulator aliases the forward instance buffers when it fits
         s.acc = c.take<float>(Pn * ACC_FLOATS);
+        s.band_list = c.take<uint32_t>(Pn);
+        s.band_ctl = c.take<uint32_t>(BAND_CTL_WORDS);
         if (bytes) *bytes = c.used();
         return s;
     }
@@ -192,9 +200,15 @@ int launch_binning(const GsrParams& p, GeomState g, ImgState im, BinState b, Scr
 int launch_render_forward(const GsrParams& p, GeomState g, ImgState im, BinState b,
                           float* out_color, float* out_invdepth, cudaStream_t st);
 int launch_render_backward(const GsrParams& p, GeomState g, ImgState im, BinState b, Scratch s,
-                           const float* dL_dpix, const float* dL_dinvdepth, cudaStream_t st);
+                           const float* dL_dpix, const float* dL_dinvdepth, int row_lo, int row_hi, bool zero_acc,
+                           cudaStream_t st);
+// band < 0: all Gaussians, dense outputs.  band >= 0 (multimem mode): the Gaussians of that band list.
 int launch_preprocess_backward(const GsrParams& p, GeomState g, Scratch s, const int32_t* radii,
-                               bool have_invdepth, const GsrBackwardIO& io, cudaStream_t st);
+                               bool have_invdepth, const GsrBackwardIO& io, int band, cudaStream_t st);
+// Groups the visible Gaussians by the tile-row band of their last tile row (band_hi[k] = exclusive
+// upper row of band k) into s.band_list / s.band_ctl; zeroes dL_dmeans2D of the culled ones.
+int launch_band_lists(const GsrParams& p, GeomState g, Scratch s, const int32_t* radii, float* dL_dmeans2D,
+                      int bands, const int* band_hi, cudaStream_t st);
 int launch_count_work(const GsrParams& p, GeomState g, ImgState im, BinState b, unsigned long long* counts,
                       cudaStream_t st);
 int launch_rebuild_keys(const GsrParams& p, GeomState g, ImgState im, BinState b, int64_t R,

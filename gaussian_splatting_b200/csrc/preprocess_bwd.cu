@@ -213,7 +213,9 @@ template <bool VEC, bool MM>
 __global__ void __launch_bounds__(PB_THREADS, PB_MIN_BLOCKS)
 preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord* __restrict__ rec,
                       const int32_t* __restrict__ radii, const float* __restrict__ acc,
-                      bool have_invdepth, GsrBackwardIO io) {
+                      bool have_invdepth, GsrBackwardIO io, const uint32_t* __restrict__ band_list,
+                      const uint32_t* __restrict__ band_ctl, int band) {
+    if (MM && band_list != nullptr && (uint32_t)(blockIdx.x * PB_THREADS) >= band_ctl[BAND_CNT + band]) return;
     __shared__ __align__(128) float sh_smem[PB_WARPS][32 * PB_STRIDE_SCALAR];
     __shared__ __align__(8) uint64_t s_bar[PB_WARPS];
     __shared__ float s_view[16], s_proj[16], s_cam[3];
@@ -229,14 +231,30 @@ preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord*
     __syncthreads();
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int idx = blockIdx.x * PB_THREADS + threadIdx.x;
     const int warp_base = blockIdx.x * PB_THREADS + warp * 32;
-    const bool in_range = idx < p.P;
-    const bool visible = in_range && radii[idx] > 0;
+    // List mode (multimem reduction, banded): this launch processes the visible Gaussians of one
+    // tile-row band, whose indices were compacted into band_list by band_fill_kernel.
+    const bool LIST = MM && band_list != nullptr;
+    int idx = blockIdx.x * PB_THREADS + threadIdx.x;
+    bool in_range = idx < p.P;
+    bool visible;
+    if (LIST) {
+        const uint32_t count = band_ctl[BAND_CNT + band];
+        in_range = (uint32_t)idx < count;
+        idx = in_range ? (int)band_list[band_ctl[BAND_OFF + band] + (uint32_t)idx] : 0;
+        visible = in_range;
+    } else {
+        visible = in_range && radii[idx] > 0;
+    }
+    const bool mine = in_range;
     const unsigned vis_mask = __ballot_sync(0xffffffffu, visible);
     const int sh_row = 3 * p.M;                                   // floats per Gaussian
     const uint32_t sh_bytes = (uint32_t)(max(0, min(32, p.P - warp_base)) * sh_row) * 4u;
-    if (VEC && vis_mask != 0 && lane == 0) {                      // prefetch this warp's SH rows
+    if (VEC && LIST) {                                            // gather: one bulk copy per Gaussian row
+        const uint32_t bar = smem_u32(&s_bar[warp]);
+        if (visible) bulk_g2s(smem_u32(sh_smem[warp] + lane * sh_row), p.shs + (size_t)idx * sh_row, (uint32_t)sh_row * 4u, bar);
+        if (lane == 0 && vis_mask != 0) mbar_arrive_expect_tx(bar, (uint32_t)__popc(vis_mask) * (uint32_t)sh_row * 4u);
+    } else if (VEC && vis_mask != 0 && lane == 0) {               // prefetch this warp's (contiguous) SH rows
         const uint32_t bar = smem_u32(&s_bar[warp]);
         mbar_arrive_expect_tx(bar, sh_bytes);
         bulk_g2s(smem_u32(sh_smem[warp]), p.shs + (size_t)warp_base * sh_row, sh_bytes, bar);
@@ -385,7 +403,17 @@ preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord*
             } else {
                 for (int k = 0; k < (row >> 2); k++) reinterpret_cast<float4*>(myrow)[k] = make_float4(0.f, 0.f, 0.f, 0.f);
             }
-            if (MM) {
+            if (MM && LIST) {
+                // 16 B multimem reductions, 12 consecutive lanes per (scattered) Gaussian row
+                __syncwarp();
+                const int row4 = row >> 2;
+                for (int f = lane; f < 32 * row4; f += 32) {
+                    const int gl = f / row4, k = f - gl * row4;
+                    const int gid = __shfl_sync(0xffffffffu, idx, gl);
+                    if ((vis_mask >> gl) & 1u)
+                        out4<true>(io.dL_dsh + (size_t)gid * row + 4 * k, reinterpret_cast<const float4*>(ws)[f]);
+                }
+            } else if (MM) {
                 // rows of this warp are contiguous: 16 B multimem reductions, coalesced across lanes
                 __syncwarp();
                 const int n4 = (int)(sh_bytes >> 4);
@@ -424,7 +452,7 @@ preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord*
         }
     }
 
-    if (!in_range) return;
+    if (!mine) return;
     if (io.dL_dmeans3D) {
         out1<MM>(io.dL_dmeans3D + 3 * idx, dL_dmean.x); out1<MM>(io.dL_dmeans3D + 3 * idx + 1, dL_dmean.y);
         out1<MM>(io.dL_dmeans3D + 3 * idx + 2, dL_dmean.z);
@@ -449,18 +477,105 @@ preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord*
     if (VEC && !MM && lane == 0) bulk_wait_read0();      // shared memory must outlive the bulk store's reads
 }
 
+// ---- band lists (multimem mode) ------------------------------------------------------------
+struct BandLimits { int n; int hi[MAX_BANDS]; };
+
+__device__ __forceinline__ int band_of(const GsRecord* r, int gy, const BandLimits& lim) {
+    const float py = r->q0.y;
+    const int rad = __float_as_int(r->q2.w);
+    const int last_row = min(gy, max(0, (int)((py + rad + TILE_Y - 1) / TILE_Y))) - 1;   // get_rect, gs_math.cuh
+    int k = 0;
+    while (k < lim.n - 1 && last_row >= lim.hi[k]) k++;
+    return k;
+}
+
+// Pass 1: per-band counts; culled Gaussians get their (never reduced) dL_dmeans2D zeroed here.
+__global__ void __launch_bounds__(256)
+band_count_kernel(int P, int gy, BandLimits lim, const GsRecord* __restrict__ rec, const int32_t* __restrict__ radii,
+                  float* __restrict__ dL_dmeans2D, uint32_t* __restrict__ ctl) {
+    __shared__ uint32_t s_cnt[MAX_BANDS];
+    if (threadIdx.x < MAX_BANDS) s_cnt[threadIdx.x] = 0;
+    __syncthreads();
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx < P) {
+        if (radii[idx] > 0) {
+            atomicAdd(&s_cnt[band_of(rec + idx, gy, lim)], 1u);
+        } else if (dL_dmeans2D) {
+            dL_dmeans2D[3 * idx] = 0.f; dL_dmeans2D[3 * idx + 1] = 0.f; dL_dmeans2D[3 * idx + 2] = 0.f;
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < lim.n && s_cnt[threadIdx.x]) atomicAdd(&ctl[BAND_CNT + threadIdx.x], s_cnt[threadIdx.x]);
+}
+
+__global__ void band_offsets_kernel(int n, uint32_t* __restrict__ ctl) {
+    uint32_t run = 0;
+    for (int k = 0; k < n; k++) {
+        ctl[BAND_OFF + k] = run;
+        ctl[BAND_CUR + k] = run;
+        run += ctl[BAND_CNT + k];
+    }
+}
+
+// Pass 2: compaction.  One atomic per (block, band); inside a block the ids stay in index order,
+// so neighbouring list entries are mostly neighbours in memory.
+__global__ void __launch_bounds__(256)
+band_fill_kernel(int P, int gy, BandLimits lim, const GsRecord* __restrict__ rec, const int32_t* __restrict__ radii,
+                 uint32_t* __restrict__ ctl, uint32_t* __restrict__ list) {
+    __shared__ uint32_t s_cnt[MAX_BANDS], s_base[MAX_BANDS];
+    if (threadIdx.x < MAX_BANDS) s_cnt[threadIdx.x] = 0;
+    __syncthreads();
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool vis = idx < P && radii[idx] > 0;
+    int k = 0;
+    uint32_t slot = 0;
+    if (vis) k = band_of(rec + idx, gy, lim);
+    // rank inside the block in thread order: warps take turns (8 warps, few bands)
+    for (int w = 0; w < 8; w++) {
+        if ((threadIdx.x >> 5) == w) {
+            for (int kb = 0; kb < lim.n; kb++) {
+                const unsigned m = __ballot_sync(0xffffffffu, vis && k == kb);
+                if (vis && k == kb) slot = s_cnt[kb] + __popc(m & ((1u << (threadIdx.x & 31)) - 1u));
+                __syncwarp();
+                if ((threadIdx.x & 31) == 0 && m) s_cnt[kb] += __popc(m);
+                __syncwarp();
+            }
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x < lim.n && s_cnt[threadIdx.x]) s_base[threadIdx.x] = atomicAdd(&ctl[BAND_CUR + threadIdx.x], s_cnt[threadIdx.x]);
+    __syncthreads();
+    if (vis) list[s_base[k] + slot] = (uint32_t)idx;
+}
+
+int launch_band_lists(const GsrParams& p, GeomState g, Scratch s, const int32_t* radii, float* dL_dmeans2D,
+                      int bands, const int* band_hi, cudaStream_t st) {
+    BandLimits lim;
+    lim.n = bands;
+    for (int k = 0; k < MAX_BANDS; k++) lim.hi[k] = k < bands ? band_hi[k] : 0x7fffffff;
+    const int gy = (p.H + TILE_Y - 1) / TILE_Y;
+    const int blocks = (p.P + 255) / 256;
+    StageTimer tm(GSR_STAGE_PREPROCESS_BWD, st);
+    GSR_CUDA_TRY(cudaMemsetAsync(s.band_ctl, 0, BAND_CTL_WORDS * sizeof(uint32_t), st));
+    GSR_LAUNCH(band_count_kernel, blocks, 256, 0, st, p.P, gy, lim, g.rec, radii, dL_dmeans2D, s.band_ctl);
+    GSR_LAUNCH(band_offsets_kernel, 1, 1, 0, st, bands, s.band_ctl);
+    GSR_LAUNCH(band_fill_kernel, blocks, 256, 0, st, p.P, gy, lim, g.rec, radii, s.band_ctl, s.band_list);
+    return check_stage("band lists", p.debug, st);
+}
+
 int launch_preprocess_backward(const GsrParams& p, GeomState g, Scratch s, const int32_t* radii,
-                               bool have_invdepth, const GsrBackwardIO& io, cudaStream_t st) {
+                               bool have_invdepth, const GsrBackwardIO& io, int band, cudaStream_t st) {
     const float focal_y = p.H / (2.0f * p.tanfovy);
     const float focal_x = p.W / (2.0f * p.tanfovx);
     const int blocks = (p.P + PB_THREADS - 1) / PB_THREADS;
+    const uint32_t* blist = band >= 0 ? s.band_list : nullptr;
     StageTimer tm(GSR_STAGE_PREPROCESS_BWD, st);
     // vector path: SH rows are whole float4s (M in {4, 8, 12, 16}) and 16 B aligned
     const bool vec = p.shs != nullptr && io.dL_dsh != nullptr && (p.M & 3) == 0 &&
                      (reinterpret_cast<uintptr_t>(p.shs) & 15) == 0 && (reinterpret_cast<uintptr_t>(io.dL_dsh) & 15) == 0;
     const bool mm = io.multimem_reduce != 0;
 #define PB_LAUNCH(V, M) GSR_LAUNCH((preprocess_bwd_kernel<V, M>), blocks, PB_THREADS, 0, st, p, focal_x, focal_y, g.rec, \
-                                   radii, s.acc, have_invdepth, io)
+                                   radii, s.acc, have_invdepth, io, blist, s.band_ctl, band)
     if (vec && mm) PB_LAUNCH(true, true);
     else if (vec) PB_LAUNCH(true, false);
     else if (mm) PB_LAUNCH(false, true);

@@ -285,7 +285,7 @@ def _backward_native(rs, means3D, radii, colors_precomp, opacities, scales, rota
         io = GsrBackwardIO(grad_out_color.data_ptr(), _ptr(grad_out_depth), addr["means3D"],
                            dL_dmeans2D.data_ptr(), addr["opacity"], addr.get("colors"), addr.get("cov3D"),
                            addr.get("sh"), addr.get("scales"), addr.get("rotations"),
-                           0 if red is None else 1, 0)
+                           0 if red is None else 1, 0 if red is None else int(getattr(red, "bands", 0)))
         _lib.check(lib.gsr_backward(C.byref(p), C.byref(buf), R, radii.data_ptr(), C.byref(io),
                                     stream.cuda_stream))
         if red is not None:

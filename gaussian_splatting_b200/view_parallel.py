@@ -110,8 +110,16 @@ class FusedGradientReducer:
 
     ALIGN = 32   # floats (128 B) between segments
 
-    def __init__(self, group: Optional[dist.ProcessGroup] = None):
+    def __init__(self, group: Optional[dist.ProcessGroup] = None, bands: int = 0):
+        """bands: tile-row bands of the blend backward pipelined against the NVLink-bound per-Gaussian
+        kernel (0 = library default, 1 = no pipelining)."""
+        import os
         import torch.distributed._symmetric_memory as symm_mem
+        self.bands = int(os.environ.get("GSR_REDUCE_BANDS", bands))
+        if self.bands <= 0:
+            # measured on 8 x B200 (profiles/r01_scaling): 4 bands 4.19 ms/step vs 4.40 unbanded at 8 ranks;
+            # at 2 ranks NVLink is not the bound and banding only adds contention (3.92 vs 3.69 ms)
+            self.bands = 4 if dist.get_world_size(group if group is not None else dist.group.WORLD) >= 8 else 1
         self._symm_mem = symm_mem
         self.group = group if group is not None else dist.group.WORLD
         self.world = dist.get_world_size(self.group)

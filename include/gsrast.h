@@ -117,7 +117,7 @@ typedef struct GsrBackwardIO {
      * replica holds the sum over ranks.  The caller zeroes its replica and synchronises the ranks
      * before and after (no NCCL all-reduce pass).  Pointers must be 16 B aligned. */
     int32_t multimem_reduce;
-    int32_t reserved1;
+    int32_t reserved1;     /* multimem mode: number of tile-row bands pipelined against the blend backward (0 or 1 = no pipelining) */
 } GsrBackwardIO;
 
 int         gsr_version(void);
