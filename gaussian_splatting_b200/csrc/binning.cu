@@ -224,8 +224,11 @@ radix_bases_kernel(const uint32_t* __restrict__ ghist, uint32_t* __restrict__ gb
     gbase[blockIdx.x * 256 + threadIdx.x] = block_excl_scan_256(c, s_w, nullptr);
 }
 
+#ifndef OS_MIN_BLOCKS
+#define OS_MIN_BLOCKS 3
+#endif
 template <bool SPLIT>
-__global__ void __launch_bounds__(OS_THREADS, 2)
+__global__ void __launch_bounds__(OS_THREADS, OS_MIN_BLOCKS)
 onesweep_kernel(const uint64_t* __restrict__ in, uint32_t n, int shift, const uint32_t* __restrict__ gbase,
                 uint32_t* status, uint32_t* ticket,
                 uint64_t* __restrict__ out, uint32_t* __restrict__ out_lo, uint32_t* __restrict__ out_hi) {
@@ -246,7 +249,7 @@ onesweep_kernel(const uint64_t* __restrict__ in, uint32_t n, int shift, const ui
     const uint32_t n_block = min((uint32_t)OS_TILE, n - block_base);
 
     uint64_t items[OS_ITEMS];
-    uint32_t ranks[OS_ITEMS];
+    uint32_t ranks[OS_ITEMS / 2];
 #pragma unroll
     for (int i = 0; i < OS_ITEMS; i++) {
         const uint32_t idx = warp * (32 * OS_ITEMS) + i * 32 + lane;
@@ -254,32 +257,26 @@ onesweep_kernel(const uint64_t* __restrict__ in, uint32_t n, int shift, const ui
     }
     // Lanes holding the same digit, by 8 ballots per item.  (MATCH.ANY costs one round per distinct
     // value in the warp -- ~30 with random 8-bit digits -- and was the bottleneck of this kernel.)
-    uint32_t masks[OS_ITEMS];
-#pragma unroll
-    for (int i = 0; i < OS_ITEMS; i++) {
-        const uint32_t idx = warp * (32 * OS_ITEMS) + i * 32 + lane;
-        const uint32_t d = (uint32_t)(items[i] >> shift) & 255u;
-        uint32_t m = __ballot_sync(0xffffffffu, idx < n_block);
-#pragma unroll
-        for (int b = 0; b < 8; b++) {
-            const bool bit = (d >> b) & 1u;
-            const uint32_t v = __ballot_sync(0xffffffffu, bit);
-            m &= bit ? v : ~v;
-        }
-        masks[i] = m;
-    }
+    // Ranks are < 512 and kept two per register to stay within OS_MIN_BLOCKS CTAs per SM.
 #pragma unroll
     for (int i = 0; i < OS_ITEMS; i++) {
         const uint32_t idx = warp * (32 * OS_ITEMS) + i * 32 + lane;
         const bool valid = idx < n_block;
         const uint32_t d = (uint32_t)(items[i] >> shift) & 255u;
-        const uint32_t mask = masks[i];
+        uint32_t mask = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+        for (int b = 0; b < 8; b++) {
+            const bool bit = (d >> b) & 1u;
+            const uint32_t v = __ballot_sync(0xffffffffu, bit);
+            mask &= bit ? v : ~v;
+        }
         const uint32_t lower = mask & ((1u << lane) - 1u);
         const uint32_t old = valid ? wh[warp][d] : 0u;     // every lane of the group reads the same counter
         __syncwarp();
         if (valid && lower == 0) wh[warp][d] = (uint16_t)(old + __popc(mask));   // group leader
         __syncwarp();
-        ranks[i] = old + __popc(lower);
+        const uint32_t r = old + __popc(lower);
+        if (i & 1) ranks[i >> 1] |= r << 16; else ranks[i >> 1] = r;
     }
     __syncthreads();
 
@@ -336,7 +333,7 @@ onesweep_kernel(const uint64_t* __restrict__ in, uint32_t n, int shift, const ui
         const uint32_t idx = warp * (32 * OS_ITEMS) + i * 32 + lane;
         if (idx < n_block) {
             const uint32_t d = (uint32_t)(items[i] >> shift) & 255u;
-            stage[s_dstart[d] + wh[warp][d] + ranks[i]] = items[i];
+            stage[s_dstart[d] + wh[warp][d] + ((ranks[i >> 1] >> ((i & 1) * 16)) & 0xffffu)] = items[i];
         }
     }
     __syncthreads();
