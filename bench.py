@@ -301,6 +301,21 @@ def rooflines(stage_ms, work, peaks, sm_mhz):
     return out
 
 
+def ncu_evidence(stage):
+    """DRAM traffic per launch and issue-slot utilisation of a stage's kernel from the committed
+    `ncu --set full` capture of this same workload (profiles/r01f_kernels.json); None if absent."""
+    path = os.path.join(ROOT, "profiles", "r01f_kernels.json")
+    kernel = {"render_bwd": "render_bwd_kernel", "render_fwd": "render_fwd_kernel",
+              "preprocess_bwd": "preprocess_bwd_kernel", "preprocess": "preprocess_fwd_kernel"}.get(stage)
+    if kernel is None or not os.path.exists(path):
+        return None
+    for k in json.load(open(path)):
+        if k["kernel"].startswith(kernel):
+            return dict(traffic=int((k["dram_read_MB"] + k["dram_write_MB"]) * 1e6),
+                        issue_active=round(k["issue_active_pct"] / 100.0, 3), source="profiles/r01f_kernels.json")
+    return None
+
+
 def measure_work(wl, device):
     """Work descriptors of this rank's view from the state of one forward (independent counting pass)."""
     from gaussian_splatting_b200 import rasterizer
@@ -430,6 +445,10 @@ def run_gpu_arm(args, module, impl, rank, world, local):
                             "ms": top["ms"],
                             "peak_source": (f"{peaks['source']} copy bandwidth (MEASURED_PEAKS.json)" if top["bound"] == "hbm"
                                             else "FP32 CUDA-core peak = 148 SMs x 128 lanes x 2 x max SM clock")}
+        ev = ncu_evidence(top["stage"]) if wl["cfg"].name == "C3" and wl["P"] == wl["cfg"].P else None
+        if ev:
+            line["roofline"].update(traffic=ev["traffic"], issue_slot_utilisation=ev["issue_active"],
+                                    ncu_source=ev["source"])
         hbm = [s for s in stages if s["bound"] == "hbm"]
         if hbm:
             line["roofline_hbm"] = hbm[0]
@@ -476,6 +495,10 @@ def main():
             return 0
         line, wl = run_gpu_arm(args, ref, "reference", 0, 1, local)
         line["n_gpus"] = 1
+        # the reference ships no CPU rasterizer: its own implementation of the path is
+        # CUDA, timed here on one B200; the CPU port of the same math is `cpu_baseline` of the ours arm
+        line["cpu_baseline"] = {"value": line["value"], "unit": UNIT, "cores": 0, "kind": "reference",
+                                "sample": "full workload on one B200 (the reference's only implementation is CUDA)"}
         line["reference"] = {"kind": "reference", "what": "the reference's own CUDA rasterizer "
                              "(submodules/diff-gaussian-rasterization) compiled for sm_100 by oracle/build_ref.py; "
                              f"variant '{args.ref_variant}' (SURVEY.md F1-F3 repairs)"}

@@ -358,18 +358,29 @@ onesweep_kernel(const uint64_t* __restrict__ in, uint32_t n, int shift, const ui
 // Stable LSD sort of n u64 items on `passes` 8-bit digits from bit `shift` (a -> b -> a ...).
 // split_last: the final pass writes low words to out_lo and high words to out_hi instead.
 // Returns through *result the buffer holding the sorted items (unused with split_last).
+static int radix_sort_reset(uint32_t n, int passes, Scratch s, cudaStream_t st) {
+    const uint32_t nb = div_up(n, OS_TILE);
+    GSR_CUDA_TRY(cudaMemsetAsync(s.sort_ctl, 0, (SORT_CTL_STATUS + (size_t)passes * 256 * nb) * sizeof(uint32_t), st));
+    return GSR_OK;
+}
+
+// have_hist: the digit histograms were already accumulated into the (reset) control block by the
+// producer of the items (instance emission), so the input is not read an extra time.
 static int radix_sort_onesweep(uint64_t* a, uint64_t* b, uint32_t n, int shift, int passes, Scratch s,
                                bool split_last, uint32_t* out_lo, uint32_t* out_hi, uint64_t** result,
-                               cudaStream_t st) {
+                               bool have_hist, cudaStream_t st) {
     const uint32_t nb = div_up(n, OS_TILE);
     uint32_t* ctl = s.sort_ctl;
-    GSR_CUDA_TRY(cudaMemsetAsync(ctl, 0, (SORT_CTL_STATUS + (size_t)passes * 256 * nb) * sizeof(uint32_t), st));
+    if (!have_hist) {
+    int rc = radix_sort_reset(n, passes, s, st);
+    if (rc) return rc;
     const uint32_t hist_blocks = min(div_up(n, 512u), 148u * 8u);
     switch (passes) {
         case 1: GSR_LAUNCH(radix_hist_multi_kernel<1>, hist_blocks, 256, 0, st, a, n, shift, ctl + SORT_CTL_HIST); break;
         case 2: GSR_LAUNCH(radix_hist_multi_kernel<2>, hist_blocks, 256, 0, st, a, n, shift, ctl + SORT_CTL_HIST); break;
         case 3: GSR_LAUNCH(radix_hist_multi_kernel<3>, hist_blocks, 256, 0, st, a, n, shift, ctl + SORT_CTL_HIST); break;
         default: GSR_LAUNCH(radix_hist_multi_kernel<4>, hist_blocks, 256, 0, st, a, n, shift, ctl + SORT_CTL_HIST); break;
+    }
     }
     GSR_LAUNCH(radix_bases_kernel, passes, 256, 0, st, ctl + SORT_CTL_HIST, ctl + SORT_CTL_BASE);
     for (int pass = 0; pass < passes; pass++) {
@@ -472,21 +483,73 @@ scan_apply_kernel(uint32_t* __restrict__ offsets, uint32_t P, const uint32_t* __
 
 // ---------------------------------------------------------------- instance emission
 // duplicateWithKeys (rasterizer_impl.cu:78-126) in depth order; item = tile<<32 | id.
-__global__ void __launch_bounds__(256)
+// Warp-cooperative: a warp owns 32 consecutive depth ranks, whose instances occupy one contiguous
+// range of the output; lane j writes instance first + j, first + j + 32, ... (coalesced 8 B stores)
+// after locating its Gaussian among the warp's 32 inclusive offsets with a 5-step shuffle search.
+// The 8-bit digit histograms of the tile ids (what the following radix sort needs) are accumulated
+// on the way, so the instance list is not read again for them.
+constexpr int EMIT_THREADS = 256;
+constexpr int EMIT_ROUNDS = 4;                     // 1024 Gaussians per CTA
+
+template <int PASSES>
+__global__ void __launch_bounds__(EMIT_THREADS)
 emit_instances_kernel(const uint64_t* __restrict__ sorted, const uint2* __restrict__ rects,
                       const uint32_t* __restrict__ offsets, uint32_t P, uint32_t grid_x,
-                      uint64_t* __restrict__ inst) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= P) return;
-    uint64_t it = sorted[i];
-    if ((uint32_t)(it >> 32) == 0xFFFFFFFFu) return;   // culled
-    uint32_t g = (uint32_t)it;
-    uint2 r = rects[g];
-    uint32_t x0 = r.x & 0xffffu, y0 = r.x >> 16, x1 = r.y & 0xffffu, y1 = r.y >> 16;
-    uint32_t off = offsets[i] - (x1 - x0) * (y1 - y0);
-    for (uint32_t y = y0; y < y1; y++)
-        for (uint32_t x = x0; x < x1; x++)
-            inst[off++] = ((uint64_t)(y * grid_x + x) << 32) | g;
+                      uint64_t* __restrict__ inst, uint32_t* __restrict__ ghist) {
+    __shared__ uint32_t s_hist[PASSES][256];
+#pragma unroll
+    for (int p = 0; p < PASSES; p++) s_hist[p][threadIdx.x] = 0;
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t last_incl = offsets[P - 1];
+    for (int round = 0; round < EMIT_ROUNDS; round++) {
+        const uint32_t i = (blockIdx.x * EMIT_ROUNDS + round) * EMIT_THREADS + threadIdx.x;
+        uint32_t g = 0, x0 = 0, y0 = 0, w = 1, incl = last_incl, cnt = 0;
+        if (i < P) {
+            const uint64_t it = sorted[i];
+            incl = offsets[i];
+            if ((uint32_t)(it >> 32) != 0xFFFFFFFFu) {          // not culled
+                g = (uint32_t)it;
+                const uint2 r = rects[g];
+                x0 = r.x & 0xffffu; y0 = r.x >> 16;
+                w = (r.y & 0xffffu) - x0;
+                cnt = w * ((r.y >> 16) - y0);
+            }
+        }
+        const uint32_t excl = incl - cnt;
+        const uint32_t first = __shfl_sync(0xffffffffu, excl, 0);
+        const uint32_t total = __shfl_sync(0xffffffffu, incl, 31) - first;
+        const uint32_t xy = x0 | (y0 << 16);
+        for (uint32_t j = lane; j < ((total + 31u) & ~31u); j += 32) {      // uniform trip count: shuffles inside
+            const uint32_t target = first + j;
+            // L = number of lanes whose inclusive offset is <= target = owner of instance `target`
+            uint32_t L = 0;
+#pragma unroll
+            for (int step = 16; step > 0; step >>= 1) {
+                const uint32_t probe = __shfl_sync(0xffffffffu, incl, (L + step - 1) & 31);
+                if (L + step <= 32 && probe <= target) L += step;
+            }
+            const uint32_t src = L & 31;
+            const uint32_t o_excl = __shfl_sync(0xffffffffu, excl, src);
+            const uint32_t o_w = __shfl_sync(0xffffffffu, w, src);
+            const uint32_t o_xy = __shfl_sync(0xffffffffu, xy, src);
+            const uint32_t o_g = __shfl_sync(0xffffffffu, g, src);
+            if (j < total) {
+                const uint32_t local = target - o_excl;
+                const uint32_t ry = local / o_w, rx = local - ry * o_w;
+                const uint32_t tile = ((o_xy >> 16) + ry) * grid_x + (o_xy & 0xffffu) + rx;
+                inst[target] = ((uint64_t)tile << 32) | o_g;
+#pragma unroll
+                for (int p = 0; p < PASSES; p++) atomicAdd(&s_hist[p][(tile >> (8 * p)) & 255u], 1u);
+            }
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int p = 0; p < PASSES; p++) {
+        const uint32_t c = s_hist[p][threadIdx.x];
+        if (c) atomicAdd(&ghist[p * 256 + threadIdx.x], c);
+    }
 }
 
 // identifyTileRanges (rasterizer_impl.cu:132-164) on the sorted tile ids; 4 instances per thread.
@@ -540,7 +603,7 @@ int launch_depth_order_and_scan(const GsrParams& p, GeomState g, Scratch s, int3
     {
         StageTimer tm(GSR_STAGE_DEPTH_SORT, st);
         if (P < OS_MAX_N) {
-            int rc = radix_sort_onesweep(a, b, P, 32, 4, s, false, nullptr, nullptr, nullptr, st);
+            int rc = radix_sort_onesweep(a, b, P, 32, 4, s, false, nullptr, nullptr, nullptr, false, st);
             if (rc) return rc;
         } else {
             for (int pass = 0; pass < 4; pass++) {
@@ -575,22 +638,36 @@ int launch_binning(const GsrParams& p, GeomState g, ImgState im, BinState b, Scr
     GSR_CUDA_TRY(cudaMemsetAsync(im.ranges, 0, (size_t)T * sizeof(uint2), st));   // rasterizer_impl.cu:342
     if (R <= 0) return GSR_OK;
     const uint32_t n = (uint32_t)R;
-    {
-        StageTimer tm(GSR_STAGE_EMIT, st);
-        GSR_LAUNCH(emit_instances_kernel, div_up(P, 256), 256, 0, st, s.depth_a, s.rects, s.offsets, P, gx, s.inst_a);
-    }
-    int rc = check_stage("emit instances", p.debug, st);
-    if (rc) return rc;
     // reference sorts bits [0, 32+getHigherMsb(T)) (rasterizer_impl.cu:332-340); the low 32
     // (depth) are already in order, so only the tile bits remain.
     const int bits = (int)higher_msb(T);
     const int passes = (bits + 7) / 8;
+    const bool fused_hist = n < OS_MAX_N;
+    int rc = GSR_OK;
+    {
+        StageTimer tm(GSR_STAGE_EMIT, st);
+        const uint32_t eb = div_up(P, EMIT_THREADS * EMIT_ROUNDS);
+        uint32_t* gh = s.sort_ctl + SORT_CTL_HIST;
+        if (fused_hist) {
+            rc = radix_sort_reset(n, passes, s, st);
+            if (rc) return rc;
+        }
+        switch (fused_hist ? passes : 0) {
+            case 1: GSR_LAUNCH(emit_instances_kernel<1>, eb, EMIT_THREADS, 0, st, s.depth_a, s.rects, s.offsets, P, gx, s.inst_a, gh); break;
+            case 2: GSR_LAUNCH(emit_instances_kernel<2>, eb, EMIT_THREADS, 0, st, s.depth_a, s.rects, s.offsets, P, gx, s.inst_a, gh); break;
+            case 3: GSR_LAUNCH(emit_instances_kernel<3>, eb, EMIT_THREADS, 0, st, s.depth_a, s.rects, s.offsets, P, gx, s.inst_a, gh); break;
+            default: GSR_LAUNCH(emit_instances_kernel<4>, eb, EMIT_THREADS, 0, st, s.depth_a, s.rects, s.offsets, P, gx, s.inst_a,
+                                s.hist /* unused scratch */); break;
+        }
+    }
+    rc = check_stage("emit instances", p.debug, st);
+    if (rc) return rc;
     uint64_t* a = s.inst_a;
     uint64_t* c = s.inst_b;
     {
         StageTimer tm(GSR_STAGE_TILE_SORT, st);
-        if (n < OS_MAX_N) {
-            rc = radix_sort_onesweep(a, c, n, 32, passes, s, true, b.point_list, s.tile_ids, nullptr, st);
+        if (fused_hist) {
+            rc = radix_sort_onesweep(a, c, n, 32, passes, s, true, b.point_list, s.tile_ids, nullptr, true, st);
             if (rc) return rc;
         } else
         for (int pass = 0; pass < passes; pass++) {
