@@ -60,7 +60,7 @@ EXPORTS = (
     "gsr_scratch_bytes", "gsr_forward_stage1", "gsr_forward_stage2", "gsr_forward", "gsr_backward",
     "gsr_mark_visible", "gsr_debug_sorted_keys", "gsr_debug_state_ptrs", "gsr_flat_grad_floats",
     "gsr_debug_count_work",
-    "gsr_profile_enable", "gsr_profile_collect", "gsr_stage_name", "gsr_launch_count",
+    "gsr_profile_enable", "gsr_profile_collect", "gsr_stage_name", "gsr_launch_count", "gsr_adam_update",
 )
 STAGE_COUNT = 9
 
@@ -113,6 +113,8 @@ def load():
     lib.gsr_stage_name.restype = C.c_char_p
     lib.gsr_stage_name.argtypes = [C.c_int]
     lib.gsr_launch_count.restype = C.c_uint64
+    lib.gsr_adam_update.restype = C.c_int
+    lib.gsr_adam_update.argtypes = [C.c_void_p] * 5 + [C.c_double] * 6 + [C.c_int64, C.c_int32, C.c_void_p]
     _lib = lib
     return lib
 

@@ -364,8 +364,17 @@ class GaussianRasterizer(nn.Module):
         return visible
 
     def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
-                cov3D_precomp=None):
+                cov3D_precomp=None, dc=None):
         raster_settings = self.raster_settings
+
+        # `dc=` is the keyword render() uses when SparseGaussianAdam is importable
+        # (gaussian_renderer/__init__.py:115-125, separate_sh): degree-0 coefficients (P,1,3) and the rest
+        # (P,15,3) arrive separately.  It is appended to the fork's signature so positional callers of the
+        # fork's order keep working.
+        if dc is not None:
+            if colors_precomp is not None:
+                raise Exception('Please provide exactly one of either SHs or precomputed colors!')
+            shs = dc if shs is None or shs.numel() == 0 else torch.cat((dc, shs), dim=1)
 
         if (shs is None and colors_precomp is None) or (shs is not None and colors_precomp is not None):
             raise Exception('Please provide exactly one of either SHs or precomputed colors!')

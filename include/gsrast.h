@@ -157,6 +157,14 @@ int gsr_backward(const GsrParams* p, const GsrBuffers* buf, int64_t R,
 int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,
                      const float* projmatrix, uint8_t* present, void* stream);
 
+/* Fused Adam step over one parameter tensor of N Gaussians x M floats (role of the
+ * `SparseGaussianAdam.step(visible, N)` that train.py:240-247 calls and the fork does not ship).
+ * torch.optim.Adam's update (bias_correction1 = 1 - beta1^t, bias_correction2_sqrt = sqrt(1 - beta2^t)),
+ * applied only where visible[g] != 0 (visible == NULL: everywhere).  In place, one pass. */
+int gsr_adam_update(float* param, const float* grad, float* exp_avg, float* exp_avg_sq,
+                    const uint8_t* visible, double lr, double beta1, double beta2, double eps,
+                    double bias_correction1, double bias_correction2_sqrt, int64_t N, int32_t M, void* stream);
+
 /* Test/inspection hooks (bit-exact parity of the binning stage):
  * rebuild the reference's sorted 64-bit key list (tile<<32 | depth bits) and
  * expose point_list / ranges held in the state buffers.  Device pointers. */

@@ -75,8 +75,9 @@ def fwd_bwd_fns(module, gs, s, dev):
     return fwd, fwdbwd
 
 
-def train_step_fn(module, gs, s, dev):
-    """C2: the per-iteration work of train.py:143-251 without datasets."""
+def train_step_fn(module, gs, s, dev, sparse_adam=False):
+    """C2: the per-iteration work of train.py:143-251 without datasets.
+    sparse_adam: the fork's accelerated branch (separate_sh / dc= keyword, optimizer.step(visible, N))."""
     P = gs["means3D"].shape[0]
     nnp = torch.nn.Parameter
     xyz = nnp(gs["means3D"].to(dev))
@@ -85,7 +86,8 @@ def train_step_fn(module, gs, s, dev):
     scaling = nnp(torch.log(gs["scales"]).to(dev))
     rotation = nnp(gs["rotations"].to(dev))
     opacity = nnp(torch.logit(gs["opacities"].clamp(1e-4, 1 - 1e-4)).to(dev))
-    opt = torch.optim.Adam([
+    Opt = module.SparseGaussianAdam if sparse_adam else torch.optim.Adam
+    opt = Opt([
         {"params": [xyz], "lr": 1.6e-4}, {"params": [f_dc], "lr": 2.5e-3}, {"params": [f_rest], "lr": 2.5e-3 / 20},
         {"params": [opacity], "lr": 0.025}, {"params": [scaling], "lr": 0.005}, {"params": [rotation], "lr": 0.001},
     ], lr=0.0, eps=1e-15)
@@ -96,12 +98,15 @@ def train_step_fn(module, gs, s, dev):
 
     def step():
         m2 = torch.zeros(P, 3, device=dev, requires_grad=True)
-        shs = torch.cat((f_dc, f_rest), dim=1)
-        color, radii, invd = rast(means3D=xyz, means2D=m2, opacities=torch.sigmoid(opacity), shs=shs,
-                                  scales=torch.exp(scaling), rotations=torch.nn.functional.normalize(rotation))
+        kw = dict(dc=f_dc, shs=f_rest) if sparse_adam else dict(shs=torch.cat((f_dc, f_rest), dim=1))
+        color, radii, invd = rast(means3D=xyz, means2D=m2, opacities=torch.sigmoid(opacity),
+                                  scales=torch.exp(scaling), rotations=torch.nn.functional.normalize(rotation), **kw)
         loss = (color - target).abs().mean() + 0.1 * (invd - target_d).abs().mean()
         loss.backward()
-        opt.step()
+        if sparse_adam:
+            opt.step(radii > 0, radii.shape[0])               # train.py:240-247
+        else:
+            opt.step()
         opt.zero_grad(set_to_none=True)
 
     return step
@@ -118,24 +123,9 @@ def main():
     except Exception as ex:  # noqa: BLE001
         print(f"# reference CUDA build unavailable: {ex}", file=sys.stderr)
     out = {}
-    for name in ("C1", "C2", "C3", "C4"):
-        cfg = synthetic.CONFIGS[name]
-        gs, s = scene(cfg)
-        row = {"P": cfg.P, "W": cfg.W, "H": cfg.H}
-        for mname, m in mods.items():
-            fwd, fwdbwd = fwd_bwd_fns(m, gs, s, dev)
-            r = {"fwd_ms": round(timeit(fwd), 3), "fwd_bwd_ms": round(timeit(fwdbwd), 3)}
-            if name == "C2":
-                r["train_step_ms"] = round(timeit(train_step_fn(m, gs, s, dev)), 3)
-            row[mname] = r
-            torch.cuda.empty_cache()
-        if "reference" in row:
-            row["speedup_fwd_bwd"] = round(row["reference"]["fwd_bwd_ms"] / row["ours"]["fwd_bwd_ms"], 2)
-            row["speedup_fwd"] = round(row["reference"]["fwd_ms"] / row["ours"]["fwd_ms"], 2)
-        out[name] = row
-        print(f"# {name}: {row}", file=sys.stderr)
     # C5: densification stress (ours): growing P, dynamic workspace, sort bit-width via resolution
     c3 = synthetic.CONFIGS["C3"]
+    ours = mods["ours"]
     c5 = []
     for k in range(11):
         P = int(500_000 * 10 ** (k / 10))
@@ -148,6 +138,24 @@ def main():
                    "regrows": st["regrows"], "wall_s": round(time.time() - t0, 2)})
         torch.cuda.empty_cache()
     out["C5"] = c5
+    for name in ("C1", "C2", "C3", "C4"):
+        cfg = synthetic.CONFIGS[name]
+        gs, s = scene(cfg)
+        row = {"P": cfg.P, "W": cfg.W, "H": cfg.H}
+        for mname, m in mods.items():
+            fwd, fwdbwd = fwd_bwd_fns(m, gs, s, dev)
+            r = {"fwd_ms": round(timeit(fwd), 3), "fwd_bwd_ms": round(timeit(fwdbwd), 3)}
+            if name == "C2":
+                r["train_step_ms"] = round(timeit(train_step_fn(m, gs, s, dev)), 3)
+                if hasattr(m, "SparseGaussianAdam"):
+                    r["train_step_sparse_adam_ms"] = round(timeit(train_step_fn(m, gs, s, dev, sparse_adam=True)), 3)
+            row[mname] = r
+            torch.cuda.empty_cache()
+        if "reference" in row:
+            row["speedup_fwd_bwd"] = round(row["reference"]["fwd_bwd_ms"] / row["ours"]["fwd_bwd_ms"], 2)
+            row["speedup_fwd"] = round(row["reference"]["fwd_ms"] / row["ours"]["fwd_ms"], 2)
+        out[name] = row
+        print(f"# {name}: {row}", file=sys.stderr)
     print(json.dumps(out, indent=1))
 
 

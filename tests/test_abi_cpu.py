@@ -78,8 +78,15 @@ def test_python_surface_matches_reference():
         "projmatrix", "sh_degree", "campos", "prefiltered", "debug", "antialiasing")
     for name in ("GaussianRasterizer", "rasterize_gaussians", "_RasterizeGaussians", "cpu_deep_copy_tuple"):
         assert hasattr(dgr, name)
-    with pytest.raises(ImportError):                         # train.py:41-45 probes for it (F4)
-        from diff_gaussian_rasterization import SparseGaussianAdam  # noqa: F401
+    # train.py:41-45 / gaussian_model.py:246-251 probe for it and build it as (params, lr=, eps=); step(visible, N)
+    from diff_gaussian_rasterization import SparseGaussianAdam
+    import inspect
+    assert issubclass(SparseGaussianAdam, torch.optim.Adam)
+    assert list(inspect.signature(SparseGaussianAdam.__init__).parameters) == ["self", "params", "lr", "eps"]
+    assert list(inspect.signature(SparseGaussianAdam.step).parameters)[:3] == ["self", "visibility", "N"]
+    # the fork's positional order of GaussianRasterizer.forward (__init__.py:218) with `dc` appended
+    assert list(inspect.signature(dgr.GaussianRasterizer.forward).parameters) == [
+        "self", "means3D", "means2D", "opacities", "shs", "colors_precomp", "scales", "rotations", "cov3D_precomp", "dc"]
 
 
 def _settings():
