@@ -71,7 +71,10 @@ _workspaces = {}
 
 
 def _workspace(device):
-    key = (device.type, device.index if device.index is not None else torch.cuda.current_device())
+    # one arena per (device, stream): calls on different streams may run concurrently and must not
+    # share scratch; calls on one stream are ordered
+    index = device.index if device.index is not None else torch.cuda.current_device()
+    key = (device.type, index, torch.cuda.current_stream(index).cuda_stream)
     ws = _workspaces.get(key)
     if ws is None:
         ws = _workspaces[key] = _DeviceWorkspace(device)
@@ -79,7 +82,8 @@ def _workspace(device):
 
 
 def workspace_stats(device=None):
-    """{'scratch_bytes', 'regrows', 'last_num_rendered'} for a device (config C5 reporting)."""
+    """{'scratch_bytes', 'regrows', 'last_num_rendered'} of the current stream's arena on a device
+    (config C5 reporting)."""
     device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
     ws = _workspace(device)
     return dict(scratch_bytes=ws.scratch.numel(), regrows=ws.regrows, last_num_rendered=ws.last_R)
