@@ -54,6 +54,14 @@ class GsrBackwardIO(C.Structure):
     ]
 
 
+class GsrSsimParams(C.Structure):
+    _fields_ = [
+        ("img1", _fp), ("img2", _fp),
+        ("B", C.c_int32), ("CH", C.c_int32), ("H", C.c_int32), ("W", C.c_int32),
+        ("C1", C.c_float), ("C2", C.c_float), ("crop", C.c_int32),
+    ]
+
+
 # every symbol include/gsrast.h declares (tests check that the library exports all of them)
 EXPORTS = (
     "gsr_version", "gsr_last_error", "gsr_geom_bytes", "gsr_img_bytes", "gsr_bin_bytes",
@@ -61,6 +69,7 @@ EXPORTS = (
     "gsr_mark_visible", "gsr_debug_sorted_keys", "gsr_debug_state_ptrs", "gsr_flat_grad_floats",
     "gsr_debug_count_work",
     "gsr_profile_enable", "gsr_profile_collect", "gsr_stage_name", "gsr_launch_count", "gsr_adam_update",
+    "gsr_ssim_partials", "gsr_ssim_forward", "gsr_ssim_backward",
 )
 STAGE_COUNT = 9
 
@@ -115,6 +124,13 @@ def load():
     lib.gsr_launch_count.restype = C.c_uint64
     lib.gsr_adam_update.restype = C.c_int
     lib.gsr_adam_update.argtypes = [C.c_void_p] * 5 + [C.c_double] * 6 + [C.c_int64, C.c_int32, C.c_void_p]
+    PS = C.POINTER(GsrSsimParams)
+    lib.gsr_ssim_partials.restype = C.c_int64
+    lib.gsr_ssim_partials.argtypes = [C.c_int32] * 4
+    lib.gsr_ssim_forward.restype = C.c_int
+    lib.gsr_ssim_forward.argtypes = [PS] + [C.c_void_p] * 7
+    lib.gsr_ssim_backward.restype = C.c_int
+    lib.gsr_ssim_backward.argtypes = [PS] + [C.c_void_p] * 7
     _lib = lib
     return lib
 

@@ -165,6 +165,34 @@ int gsr_adam_update(float* param, const float* grad, float* exp_avg, float* exp_
                     const uint8_t* visible, double lr, double beta1, double beta2, double eps,
                     double bias_correction1, double bias_correction2_sqrt, int64_t N, int32_t M, void* stream);
 
+/* Fused SSIM: replaces `fusedssim` / `fusedssim_backward` of the reference's
+ * fused-ssim submodule (submodules/fused-ssim/ssim.h:7-26, ssim.cu:367-444), the D-SSIM term of the
+ * training loss (train.py:155-162).  Images are [B, CH, H, W] fp32, contiguous; 11x11 Gaussian
+ * window (sigma 1.5), zero padding.  crop = 0 is the reference's padding="same"; crop = 5 its
+ * padding="valid" (fused_ssim/__init__.py:13-14,29-31): the mean covers, and a scalar upstream
+ * gradient is spread over, [crop, H-crop) x [crop, W-crop) only. */
+typedef struct GsrSsimParams {
+    const float* img1;   /* the rendered image (receives the gradient) */
+    const float* img2;   /* ground truth */
+    int32_t B, CH, H, W;
+    float C1, C2;        /* 0.01^2, 0.03^2 in the reference (fused_ssim/__init__.py:36-37) */
+    int32_t crop;
+} GsrSsimParams;
+
+/* floats of scratch `partials` that gsr_ssim_forward needs when mean_out != NULL */
+int64_t gsr_ssim_partials(int32_t B, int32_t CH, int32_t H, int32_t W);
+/* ssim_map (nullable): the [B,CH,H,W] map.  dm_*: the three partial-derivative maps the backward
+ * consumes (ssim.cu:268-277) — all three or none (none = the reference's train=False).
+ * mean_out (nullable, device scalar): mean of the (cropped) map, reduced in the same launch in a
+ * fixed order; needs `partials`. */
+int gsr_ssim_forward(const GsrSsimParams* p, float* ssim_map, float* dm_dmu1, float* dm_dsigma1_sq,
+                     float* dm_dsigma12, float* mean_out, float* partials, void* stream);
+/* dL_dimg1 [B,CH,H,W] from either dL_dmap (full-size map gradient, ssim.cu:283-365) or, when
+ * dL_dmap == NULL, the device scalar *dL_dmean = dL/d(mean of the cropped map). */
+int gsr_ssim_backward(const GsrSsimParams* p, const float* dL_dmap, const float* dL_dmean,
+                      const float* dm_dmu1, const float* dm_dsigma1_sq, const float* dm_dsigma12,
+                      float* dL_dimg1, void* stream);
+
 /* Test/inspection hooks (bit-exact parity of the binning stage):
  * rebuild the reference's sorted 64-bit key list (tile<<32 | depth bits) and
  * expose point_list / ranges held in the state buffers.  Device pointers. */

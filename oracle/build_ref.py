@@ -16,7 +16,11 @@ repairs, all of them additive:
       by a comment (backward.cu:285-290), written from the chain rule of
       cov2D = T^T Vrk^T T.  Variant `asis` leaves the truncation.
 
-Usage:  python oracle/build_ref.py [asis] [restored] [--force]
+The reference's fused-ssim submodule is built unmodified the same way
+(`ssim`): submodules/fused-ssim/{ssim.cu, ext.cpp} -> oracle/_ref/fused_ssim/fused_ssim_cuda.so plus its
+own Python wrapper.
+
+Usage:  python oracle/build_ref.py [asis] [restored] [ssim] [--force]
 """
 import os
 import shutil
@@ -158,7 +162,50 @@ def build_variant(variant, force=False):
     return out_so
 
 
+REF_SSIM = "/root/reference/submodules/fused-ssim"
+
+
+def build_fused_ssim(force=False):
+    """The reference's fused-ssim extension, unmodified, for sm_100."""
+    out_dir = os.path.join(OUT_ROOT, "fused_ssim")
+    out_so = os.path.join(out_dir, "fused_ssim_cuda.so")
+    if os.path.exists(out_so) and not force:
+        return out_so
+    if not os.path.isdir(REF_SSIM):
+        raise RuntimeError(f"{REF_SSIM} not present: the reference can only be built in the authoring container")
+    tmp = os.path.join(TMP_ROOT, "fused_ssim")
+    shutil.rmtree(tmp, ignore_errors=True)
+    os.makedirs(tmp)
+    inc, libdir, abi = _torch_paths()
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    common = [nvcc, "-std=c++17", "-O3", "-gencode", "arch=compute_100,code=sm_100", "-Xcompiler", "-fPIC",
+              "-DTORCH_EXTENSION_NAME=fused_ssim_cuda", "-DTORCH_API_INCLUDE_EXTENSION_H",
+              f"-D_GLIBCXX_USE_CXX11_ABI={abi}", "--expt-relaxed-constexpr", "-w",
+              "-I" + REF_SSIM, "-I" + sysconfig.get_paths()["include"]]
+    for i in inc:
+        common += ["-I" + i]
+    objs, procs = [], []
+    for s in ("ssim.cu", "ext.cpp"):                      # compiled where they lie; only objects go to /tmp
+        o = os.path.join(tmp, s + ".o")
+        objs.append(o)
+        extra = ["-x", "cu"] if s.endswith(".cpp") else []
+        procs.append(subprocess.Popen(common + extra + ["-c", os.path.join(REF_SSIM, s), "-o", o], cwd=tmp))
+    for p in procs:
+        if p.wait() != 0:
+            raise RuntimeError("fused-ssim reference compilation failed")
+    os.makedirs(os.path.join(out_dir, "fused_ssim"), exist_ok=True)
+    link = [nvcc, "-shared", "-cudart", "static", "-o", out_so] + objs + \
+           ["-L" + libdir, "-lc10", "-ltorch", "-ltorch_cpu", "-ltorch_python", "-lc10_cuda", "-ltorch_cuda",
+            "-Xlinker", "-rpath," + libdir]
+    subprocess.check_call(link, cwd=tmp)
+    shutil.copy(os.path.join(REF_SSIM, "fused_ssim", "__init__.py"), os.path.join(out_dir, "fused_ssim", "__init__.py"))
+    return out_so
+
+
 if __name__ == "__main__":
-    variants = [a for a in sys.argv[1:] if a in ("asis", "restored")] or ["restored", "asis"]
+    args = [a for a in sys.argv[1:] if not a.startswith("--")]
+    variants = [a for a in args if a in ("asis", "restored")] or ([] if args else ["restored", "asis"])
     for v in variants:
         print(build_variant(v, force="--force" in sys.argv))
+    if "ssim" in args or not args:
+        print(build_fused_ssim(force="--force" in sys.argv))

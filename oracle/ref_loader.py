@@ -36,6 +36,34 @@ def load(variant="restored"):
     return mod
 
 
+def fused_ssim_available():
+    return os.path.exists(os.path.join(_HERE, "_ref", "fused_ssim", "fused_ssim_cuda.so"))
+
+
+def load_fused_ssim():
+    """The reference's fused_ssim package (fused_ssim(), FusedSSIMMap) over its own ssim.cu built for sm_100.
+    Its wrapper does `from fused_ssim_cuda import ...`, so the extension is registered under that name; the
+    package itself is imported under a private name (the drop-in is also called `fused_ssim`)."""
+    if "fused_ssim" in _cache:
+        return _cache["fused_ssim"]
+    d = os.path.join(_HERE, "_ref", "fused_ssim")
+    so = os.path.join(d, "fused_ssim_cuda.so")
+    if not os.path.exists(so):
+        raise RuntimeError("reference fused-ssim build missing: run `python oracle/build_ref.py ssim` "
+                           "in the authoring container (needs /root/reference)")
+    import torch  # noqa: F401
+    spec = importlib.util.spec_from_file_location("fused_ssim_cuda", so)
+    ext = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(ext)
+    sys.modules["fused_ssim_cuda"] = ext
+    spec = importlib.util.spec_from_file_location("_gsref_fused_ssim", os.path.join(d, "fused_ssim", "__init__.py"))
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules["_gsref_fused_ssim"] = mod
+    spec.loader.exec_module(mod)
+    _cache["fused_ssim"] = mod
+    return mod
+
+
 def forward_state(ref, settings, means3D, sh, colors_precomp, opacities, scales, rotations, cov3D_precomp):
     """Calls the reference's native forward directly and decodes its state buffers
     (layout: rasterizer_impl.cu:184-223 fromChunk order, 128-byte aligned `obtain`).

@@ -75,9 +75,11 @@ def fwd_bwd_fns(module, gs, s, dev):
     return fwd, fwdbwd
 
 
-def train_step_fn(module, gs, s, dev, sparse_adam=False):
+def train_step_fn(module, gs, s, dev, sparse_adam=False, ssim=None):
     """C2: the per-iteration work of train.py:143-251 without datasets.
-    sparse_adam: the fork's accelerated branch (separate_sh / dc= keyword, optimizer.step(visible, N))."""
+    sparse_adam: the fork's accelerated branch (separate_sh / dc= keyword, optimizer.step(visible, N)).
+    ssim: a fused_ssim(img1, img2) callable -> the full loss of train.py:155-162,
+    0.8 * L1 + 0.2 * (1 - SSIM), plus the inverse-depth L1 term."""
     P = gs["means3D"].shape[0]
     nnp = torch.nn.Parameter
     xyz = nnp(gs["means3D"].to(dev))
@@ -101,7 +103,11 @@ def train_step_fn(module, gs, s, dev, sparse_adam=False):
         kw = dict(dc=f_dc, shs=f_rest) if sparse_adam else dict(shs=torch.cat((f_dc, f_rest), dim=1))
         color, radii, invd = rast(means3D=xyz, means2D=m2, opacities=torch.sigmoid(opacity),
                                   scales=torch.exp(scaling), rotations=torch.nn.functional.normalize(rotation), **kw)
-        loss = (color - target).abs().mean() + 0.1 * (invd - target_d).abs().mean()
+        if ssim is None:
+            loss = (color - target).abs().mean() + 0.1 * (invd - target_d).abs().mean()
+        else:
+            loss = 0.8 * (color - target).abs().mean() + 0.2 * (1.0 - ssim(color.unsqueeze(0), target.unsqueeze(0))) \
+                + 0.1 * (invd - target_d).abs().mean()
         loss.backward()
         if sparse_adam:
             opt.step(radii > 0, radii.shape[0])               # train.py:240-247
@@ -122,6 +128,14 @@ def main():
         mods["reference"] = ref_loader.load("restored")
     except Exception as ex:  # noqa: BLE001
         print(f"# reference CUDA build unavailable: {ex}", file=sys.stderr)
+    ssim_of = {}
+    try:
+        import fused_ssim
+        ssim_of["ours"] = fused_ssim.fused_ssim
+        from oracle import ref_loader
+        ssim_of["reference"] = ref_loader.load_fused_ssim().fused_ssim
+    except Exception as ex:  # noqa: BLE001
+        print(f"# fused-ssim unavailable: {ex}", file=sys.stderr)
     out = {}
     # C5: densification stress (ours): growing P, dynamic workspace, sort bit-width via resolution
     c3 = synthetic.CONFIGS["C3"]
@@ -149,6 +163,11 @@ def main():
                 r["train_step_ms"] = round(timeit(train_step_fn(m, gs, s, dev)), 3)
                 if hasattr(m, "SparseGaussianAdam"):
                     r["train_step_sparse_adam_ms"] = round(timeit(train_step_fn(m, gs, s, dev, sparse_adam=True)), 3)
+                if mname in ssim_of:
+                    # the full loss of train.py:155-162 with each side's fastest shipped pieces:
+                    # ours = SparseGaussianAdam + our fused SSIM, reference = torch Adam + its own fused-ssim CUDA
+                    r["train_step_ssim_ms"] = round(timeit(train_step_fn(
+                        m, gs, s, dev, sparse_adam=hasattr(m, "SparseGaussianAdam"), ssim=ssim_of[mname])), 3)
             row[mname] = r
             torch.cuda.empty_cache()
         if "reference" in row:

@@ -40,7 +40,8 @@ def test_struct_layouts_match_header():
     from gaussian_splatting_b200 import _lib
     h = _header()
     for name, cls in (("GsrParams", _lib.GsrParams), ("GsrBuffers", _lib.GsrBuffers),
-                      ("GsrForwardOut", _lib.GsrForwardOut), ("GsrBackwardIO", _lib.GsrBackwardIO)):
+                      ("GsrForwardOut", _lib.GsrForwardOut), ("GsrBackwardIO", _lib.GsrBackwardIO),
+                      ("GsrSsimParams", _lib.GsrSsimParams)):
         body = re.search(r"typedef struct %s \{(.*?)\} %s;" % (name, name), h, re.S).group(1)
         body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
         fields = []
@@ -55,6 +56,7 @@ def test_struct_layouts_match_header():
         assert fields == [f[0] for f in cls._fields_], name
     assert C.sizeof(_lib.GsrParams) == 12 * 4 + 11 * 8
     assert C.sizeof(_lib.GsrBuffers) == 9 * 8
+    assert C.sizeof(_lib.GsrSsimParams) == 2 * 8 + 8 * 4        # 7 ints/floats + tail padding
 
 
 def test_workspace_size_queries(lib):
@@ -87,6 +89,27 @@ def test_python_surface_matches_reference():
     # the fork's positional order of GaussianRasterizer.forward (__init__.py:218) with `dc` appended
     assert list(inspect.signature(dgr.GaussianRasterizer.forward).parameters) == [
         "self", "means3D", "means2D", "opacities", "shs", "colors_precomp", "scales", "rotations", "cov3D_precomp", "dc"]
+
+
+def test_fused_ssim_surface_matches_reference():
+    """submodules/fused-ssim/fused_ssim/__init__.py: names, signatures, padding modes, no CPU path."""
+    import inspect
+    import fused_ssim as fs
+    assert fs.allowed_padding == ["same", "valid"]
+    assert list(inspect.signature(fs.fused_ssim).parameters) == ["img1", "img2", "padding", "train"]
+    assert inspect.signature(fs.fused_ssim).parameters["padding"].default == "same"
+    assert inspect.signature(fs.fused_ssim).parameters["train"].default is True
+    assert list(inspect.signature(fs.FusedSSIMMap.forward).parameters) == [
+        "ctx", "C1", "C2", "img1", "img2", "padding", "train"]
+    with pytest.raises(AssertionError):
+        fs.fused_ssim(torch.zeros(1, 3, 16, 16), torch.zeros(1, 3, 16, 16), padding="reflect")
+    with pytest.raises(RuntimeError, match="CUDA"):
+        fs.fused_ssim(torch.zeros(1, 3, 16, 16), torch.zeros(1, 3, 16, 16))
+
+
+def test_ssim_scratch_query(lib):
+    assert lib.gsr_ssim_partials(1, 3, 1080, 1920) == 3 * 34 * 60
+    assert lib.gsr_ssim_partials(2, 3, 1, 1) == 6 and lib.gsr_ssim_partials(0, 3, 8, 8) == 0
 
 
 def _settings():
@@ -129,7 +152,8 @@ def test_no_cpu_fallback():
 
 
 def test_product_never_touches_the_oracle():
-    pkg_dirs = [os.path.join(ROOT, "gaussian_splatting_b200"), os.path.join(ROOT, "diff_gaussian_rasterization")]
+    pkg_dirs = [os.path.join(ROOT, "gaussian_splatting_b200"), os.path.join(ROOT, "diff_gaussian_rasterization"),
+                os.path.join(ROOT, "fused_ssim")]
     for d in pkg_dirs:
         for base, _, files in os.walk(d):
             for f in files:
