@@ -32,6 +32,9 @@ constexpr int SS_R = 5;                  // window radius
 constexpr int SS_IN = SS_T + 2 * SS_R;   // 42 staged rows / columns
 constexpr int SS_PITCH = 44;             // floats per staged row (16 B aligned rows, 2 pad columns)
 constexpr int SS_THREADS = 256;
+#ifndef SS_MIN_BLOCKS
+#define SS_MIN_BLOCKS 5                   // 5 x 41.7 KB of shared memory, <= 51 registers
+#endif
 
 // fp32 taps of gaussian(11, 1.5) / sum (loss_utils.py:42-44)
 #define SS_G(k)                                                                                          \
@@ -87,7 +90,7 @@ __device__ __forceinline__ float rcp_newton(float x) {
 
 // TRAIN: write the three partial-derivative maps.  `map` and `partial` are optional (nullptr).
 template <bool TRAIN>
-__global__ void __launch_bounds__(SS_THREADS, 4)
+__global__ void __launch_bounds__(SS_THREADS, SS_MIN_BLOCKS)
 ssim_fwd_kernel(const float* __restrict__ img1, const float* __restrict__ img2, float* __restrict__ map,
                 float* __restrict__ dm_dmu1, float* __restrict__ dm_dsigma1_sq, float* __restrict__ dm_dsigma12,
                 float* __restrict__ partial, int H, int W, float C1, float C2, int crop) {
@@ -214,7 +217,7 @@ __global__ void __launch_bounds__(1024) ssim_mean_kernel(const float* __restrict
 // (ssim.cu:309-358).  SCALAR: dL_dmap is the constant  *dL_dmean * inv_count  inside the crop window
 // and zero outside — the gradient of map[crop].mean() — so no dL_dmap tensor is read.
 template <bool SCALAR>
-__global__ void __launch_bounds__(SS_THREADS, 4)
+__global__ void __launch_bounds__(SS_THREADS, SS_MIN_BLOCKS)
 ssim_bwd_kernel(const float* __restrict__ img1, const float* __restrict__ img2, const float* __restrict__ dL_dmap,
                 const float* __restrict__ dL_dmean, float inv_count, const float* __restrict__ dm_dmu1,
                 const float* __restrict__ dm_dsigma1_sq, const float* __restrict__ dm_dsigma12,
@@ -287,6 +290,22 @@ ssim_bwd_kernel(const float* __restrict__ img1, const float* __restrict__ img2, 
     }
 }
 
+// several CTAs per SM only fit with the large shared-memory carveout
+template <typename K>
+static void ssim_prefer_smem(K kernel) {
+    cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+}
+static void ssim_init_once() {
+    static const bool done = [] {
+        ssim_prefer_smem(ssim_fwd_kernel<true>);
+        ssim_prefer_smem(ssim_fwd_kernel<false>);
+        ssim_prefer_smem(ssim_bwd_kernel<true>);
+        ssim_prefer_smem(ssim_bwd_kernel<false>);
+        return true;
+    }();
+    (void)done;
+}
+
 static long long ssim_tiles(int B, int CH, int H, int W) {
     return (long long)B * CH * ((H + SS_T - 1) / SS_T) * ((W + SS_T - 1) / SS_T);
 }
@@ -324,6 +343,7 @@ extern "C" int gsr_ssim_forward(const GsrSsimParams* p, float* ssim_map, float* 
         return GSR_ERR_INVALID_ARG;
     }
     cudaStream_t st = (cudaStream_t)stream;
+    ssim_init_once();
     const long long tiles = ssim_tiles(p->B, p->CH, p->H, p->W);
     if (tiles > 0) {
         const dim3 grid((p->W + SS_T - 1) / SS_T, (p->H + SS_T - 1) / SS_T, p->B * p->CH);
@@ -357,6 +377,7 @@ extern "C" int gsr_ssim_backward(const GsrSsimParams* p, const float* dL_dmap, c
         return GSR_ERR_INVALID_ARG;
     }
     cudaStream_t st = (cudaStream_t)stream;
+    ssim_init_once();
     const dim3 grid((p->W + SS_T - 1) / SS_T, (p->H + SS_T - 1) / SS_T, p->B * p->CH);
     if (dL_dmap) {
         GSR_LAUNCH(ssim_bwd_kernel<false>, grid, SS_THREADS, 0, st, p->img1, p->img2, dL_dmap, dL_dmean, 0.f, dm_dmu1,

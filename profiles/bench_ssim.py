@@ -49,14 +49,18 @@ def main():
     torch.cuda.set_device(dev)
     import fused_ssim as ours
     impls = {"ours": ours.fused_ssim}
+    only_ours = "--ours-only" in sys.argv          # A/B runs of kernel variants (GSR_LIB=...)
     try:
+        if only_ours:
+            raise RuntimeError("skipped (--ours-only)")
         from oracle import ref_loader
         impls["reference_cuda"] = ref_loader.load_fused_ssim().fused_ssim
     except Exception as ex:  # noqa: BLE001
         print(f"# reference fused-ssim unavailable: {ex}", file=sys.stderr)
     from oracle import ssim_ref
     g = torch.from_numpy(ssim_ref.taps()).to(dev)
-    impls["conv2d"] = conv_ssim((g[:, None] @ g[None, :])[None, None])
+    if not only_ours:
+        impls["conv2d"] = conv_ssim((g[:, None] @ g[None, :])[None, None])
     peak = 6552.0
     try:
         peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
@@ -88,7 +92,8 @@ def main():
             row[name] = r
         if "reference_cuda" in row:
             row["speedup_vs_reference_cuda"] = round(row["reference_cuda"]["fwd_bwd_ms"] / row["ours"]["fwd_bwd_ms"], 2)
-        row["speedup_vs_conv2d"] = round(row["conv2d"]["fwd_bwd_ms"] / row["ours"]["fwd_bwd_ms"], 2)
+        if "conv2d" in row:
+            row["speedup_vs_conv2d"] = round(row["conv2d"]["fwd_bwd_ms"] / row["ours"]["fwd_bwd_ms"], 2)
         out["shapes"]["x".join(map(str, shape))] = row
         print(f"# {shape}: {row}", file=sys.stderr)
         del img1, img2
