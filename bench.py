@@ -50,6 +50,8 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="C3", help="C1|C2|C3|C4 (SURVEY.md §8d) or C3 with --P override")
     ap.add_argument("--P", type=int, default=None, help="override the Gaussian count")
+    ap.add_argument("--yaw-step", type=float, default=45.0,
+                    help="rank r looks at the scene from yaw r * step degrees (0: every rank has the same camera; diagnostic)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--ref-variant", default="restored", choices=["restored", "asis"])
@@ -128,7 +130,7 @@ def build_workload(args, rank, device):
     from gaussian_splatting_b200 import synthetic
     cfg = synthetic.CONFIGS[args.workload]
     P = args.P or cfg.P
-    gs, cam = synthetic.make_scene(cfg, P=P, yaw_deg=45.0 * rank)
+    gs, cam = synthetic.make_scene(cfg, P=P, yaw_deg=args.yaw_step * rank)
     W, H = cfg.W, cfg.H
     g = torch.Generator().manual_seed(1000 + cfg.seed)
     target, target_d = synthetic.make_targets(W, H, cfg.seed)
@@ -389,8 +391,12 @@ def run_gpu_arm(args, module, impl, rank, world, local):
         reduce_mode = "nccl all-reduce of the packed gradients"
         if impl == "ours" and args.reduce == "fused" and FusedGradientReducer.available():
             try:
-                FusedGradientReducer().install()
-                reduce_mode = "fused: multimem.red into NVLink-multicast buffers inside the backward kernel"
+                red = FusedGradientReducer().install()
+                reduce_mode = ("fused: factored exchange (64 B per contributing Gaussian via multimem.red into NVLink-multicast "
+                               "buffers inside the backward kernel, SH gradients rebuilt locally per sender camera)"
+                               if red.factored else
+                               f"fused: multimem.red of all gradients into NVLink-multicast buffers inside the backward kernel, "
+                               f"{red.bands} band(s)")
             except Exception as ex:      # noqa: BLE001
                 reduce_mode += f" (fused unavailable: {ex})"
         if not reduce_mode.startswith("fused"):

@@ -51,6 +51,7 @@ class GsrBackwardIO(C.Structure):
         ("dL_dmeans3D", _fp), ("dL_dmeans2D", _fp), ("dL_dopacity", _fp), ("dL_dcolors", _fp),
         ("dL_dcov3D", _fp), ("dL_dsh", _fp), ("dL_dscales", _fp), ("dL_drotations", _fp),
         ("multimem_reduce", C.c_int32), ("reserved1", C.c_int32),
+        ("xchg_records", _fp), ("xchg_rgb", _fp), ("xchg_campos", _fp),
     ]
 
 
@@ -69,7 +70,7 @@ EXPORTS = (
     "gsr_mark_visible", "gsr_debug_sorted_keys", "gsr_debug_state_ptrs", "gsr_flat_grad_floats",
     "gsr_debug_count_work",
     "gsr_profile_enable", "gsr_profile_collect", "gsr_stage_name", "gsr_launch_count", "gsr_adam_update",
-    "gsr_ssim_partials", "gsr_ssim_forward", "gsr_ssim_backward",
+    "gsr_ssim_partials", "gsr_ssim_forward", "gsr_ssim_backward", "gsr_exchange_expand",
 )
 STAGE_COUNT = 9
 
@@ -124,6 +125,8 @@ def load():
     lib.gsr_launch_count.restype = C.c_uint64
     lib.gsr_adam_update.restype = C.c_int
     lib.gsr_adam_update.argtypes = [C.c_void_p] * 5 + [C.c_double] * 6 + [C.c_int64, C.c_int32, C.c_void_p]
+    lib.gsr_exchange_expand.restype = C.c_int
+    lib.gsr_exchange_expand.argtypes = [PP, C.c_int32] + [C.c_void_p] * 9
     PS = C.POINTER(GsrSsimParams)
     lib.gsr_ssim_partials.restype = C.c_int64
     lib.gsr_ssim_partials.argtypes = [C.c_int32] * 4

@@ -250,7 +250,17 @@ int gsr_backward(const GsrParams* p, const GsrBuffers* buf, int64_t R, const int
     Scratch s = Scratch::carve(buf->scratch, p->P, (size_t)R, nullptr);
     const int gy = (p->H + TILE_Y - 1) / TILE_Y;
     const bool have_invdepth = io->dL_dout_invdepth != nullptr;
-    int bands = io->multimem_reduce ? (io->reserved1 > 0 ? io->reserved1 : 1) : 1;
+    const bool fact = io->xchg_records != nullptr;
+    if (fact) {
+        const auto misaligned = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) != 0; };
+        if (!io->xchg_rgb || !io->xchg_campos || !p->shs || !p->scales || !p->rotations || p->colors_precomp ||
+            p->cov3D_precomp || misaligned(io->xchg_records) || misaligned(io->xchg_rgb) || misaligned(io->xchg_campos)) {
+            set_error("factored exchange needs SH + scale/rotation inputs and three 16-byte aligned xchg_* buffers");
+            return GSR_ERR_INVALID_ARG;
+        }
+    }
+    // the factored exchange moves ~4x fewer NVLink bytes: no band pipelining needed
+    int bands = (io->multimem_reduce && !fact) ? (io->reserved1 > 0 ? io->reserved1 : 1) : 1;
     if (bands > gy) bands = gy;
     if (bands > MAX_BANDS) bands = MAX_BANDS;
     SideStream* side = bands > 1 ? side_stream() : nullptr;

@@ -67,6 +67,8 @@ __device__ __forceinline__ float3 dnormvdv(float3 v, float3 dv) {
 // SH backward for one Gaussian (backward.cu:12-146).  `row` is this lane's padded row in
 // shared memory holding the coefficients on entry (first 3*(deg+1)^2 floats valid) and the
 // coefficient gradients on exit (all `rowlen` floats written).  Returns dL/d(mean).
+// STORE = false (factored exchange): only dL/d(mean) is needed, the row is left untouched.
+template <bool STORE = true>
 __device__ __forceinline__ float3 sh_backward(float* row, int rowlen, int deg, float3 dir_orig,
                                               const float dL_dRGB[3]) {
     const float len = sqrtf(dir_orig.x * dir_orig.x + dir_orig.y * dir_orig.y + dir_orig.z * dir_orig.z);
@@ -138,15 +140,17 @@ __device__ __forceinline__ float3 sh_backward(float* row, int rowlen, int deg, f
         }
     }
 #undef SHC
-    const int ncoef = (deg + 1) * (deg + 1);
-    const int nrow = rowlen / 3;
+    if (STORE) {
+        const int ncoef = (deg + 1) * (deg + 1);
+        const int nrow = rowlen / 3;
 #pragma unroll
-    for (int k = 0; k < 16; k++) {
-        if (k < nrow) {
-            const float wk = k < ncoef ? w[k] : 0.f;
-            row[k * 3 + 0] = wk * dL_dRGB[0];
-            row[k * 3 + 1] = wk * dL_dRGB[1];
-            row[k * 3 + 2] = wk * dL_dRGB[2];
+        for (int k = 0; k < 16; k++) {
+            if (k < nrow) {
+                const float wk = k < ncoef ? w[k] : 0.f;
+                row[k * 3 + 0] = wk * dL_dRGB[0];
+                row[k * 3 + 1] = wk * dL_dRGB[1];
+                row[k * 3 + 2] = wk * dL_dRGB[2];
+            }
         }
     }
     float3 dL_ddir = {dx[0] * dL_dRGB[0] + dx[1] * dL_dRGB[1] + dx[2] * dL_dRGB[2],
@@ -156,6 +160,7 @@ __device__ __forceinline__ float3 sh_backward(float* row, int rowlen, int deg, f
 }
 
 // Vector path: the row is pulled into registers with LDS.128, the gradients go back with STS.128.
+template <bool STORE = true>
 __device__ __forceinline__ float3 sh_backward_vec(float* row, int rowlen, int deg, float3 dir_orig,
                                                   const float dL_dRGB[3]) {
     float sh[PB_ROW];
@@ -165,11 +170,13 @@ __device__ __forceinline__ float3 sh_backward_vec(float* row, int rowlen, int de
         const float4 v = row4[m];
         sh[4 * m] = v.x; sh[4 * m + 1] = v.y; sh[4 * m + 2] = v.z; sh[4 * m + 3] = v.w;
     }
-    const float3 r = sh_backward(sh, rowlen, deg, dir_orig, dL_dRGB);
-    const int n4 = rowlen >> 2;
+    const float3 r = sh_backward<STORE>(sh, rowlen, deg, dir_orig, dL_dRGB);
+    if (STORE) {
+        const int n4 = rowlen >> 2;
 #pragma unroll
-    for (int m = 0; m < PB_ROW / 4; m++)
-        if (m < n4) row4[m] = make_float4(sh[4 * m], sh[4 * m + 1], sh[4 * m + 2], sh[4 * m + 3]);
+        for (int m = 0; m < PB_ROW / 4; m++)
+            if (m < n4) row4[m] = make_float4(sh[4 * m], sh[4 * m + 1], sh[4 * m + 2], sh[4 * m + 3]);
+    }
     return r;
 }
 
@@ -384,6 +391,52 @@ preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord*
         if (p.scales != nullptr) cov3D_backward(sc, p.scale_modifier, rot, dL_dcov, &dL_dscale, &dL_drot);
     }
 
+    // ---- factored exchange: publish {mean, opacity, scale, rotation} gradients as one 48 B
+    // record (summed across ranks) and the clamp-masked dL_dRGB in this rank's slot; dL_dsh is rebuilt
+    // by every receiver (exchange.cu).  16 B multimem operations only; culled rows are not touched.
+    if (io.xchg_records != nullptr) {
+        float dL_dRGB[3];
+#pragma unroll
+        for (int c = 0; c < 3; c++) dL_dRGB[c] = ((clamped_bits >> c) & 1) ? 0.f : dL_dcolor[c];
+        const float3 dir_orig = {mean.x - s_cam[0], mean.y - s_cam[1], mean.z - s_cam[2]};
+        float* ws = sh_smem[warp];
+        if (VEC) {
+            if (vis_mask != 0) mbar_wait(smem_u32(&s_bar[warp]), 0);
+            if (visible) {
+                const float3 dm = sh_backward_vec<false>(ws + lane * sh_row, sh_row, p.D, dir_orig, dL_dRGB);
+                dL_dmean.x += dm.x; dL_dmean.y += dm.y; dL_dmean.z += dm.z;
+            }
+        } else {
+            const int L = 3 * (p.D + 1) * (p.D + 1);
+            if (vis_mask != 0) {
+                const float* src = p.shs + (size_t)warp_base * sh_row;
+                for (int i = lane; i < 32 * L; i += 32) {
+                    int g = i / L, k = i - g * L;
+                    if ((vis_mask >> g) & 1u) ws[g * PB_STRIDE_SCALAR + k] = __ldg(src + (size_t)g * sh_row + k);
+                }
+            }
+            __syncwarp();
+            if (visible) {
+                const float3 dm = sh_backward<false>(ws + lane * PB_STRIDE_SCALAR, sh_row, p.D, dir_orig, dL_dRGB);
+                dL_dmean.x += dm.x; dL_dmean.y += dm.y; dL_dmean.z += dm.z;
+            }
+        }
+        if (blockIdx.x == 0 && threadIdx.x == 0)
+            out4<MM>(io.xchg_campos, make_float4(s_cam[0], s_cam[1], s_cam[2], 1.f));
+        if (!mine) return;
+        if (io.dL_dmeans2D) {
+            io.dL_dmeans2D[3 * idx] = dL_dmean2D.x; io.dL_dmeans2D[3 * idx + 1] = dL_dmean2D.y; io.dL_dmeans2D[3 * idx + 2] = 0.f;
+        }
+        if (visible) {
+            float* r = io.xchg_records + 12 * (size_t)idx;
+            out4<MM>(r, make_float4(dL_dmean.x, dL_dmean.y, dL_dmean.z, dL_dopacity));
+            out4<MM>(r + 4, make_float4(dL_dscale.x, dL_dscale.y, dL_dscale.z, 0.f));
+            out4<MM>(r + 8, dL_drot);
+            out4<MM>(io.xchg_rgb + 4 * (size_t)idx, make_float4(dL_dRGB[0], dL_dRGB[1], dL_dRGB[2], 0.f));
+        }
+        return;
+    }
+
     // ---- SH backward; dL_dsh rows leave coalesced (bulk store or transposed scalar stores) ----
     if (p.shs != nullptr && io.dL_dsh != nullptr) {
         const int L = 3 * (p.D + 1) * (p.D + 1);
@@ -571,8 +624,10 @@ int launch_preprocess_backward(const GsrParams& p, GeomState g, Scratch s, const
     const uint32_t* blist = band >= 0 ? s.band_list : nullptr;
     StageTimer tm(GSR_STAGE_PREPROCESS_BWD, st);
     // vector path: SH rows are whole float4s (M in {4, 8, 12, 16}) and 16 B aligned
-    const bool vec = p.shs != nullptr && io.dL_dsh != nullptr && (p.M & 3) == 0 &&
-                     (reinterpret_cast<uintptr_t>(p.shs) & 15) == 0 && (reinterpret_cast<uintptr_t>(io.dL_dsh) & 15) == 0;
+    const bool fact = io.xchg_records != nullptr;
+    const bool vec = p.shs != nullptr && (fact || io.dL_dsh != nullptr) && (p.M & 3) == 0 &&
+                     (reinterpret_cast<uintptr_t>(p.shs) & 15) == 0 &&
+                     (fact || (reinterpret_cast<uintptr_t>(io.dL_dsh) & 15) == 0);
     const bool mm = io.multimem_reduce != 0;
 #define PB_LAUNCH(V, M) GSR_LAUNCH((preprocess_bwd_kernel<V, M>), blocks, PB_THREADS, 0, st, p, focal_x, focal_y, g.rec, \
                                    radii, s.acc, have_invdepth, io, blist, s.band_ctl, band)

@@ -223,6 +223,19 @@ def _inspect_state(lib, p, buf, R, geom, binb, img, stream):
                 work_counts=counts)
 
 
+def _present(t):
+    return t is not None and t.numel() > 0
+
+
+def _grad_layout(P, M, colors_precomp, cov3Ds_precomp, sh, scales, rotations):
+    """Names and shapes of the per-Gaussian gradient tensors the backward kernel writes."""
+    want = [("means3D", (P, 3), True), ("opacity", (P, 1), True),
+            ("colors", (P, 3), _present(colors_precomp)), ("cov3D", (P, 6), _present(cov3Ds_precomp)),
+            ("sh", (P, M, 3), _present(sh)), ("scales", (P, 3), _present(scales)),
+            ("rotations", (P, 4), _present(rotations))]
+    return [n for n, _, on in want if on], [shp for _, shp, on in want if on]
+
+
 def _backward_native(rs, means3D, radii, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
                      grad_out_color, grad_out_depth, sh, geom, R, binb, img):
     """Role of _C.rasterize_gaussians_backward (rasterize_points.cu:149-248).
@@ -268,15 +281,11 @@ def _backward_native(rs, means3D, radii, colors_precomp, opacities, scales, rota
         buf.num_rendered_host = ws.pinned.data_ptr()
 
         dL_dmeans2D = torch.empty((P, 3), **f32)
-        want = [("means3D", (P, 3), True), ("opacity", (P, 1), True),
-                ("colors", (P, 3), colors_precomp is not None), ("cov3D", (P, 6), cov3Ds_precomp is not None),
-                ("sh", (P, M, 3), sh_c is not None), ("scales", (P, 3), scales is not None),
-                ("rotations", (P, 4), rotations is not None)]
-        names = [n for n, _, on in want if on]
-        shapes = [shp for _, shp, on in want if on]
+        names, shapes = _grad_layout(P, M, colors_precomp, cov3Ds_precomp, sh_c, scales, rotations)
         red = _gradient_reducer
-        if red is None:
-            # every output is fully written by the fused backward kernel: no zero fills
+        exchange = red is not None and hasattr(red, "use_exchange") and red.use_exchange(names)
+        if red is None or exchange:
+            # every output is fully written (by the fused backward kernel, or by the expand pass): no zero fills
             outs = {n: torch.empty(shp, **f32) for n, shp in zip(names, shapes)}
             addr = {n: t.data_ptr() for n, t in outs.items()}
         else:
@@ -285,15 +294,32 @@ def _backward_native(rs, means3D, radii, colors_precomp, opacities, scales, rota
             views, addrs = red.buffers(shapes, device)
             outs = dict(zip(names, views))
             addr = dict(zip(names, addrs))
+        if exchange:
+            # factored exchange: the kernel publishes 64 B per contributing Gaussian through the multicast
+            # address; after the rank barrier the expand pass rebuilds the dense, summed gradients locally
+            local, mcast = red.exchange_buffers(P, device)
             red.begin()
-        io = GsrBackwardIO(grad_out_color.data_ptr(), _ptr(grad_out_depth), addr["means3D"],
-                           dL_dmeans2D.data_ptr(), addr["opacity"], addr.get("colors"), addr.get("cov3D"),
-                           addr.get("sh"), addr.get("scales"), addr.get("rotations"),
-                           0 if red is None else 1, 0 if red is None else int(getattr(red, "bands", 0)))
-        _lib.check(lib.gsr_backward(C.byref(p), C.byref(buf), R, radii.data_ptr(), C.byref(io),
-                                    stream.cuda_stream))
-        if red is not None:
+            io = GsrBackwardIO(grad_out_color.data_ptr(), _ptr(grad_out_depth), None, dL_dmeans2D.data_ptr(),
+                               None, None, None, None, None, None, int(getattr(red, "multicast", True)), 0,
+                               mcast["records"], mcast["rgb"], mcast["campos"])
+            _lib.check(lib.gsr_backward(C.byref(p), C.byref(buf), R, radii.data_ptr(), C.byref(io),
+                                        stream.cuda_stream))
             red.end()
+            _lib.check(lib.gsr_exchange_expand(C.byref(p), red.world, local["records"], local["rgb"], local["campos"],
+                                               addr["means3D"], addr["opacity"], addr["sh"], addr["scales"],
+                                               addr["rotations"], stream.cuda_stream))
+        else:
+            if red is not None:
+                red.begin()
+            io = GsrBackwardIO(grad_out_color.data_ptr(), _ptr(grad_out_depth), addr["means3D"],
+                               dL_dmeans2D.data_ptr(), addr["opacity"], addr.get("colors"), addr.get("cov3D"),
+                               addr.get("sh"), addr.get("scales"), addr.get("rotations"),
+                               0 if red is None else 1, 0 if red is None else int(getattr(red, "bands", 0)),
+                               None, None, None)
+            _lib.check(lib.gsr_backward(C.byref(p), C.byref(buf), R, radii.data_ptr(), C.byref(io),
+                                        stream.cuda_stream))
+            if red is not None:
+                red.end()
         dL_dmeans3D, dL_dopacity = outs["means3D"], outs["opacity"]
         dL_dcolors, dL_dcov3D, dL_dsh = outs.get("colors"), outs.get("cov3D"), outs.get("sh")
         dL_dscales, dL_drotations = outs.get("scales"), outs.get("rotations")
@@ -310,6 +336,13 @@ class _RasterizeGaussians(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
                 raster_settings):
+        red = _gradient_reducer
+        if red is not None and any(ctx.needs_input_grad) and means3D.shape[0] > 0 and hasattr(red, "prepare"):
+            # view-parallel: clear the symmetric gradient buffer + rank barrier overlap the forward
+            M = sh.shape[1] if _present(sh) else 0
+            names, shapes = _grad_layout(means3D.shape[0], M, colors_precomp, cov3Ds_precomp, sh, scales, rotations)
+            xchg = hasattr(red, "use_exchange") and red.use_exchange(names)
+            red.prepare(shapes, means3D.device, exchange_P=means3D.shape[0] if xchg else None)
         num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, invdepths = _forward_native(
             raster_settings, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp)
         ctx.raster_settings = raster_settings

@@ -6,6 +6,7 @@ The reference has no distributed code at all; this is the exchange step north_st
 Densification statistics are reduced as per-view values because the reference sums per-view
 norms (scene/gaussian_model.py:643-654) and takes a running max of radii (train.py:212).
 """
+import os
 from typing import List, Optional, Sequence
 
 import torch
@@ -101,7 +102,8 @@ class FusedGradientReducer:
 
     Contract (same as any gradient bucket that is reused): every rank calls backward the same number
     of times, and the gradients returned by one backward are consumed (optimizer step / copy /
-    `grad = None`) before the next backward on this device.  dL_dmeans2D (per-view densification
+    `grad = None`) before the next differentiable forward on this device (the replica is cleared
+    during that forward).  dL_dmeans2D (per-view densification
     statistic) is never reduced.
 
     PyTorch is plumbing here: symmetric allocation + rendezvous + stream barriers come from
@@ -113,7 +115,6 @@ class FusedGradientReducer:
     def __init__(self, group: Optional[dist.ProcessGroup] = None, bands: int = 0):
         """bands: tile-row bands of the blend backward pipelined against the NVLink-bound per-Gaussian
         kernel (0 = library default, 1 = no pipelining)."""
-        import os
         import torch.distributed._symmetric_memory as symm_mem
         self.bands = int(os.environ.get("GSR_REDUCE_BANDS", bands))
         if self.bands <= 0:
@@ -127,6 +128,13 @@ class FusedGradientReducer:
         self.hdl = None
         self.key = None
         self.bytes_reduced = 0
+        # GSR_REDUCE_EARLY=0: zero + barrier at the start of the backward instead of during the forward
+        self.early = os.environ.get("GSR_REDUCE_EARLY", "1") != "0"
+        # GSR_REDUCE_FACTORED=0: all-reduce the full SH gradients (236 B / Gaussian) instead of the factored
+        # exchange (64 B / Gaussian + a local expand pass)
+        self.factored = os.environ.get("GSR_REDUCE_FACTORED", "1") != "0"
+        self._side = self._ready = None
+        self._prepared = False
 
     @staticmethod
     def available() -> bool:
@@ -166,8 +174,64 @@ class FusedGradientReducer:
             addrs.append(self.hdl.multicast_ptr + 4 * off)
         return views, addrs
 
+    EXCHANGE_NAMES = ["means3D", "opacity", "sh", "scales", "rotations"]
+
+    def use_exchange(self, names) -> bool:
+        """Factored exchange (csrc/exchange.cu): SH + scale/rotation inputs, i.e. the training configuration."""
+        return self.factored and list(names) == self.EXCHANGE_NAMES
+
+    def exchange_buffers(self, P, device):
+        """Symmetric buffer of the factored exchange: records [P][12] | rgb [world][P][4] | campos [world][4].
+        Returns (local addresses, multicast addresses) as dicts with keys records / rgb / campos; the
+        multicast rgb / campos addresses point at THIS rank's slot.  (Re)allocates + rendezvous (a
+        collective) when P changes, e.g. after densification."""
+        key = ("xchg", int(P), str(device))
+        if key != self.key:
+            al = lambda n: (n + self.ALIGN - 1) // self.ALIGN * self.ALIGN  # noqa: E731
+            o_rgb = al(12 * P)
+            o_cam = o_rgb + al(4 * P * self.world)
+            total = o_cam + al(4 * self.world)
+            self.flat = self._symm_mem.empty(total, dtype=torch.float32, device=device)
+            self.hdl = self._symm_mem.rendezvous(self.flat, self.group.group_name)
+            if not self.hdl.multicast_ptr:
+                raise RuntimeError("NVLink multicast (NVLS) is not available for this group: use FlatGradients")
+            self.key, self.offs, self.total = key, [0, o_rgb, o_cam], total
+        rank = dist.get_rank(self.group)
+        base, mc = self.flat.data_ptr(), self.hdl.multicast_ptr
+        o_rec, o_rgb, o_cam = self.offs
+        local = dict(records=base + 4 * o_rec, rgb=base + 4 * o_rgb, campos=base + 4 * o_cam)
+        mcast = dict(records=mc + 4 * o_rec, rgb=mc + 4 * (o_rgb + 4 * P * rank), campos=mc + 4 * (o_cam + 4 * rank))
+        return local, mcast
+
+    def prepare(self, shapes, device, exchange_P=None):
+        """Called from the rasterizer's forward (grad mode): zero this rank's replica and run the
+        all-ranks-zeroed barrier on a side stream, overlapped with the forward pass, so the backward
+        starts reducing at once.  Ordered after everything already enqueued on the current stream,
+        i.e. after the consumers of the previous step's gradients."""
+        if not self.early:
+            return
+        if exchange_P is not None:
+            self.exchange_buffers(exchange_P, device)
+        else:
+            self.buffers(shapes, device)
+        main = torch.cuda.current_stream(device)
+        if self._side is None:
+            self._side = torch.cuda.Stream(device=device)
+            self._ready = torch.cuda.Event()
+        self._side.wait_stream(main)
+        with torch.cuda.stream(self._side):
+            self.flat.zero_()
+            self.hdl.barrier(channel=0)
+            self._ready.record(self._side)
+        self._prepared = True
+
     def begin(self):
-        """Zero this rank's replica and wait until every rank has done so (on the current stream)."""
+        """Zero this rank's replica and wait until every rank has done so (on the current stream);
+        already done during the forward when prepare() ran."""
+        if self._prepared:
+            torch.cuda.current_stream(self.flat.device).wait_event(self._ready)
+            self._prepared = False
+            return
         self.flat.zero_()
         self.hdl.barrier(channel=0)
 

@@ -118,6 +118,16 @@ typedef struct GsrBackwardIO {
      * before and after (no NCCL all-reduce pass).  Pointers must be 16 B aligned. */
     int32_t multimem_reduce;
     int32_t reserved1;     /* multimem mode: number of tile-row bands pipelined against the blend backward (0 or 1 = no pipelining) */
+    /* Factored exchange (view-parallel, SH + scale/rotation inputs).  dL_dsh is the outer
+     * product  basis(mean - campos) x dL_dRGB  (backward.cu:12-146), so a rank only has to publish the 3
+     * clamp-masked colour gradients of a Gaussian instead of its 3*M SH gradients; every receiver rebuilds
+     * the basis of each sender's camera from its own copy of the means (gsr_exchange_expand).  When
+     * xchg_records != NULL the kernel writes ONLY these three buffers and dL_dmeans2D (the five per-input
+     * gradient pointers above are ignored); rows of culled Gaussians are not touched, so the caller
+     * zeroes the buffers beforehand.  With multimem_reduce = 1 the three pointers are multicast addresses. */
+    float* xchg_records;   /* P*12: {dL_dmeans3D xyz, dL_dopacity, dL_dscales xyz, 0, dL_drotations wxyz}, summed over ranks */
+    float* xchg_rgb;       /* this rank's slot of [world][P][4]: {dL_dR, dL_dG, dL_dB, 0} */
+    float* xchg_campos;    /* this rank's slot of [world][4]:    {campos xyz, 1} */
 } GsrBackwardIO;
 
 int         gsr_version(void);
@@ -152,6 +162,15 @@ int gsr_forward(const GsrParams* p, const GsrBuffers* buf,
 /* Backward of the whole path. R as returned by forward. */
 int gsr_backward(const GsrParams* p, const GsrBuffers* buf, int64_t R,
                  const int32_t* radii, const GsrBackwardIO* io, void* stream);
+
+/* Second half of the factored exchange: after every rank's gsr_backward has landed (rank barrier), turn this
+ * rank's replica of the exchange buffers into the dense gradient tensors, summed over ranks:
+ *   dL_dsh[g] = sum_r basis_D(means3D[g] - campos[r]) x rgb[r][g]   (fixed order r = 0..world-1, deterministic),
+ * the other four straight from the records.  Uses p->P, D, M, means3D.  Every output row is written. */
+int gsr_exchange_expand(const GsrParams* p, int32_t world, const float* records /* P*12 */,
+                        const float* rgb /* world*P*4 */, const float* campos /* world*4 */,
+                        float* dL_dmeans3D, float* dL_dopacity, float* dL_dsh, float* dL_dscales,
+                        float* dL_drotations, void* stream);
 
 /* present[i] = (W2V * p_i).z > 0.2   (rasterizer_impl.cu:56-73). present is P bytes (bool). */
 int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,

@@ -50,7 +50,11 @@ def main():
     # fused: reduced inside the kernel
     red = FusedGradientReducer().install()
     worst = 0.0
-    for rep in range(3):
+    # factored exchange (default) and full-gradient reduction, each with both orderings of the buffer clear +
+    # rank barrier: overlapped with the forward (default) and at backward start
+    for rep in range(8):
+        red.factored = rep < 4
+        red.early = rep % 4 < 2
         got, m2 = run()
         torch.cuda.synchronize()
         for k in want:
