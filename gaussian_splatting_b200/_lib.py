@@ -27,7 +27,7 @@ class GsrParams(C.Structure):
         ("reserved0", C.c_int32),
         ("background", _fp), ("means3D", _fp), ("shs", _fp), ("colors_precomp", _fp),
         ("opacities", _fp), ("scales", _fp), ("rotations", _fp), ("cov3D_precomp", _fp),
-        ("viewmatrix", _fp), ("projmatrix", _fp), ("campos", _fp),
+        ("viewmatrix", _fp), ("projmatrix", _fp), ("campos", _fp), ("sh_dc", _fp),
     ]
 
 
@@ -51,7 +51,7 @@ class GsrBackwardIO(C.Structure):
         ("dL_dmeans3D", _fp), ("dL_dmeans2D", _fp), ("dL_dopacity", _fp), ("dL_dcolors", _fp),
         ("dL_dcov3D", _fp), ("dL_dsh", _fp), ("dL_dscales", _fp), ("dL_drotations", _fp),
         ("multimem_reduce", C.c_int32), ("reserved1", C.c_int32),
-        ("xchg_records", _fp), ("xchg_rgb", _fp), ("xchg_campos", _fp),
+        ("xchg_records", _fp), ("xchg_rgb", _fp), ("xchg_campos", _fp), ("dL_dsh_dc", _fp),
     ]
 
 
@@ -126,7 +126,7 @@ def load():
     lib.gsr_adam_update.restype = C.c_int
     lib.gsr_adam_update.argtypes = [C.c_void_p] * 5 + [C.c_double] * 6 + [C.c_int64, C.c_int32, C.c_void_p]
     lib.gsr_exchange_expand.restype = C.c_int
-    lib.gsr_exchange_expand.argtypes = [PP, C.c_int32] + [C.c_void_p] * 9
+    lib.gsr_exchange_expand.argtypes = [PP, C.c_int32] + [C.c_void_p] * 10
     PS = C.POINTER(GsrSsimParams)
     lib.gsr_ssim_partials.restype = C.c_int64
     lib.gsr_ssim_partials.argtypes = [C.c_int32] * 4

@@ -76,6 +76,10 @@ static int validate(const GsrParams* p, const GsrBuffers* buf) {
         set_error("Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!");
         return GSR_ERR_INVALID_ARG;
     }
+    if (p->sh_dc && (!p->shs || p->M < 2)) {
+        set_error("split SH storage (sh_dc) needs shs = coefficients 1..M-1 and M >= 2");
+        return GSR_ERR_INVALID_ARG;
+    }
     if (p->shs) {
         if (p->D < 0 || p->D > 3) { set_error("sh_degree must be in 0..3"); return GSR_ERR_INVALID_ARG; }
         if (p->M < (p->D + 1) * (p->D + 1) || p->M > 16) {
@@ -251,6 +255,10 @@ int gsr_backward(const GsrParams* p, const GsrBuffers* buf, int64_t R, const int
     const int gy = (p->H + TILE_Y - 1) / TILE_Y;
     const bool have_invdepth = io->dL_dout_invdepth != nullptr;
     const bool fact = io->xchg_records != nullptr;
+    if (p->sh_dc && !fact && ((io->dL_dsh == nullptr) != (io->dL_dsh_dc == nullptr))) {
+        set_error("split SH storage: pass both dL_dsh (coefficients 1..M-1) and dL_dsh_dc, or neither");
+        return GSR_ERR_INVALID_ARG;
+    }
     if (fact) {
         const auto misaligned = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) != 0; };
         if (!io->xchg_rgb || !io->xchg_campos || !p->shs || !p->scales || !p->rotations || p->colors_precomp ||
@@ -265,7 +273,7 @@ int gsr_backward(const GsrParams* p, const GsrBuffers* buf, int64_t R, const int
     if (bands > MAX_BANDS) bands = MAX_BANDS;
     SideStream* side = bands > 1 ? side_stream() : nullptr;
     // list mode needs whole-float4, 16 B aligned SH rows (same condition as the bulk-copy path)
-    const bool list_ok = p->shs == nullptr || io->dL_dsh == nullptr ||
+    const bool list_ok = p->sh_dc != nullptr ? false : p->shs == nullptr || io->dL_dsh == nullptr ||
                          ((p->M & 3) == 0 && (reinterpret_cast<uintptr_t>(p->shs) & 15) == 0 &&
                           (reinterpret_cast<uintptr_t>(io->dL_dsh) & 15) == 0);
     if (bands <= 1 || side == nullptr || !list_ok) {

@@ -61,7 +61,7 @@ exchange_expand_kernel(int P, int D, int M, int world, const float* __restrict__
                        const float4* __restrict__ records, const float4* __restrict__ rgb,
                        const float4* __restrict__ campos, float* __restrict__ dL_dmeans3D,
                        float* __restrict__ dL_dopacity, float* __restrict__ dL_dsh, float* __restrict__ dL_dscales,
-                       float* __restrict__ dL_drotations) {
+                       float* __restrict__ dL_drotations, float* __restrict__ dL_dsh_dc) {
     __shared__ __align__(128) float s_rows[BULK ? XE_WARPS * 32 * XE_ROW : 4];
     __shared__ float4 s_cam[XE_MAX_WORLD];
     if ((int)threadIdx.x < world) s_cam[threadIdx.x] = campos[threadIdx.x];
@@ -102,25 +102,42 @@ exchange_expand_kernel(int P, int D, int M, int world, const float* __restrict__
         }
     }
     if (!dL_dsh) return;
-    if (BULK) {
+    const bool split = dL_dsh_dc != nullptr;       // split SH storage: dc rows [P][3] + rest rows [P][M-1][3]
+    const int row = 3 * M, rest = row - 3;
+    const int nvalid = max(0, min(32, P - warp_base));
+    if (BULK && (!split || (nvalid & 3) == 0)) {
         float* ws = s_rows + warp * 32 * XE_ROW;
-        float4* my = reinterpret_cast<float4*>(ws + lane * XE_ROW);
+        if (!split) {
+            float4* my = reinterpret_cast<float4*>(ws + lane * XE_ROW);
 #pragma unroll
-        for (int m = 0; m < XE_ROW / 4; m++) my[m] = make_float4(sh[4 * m], sh[4 * m + 1], sh[4 * m + 2], sh[4 * m + 3]);
+            for (int m = 0; m < XE_ROW / 4; m++) my[m] = make_float4(sh[4 * m], sh[4 * m + 1], sh[4 * m + 2], sh[4 * m + 3]);
+        } else {
+#pragma unroll
+            for (int k = 0; k < 3; k++) ws[lane * 3 + k] = sh[k];
+#pragma unroll
+            for (int k = 3; k < XE_ROW; k++) ws[96 + lane * (XE_ROW - 3) + (k - 3)] = sh[k];
+        }
         fence_proxy_async_smem();
         __syncwarp();
-        const int nvalid = max(0, min(32, P - warp_base));
         if (lane == 0 && nvalid > 0) {
-            bulk_s2g(dL_dsh + (size_t)warp_base * XE_ROW, smem_u32(ws), (uint32_t)nvalid * XE_ROW * 4u);
+            if (!split) {
+                bulk_s2g(dL_dsh + (size_t)warp_base * XE_ROW, smem_u32(ws), (uint32_t)nvalid * XE_ROW * 4u);
+            } else {
+                bulk_s2g(dL_dsh_dc + (size_t)warp_base * 3, smem_u32(ws), (uint32_t)nvalid * 12u);
+                bulk_s2g(dL_dsh + (size_t)warp_base * (XE_ROW - 3), smem_u32(ws + 96), (uint32_t)nvalid * (XE_ROW - 3) * 4u);
+            }
             bulk_commit();
             bulk_wait_read0();
         }
     } else if (mine) {
-        const int row = 3 * M;
-        float* dst = dL_dsh + (size_t)idx * row;
+        float* dst = split ? dL_dsh + (size_t)idx * rest : dL_dsh + (size_t)idx * row;
+        if (split) {
+#pragma unroll
+            for (int k = 0; k < 3; k++) dL_dsh_dc[3 * (size_t)idx + k] = sh[k];
+        }
 #pragma unroll
         for (int k = 0; k < XE_ROW; k++)
-            if (k < row) dst[k] = sh[k];
+            if (k < row && (!split || k >= 3)) dst[split ? k - 3 : k] = sh[k];
     }
 }
 
@@ -128,7 +145,7 @@ exchange_expand_kernel(int P, int D, int M, int world, const float* __restrict__
 
 extern "C" int gsr_exchange_expand(const GsrParams* p, int32_t world, const float* records, const float* rgb,
                                    const float* campos, float* dL_dmeans3D, float* dL_dopacity, float* dL_dsh,
-                                   float* dL_dscales, float* dL_drotations, void* stream) {
+                                   float* dL_dscales, float* dL_drotations, float* dL_dsh_dc, void* stream) {
     using namespace gsr;
     if (!p || p->P < 0 || world < 1 || world > XE_MAX_WORLD || p->D < 0 || p->D > 3 || p->M < 0 || p->M > 16 ||
         (p->D + 1) * (p->D + 1) > (p->M > 0 ? p->M : 16)) {
@@ -147,12 +164,16 @@ extern "C" int gsr_exchange_expand(const GsrParams* p, int32_t world, const floa
     }
     cudaStream_t st = (cudaStream_t)stream;
     const int blocks = (p->P + XE_THREADS - 1) / XE_THREADS;
-    const bool bulk = dL_dsh && p->M == 16 && !misaligned(dL_dsh);
+    if (dL_dsh_dc && (!dL_dsh || p->M < 2)) {
+        set_error("gsr_exchange_expand: split SH storage needs dL_dsh (rest) and M >= 2");
+        return GSR_ERR_INVALID_ARG;
+    }
+    const bool bulk = dL_dsh && p->M == 16 && !misaligned(dL_dsh) && !misaligned(dL_dsh_dc);
     StageTimer tm(GSR_STAGE_PREPROCESS_BWD, st);      // accounted with the per-Gaussian backward
 #define XE_LAUNCH(B) GSR_LAUNCH(exchange_expand_kernel<B>, blocks, XE_THREADS, 0, st, p->P, p->D, p->M, (int)world, \
                                 p->means3D, reinterpret_cast<const float4*>(records), reinterpret_cast<const float4*>(rgb), \
                                 reinterpret_cast<const float4*>(campos), dL_dmeans3D, dL_dopacity, dL_dsh, dL_dscales, \
-                                dL_drotations)
+                                dL_drotations, dL_dsh_dc)
     if (bulk) XE_LAUNCH(true);
     else XE_LAUNCH(false);
 #undef XE_LAUNCH

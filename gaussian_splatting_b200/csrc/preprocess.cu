@@ -138,7 +138,29 @@ preprocess_fwd_kernel(GsrParams p, float focal_x, float focal_y, int gx, int gy,
             const int row = 3 * p.M;                      // floats stored per Gaussian
             float* ws = sh_smem[warp];
             const float* src = p.shs + (size_t)warp_base * row;
-            if ((L & 3) == 0 && (row & 3) == 0) {
+            if (p.sh_dc != nullptr) {
+                // split storage: coefficient 0 from sh_dc [P][3], coefficients 1.. from shs [P][M-1][3]; both
+                // blocks of the warp's 32 Gaussians are contiguous, so the scalar loads stay coalesced
+                const int rrow = row - 3;
+                const float* dc = p.sh_dc + (size_t)warp_base * 3;
+                const float* rest = p.shs + (size_t)warp_base * rrow;
+                for (int i = lane; i < 32 * 3; i += 32) {
+                    int g = i / 3, k = i - g * 3;
+                    if ((vis_mask >> g) & 1u) ws[g * SH_ROW_PAD + k] = __ldg(dc + i);
+                }
+                const int Lr = L - 3;
+                if (Lr == rrow) {                 // all stored coefficients are active: one flat, contiguous sweep
+                    for (int i = lane; i < 32 * rrow; i += 32) {
+                        int g = i / rrow, k = i - g * rrow;
+                        if ((vis_mask >> g) & 1u) ws[g * SH_ROW_PAD + 3 + k] = __ldg(rest + i);
+                    }
+                } else {
+                    for (int i = lane; i < 32 * Lr; i += 32) {
+                        int g = i / Lr, k = i - g * Lr;
+                        if ((vis_mask >> g) & 1u) ws[g * SH_ROW_PAD + 3 + k] = __ldg(rest + (size_t)g * rrow + k);
+                    }
+                }
+            } else if ((L & 3) == 0 && (row & 3) == 0) {
                 const int L4 = L >> 2;
                 for (int i = lane; i < 32 * L4; i += 32) {
                     int g = i / L4, k = i - g * L4;

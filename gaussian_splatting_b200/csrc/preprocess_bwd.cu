@@ -159,25 +159,63 @@ __device__ __forceinline__ float3 sh_backward(float* row, int rowlen, int deg, f
     return dnormvdv(dir_orig, dL_ddir);
 }
 
-// Vector path: the row is pulled into registers with LDS.128, the gradients go back with STS.128.
-template <bool STORE = true>
-__device__ __forceinline__ float3 sh_backward_vec(float* row, int rowlen, int deg, float3 dir_orig,
-                                                  const float dL_dRGB[3]) {
+// Where a lane's coefficient row lives in the warp's shared-memory staging area.
+//   kind 0: padded rows of PB_STRIDE_SCALAR floats (scalar path)
+//   kind 1: dense rows of `rowlen` floats, whole float4s (vector path: LDS.128 / STS.128)
+//   kind 2: split storage — 32 dc rows of 3 floats, then from SPLIT_REST_OFF 32 rest rows of rowlen-3 floats
+//           (odd stride: conflict-free scalar accesses)
+struct RowLayout { int kind; int rowlen; };
+constexpr int SPLIT_REST_OFF = 96;
+
+// SH backward for this lane's row, through registers.  STORE: write the coefficient gradients back in place.
+template <bool STORE>
+__device__ __forceinline__ float3 sh_backward_smem(float* ws, int lane, RowLayout lay, int deg, float3 dir_orig,
+                                                   const float dL_dRGB[3]) {
+    if (lay.kind == 0) return sh_backward<STORE>(ws + lane * PB_STRIDE_SCALAR, lay.rowlen, deg, dir_orig, dL_dRGB);
     float sh[PB_ROW];
-    float4* row4 = reinterpret_cast<float4*>(row);
+    const int rowlen = lay.rowlen, rest = rowlen - 3;
+    float4* row4 = reinterpret_cast<float4*>(ws + lane * rowlen);
+    if (lay.kind == 1) {
 #pragma unroll
-    for (int m = 0; m < PB_ROW / 4; m++) {
-        const float4 v = row4[m];
-        sh[4 * m] = v.x; sh[4 * m + 1] = v.y; sh[4 * m + 2] = v.z; sh[4 * m + 3] = v.w;
+        for (int m = 0; m < PB_ROW / 4; m++) {
+            const float4 v = row4[m];
+            sh[4 * m] = v.x; sh[4 * m + 1] = v.y; sh[4 * m + 2] = v.z; sh[4 * m + 3] = v.w;
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < 3; k++) sh[k] = ws[lane * 3 + k];
+#pragma unroll
+        for (int k = 3; k < PB_ROW; k++) sh[k] = k < rowlen ? ws[SPLIT_REST_OFF + lane * rest + (k - 3)] : 0.f;
     }
     const float3 r = sh_backward<STORE>(sh, rowlen, deg, dir_orig, dL_dRGB);
     if (STORE) {
-        const int n4 = rowlen >> 2;
+        if (lay.kind == 1) {
+            const int n4 = rowlen >> 2;
 #pragma unroll
-        for (int m = 0; m < PB_ROW / 4; m++)
-            if (m < n4) row4[m] = make_float4(sh[4 * m], sh[4 * m + 1], sh[4 * m + 2], sh[4 * m + 3]);
+            for (int m = 0; m < PB_ROW / 4; m++)
+                if (m < n4) row4[m] = make_float4(sh[4 * m], sh[4 * m + 1], sh[4 * m + 2], sh[4 * m + 3]);
+        } else {
+#pragma unroll
+            for (int k = 0; k < 3; k++) ws[lane * 3 + k] = sh[k];
+#pragma unroll
+            for (int k = 3; k < PB_ROW; k++)
+                if (k < rowlen) ws[SPLIT_REST_OFF + lane * rest + (k - 3)] = sh[k];
+        }
     }
     return r;
+}
+
+// zero gradient row of a culled Gaussian
+__device__ __forceinline__ void row_zero(float* ws, int lane, RowLayout lay) {
+    const int rowlen = lay.rowlen;
+    if (lay.kind == 0) {
+        for (int k = 0; k < rowlen; k++) ws[lane * PB_STRIDE_SCALAR + k] = 0.f;
+    } else if (lay.kind == 1) {
+        for (int k = 0; k < (rowlen >> 2); k++) reinterpret_cast<float4*>(ws + lane * rowlen)[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+    } else {
+        for (int k = 0; k < 3; k++) ws[lane * 3 + k] = 0.f;
+        for (int k = 0; k < rowlen - 3; k++) ws[SPLIT_REST_OFF + lane * (rowlen - 3) + k] = 0.f;
+    }
 }
 
 // cov3D backward (backward.cu:296-365) with GLM indexing m[c][r].
@@ -256,17 +294,29 @@ preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord*
     const bool mine = in_range;
     const unsigned vis_mask = __ballot_sync(0xffffffffu, visible);
     const int sh_row = 3 * p.M;                                   // floats per Gaussian
-    const uint32_t sh_bytes = (uint32_t)(max(0, min(32, p.P - warp_base)) * sh_row) * 4u;
+    const int nvalid = max(0, min(32, p.P - warp_base));
+    const uint32_t sh_bytes = (uint32_t)(nvalid * sh_row) * 4u;
+    // Split SH storage (GsrParams.sh_dc): the warp's 32 dc rows (96 floats) and 32 rest rows are two contiguous
+    // blocks; in shared memory the dc block comes first, the rest block follows at SPLIT_REST_OFF.
+    const bool split = p.sh_dc != nullptr;
+    const int rest_row = sh_row - 3;
+    // bulk copies need 16 B multiples: a ragged last warp (nvalid % 4 != 0) of the split layout is copied by the lanes
+    const bool bulk_ok = !split || (nvalid & 3) == 0;
     if (VEC && LIST) {                                            // gather: one bulk copy per Gaussian row
         const uint32_t bar = smem_u32(&s_bar[warp]);
         if (visible) bulk_g2s(smem_u32(sh_smem[warp] + lane * sh_row), p.shs + (size_t)idx * sh_row, (uint32_t)sh_row * 4u, bar);
         if (lane == 0 && vis_mask != 0) mbar_arrive_expect_tx(bar, (uint32_t)__popc(vis_mask) * (uint32_t)sh_row * 4u);
-    } else if (VEC && vis_mask != 0 && lane == 0) {               // prefetch this warp's (contiguous) SH rows
+    } else if (VEC && vis_mask != 0 && lane == 0 && bulk_ok) {    // prefetch this warp's (contiguous) SH rows
         const uint32_t bar = smem_u32(&s_bar[warp]);
         mbar_arrive_expect_tx(bar, sh_bytes);
-        bulk_g2s(smem_u32(sh_smem[warp]), p.shs + (size_t)warp_base * sh_row, sh_bytes, bar);
+        if (split) {
+            bulk_g2s(smem_u32(sh_smem[warp]), p.sh_dc + (size_t)warp_base * 3, (uint32_t)nvalid * 12u, bar);
+            bulk_g2s(smem_u32(sh_smem[warp] + SPLIT_REST_OFF), p.shs + (size_t)warp_base * rest_row,
+                     (uint32_t)(nvalid * rest_row) * 4u, bar);
+        } else {
+            bulk_g2s(smem_u32(sh_smem[warp]), p.shs + (size_t)warp_base * sh_row, sh_bytes, bar);
+        }
     }
-
     float3 dL_dmean = {0.f, 0.f, 0.f};
     float2 dL_dmean2D = {0.f, 0.f};
     float dL_dopacity = 0.f;
@@ -391,116 +441,112 @@ preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord*
         if (p.scales != nullptr) cov3D_backward(sc, p.scale_modifier, rot, dL_dcov, &dL_dscale, &dL_drot);
     }
 
-    // ---- factored exchange: publish {mean, opacity, scale, rotation} gradients as one 48 B
-    // record (summed across ranks) and the clamp-masked dL_dRGB in this rank's slot; dL_dsh is rebuilt
-    // by every receiver (exchange.cu).  16 B multimem operations only; culled rows are not touched.
-    if (io.xchg_records != nullptr) {
+    // SH rows of the warp in shared memory.  Layouts (RowLayout): dense rows of `sh_row` floats (vector path),
+    // dc block + rest block (split storage), or padded 49-float rows (scalar path).
+    const bool has_sh = p.shs != nullptr;
+    const bool fact = io.xchg_records != nullptr;
+    if (has_sh && (fact || io.dL_dsh != nullptr)) {
+        float* ws = sh_smem[warp];
+        const RowLayout lay = {VEC ? (split ? 2 : 1) : 0, sh_row};
         float dL_dRGB[3];
 #pragma unroll
         for (int c = 0; c < 3; c++) dL_dRGB[c] = ((clamped_bits >> c) & 1) ? 0.f : dL_dcolor[c];
         const float3 dir_orig = {mean.x - s_cam[0], mean.y - s_cam[1], mean.z - s_cam[2]};
-        float* ws = sh_smem[warp];
-        if (VEC) {
+        // ---- coefficients in ----
+        if (VEC && (LIST || bulk_ok)) {
             if (vis_mask != 0) mbar_wait(smem_u32(&s_bar[warp]), 0);
-            if (visible) {
-                const float3 dm = sh_backward_vec<false>(ws + lane * sh_row, sh_row, p.D, dir_orig, dL_dRGB);
-                dL_dmean.x += dm.x; dL_dmean.y += dm.y; dL_dmean.z += dm.z;
-            }
+        } else if (VEC) {                       // ragged last warp of the split layout
+            for (int i = lane; i < nvalid * 3; i += 32) ws[i] = __ldg(p.sh_dc + (size_t)warp_base * 3 + i);
+            for (int i = lane; i < nvalid * rest_row; i += 32) ws[SPLIT_REST_OFF + i] = __ldg(p.shs + (size_t)warp_base * rest_row + i);
+            __syncwarp();
         } else {
-            const int L = 3 * (p.D + 1) * (p.D + 1);
             if (vis_mask != 0) {
-                const float* src = p.shs + (size_t)warp_base * sh_row;
-                for (int i = lane; i < 32 * L; i += 32) {
-                    int g = i / L, k = i - g * L;
-                    if ((vis_mask >> g) & 1u) ws[g * PB_STRIDE_SCALAR + k] = __ldg(src + (size_t)g * sh_row + k);
+                const int Lc = 3 * (p.D + 1) * (p.D + 1);
+                for (int i = lane; i < 32 * Lc; i += 32) {
+                    const int g = i / Lc, k = i - g * Lc;
+                    if ((vis_mask >> g) & 1u) {
+                        const size_t gi = (size_t)(warp_base + g);
+                        ws[g * PB_STRIDE_SCALAR + k] = !split ? __ldg(p.shs + gi * sh_row + k)
+                                                       : (k < 3 ? __ldg(p.sh_dc + gi * 3 + k) : __ldg(p.shs + gi * rest_row + (k - 3)));
+                    }
                 }
             }
             __syncwarp();
+        }
+        // ---- factored exchange: publish {mean, opacity, scale, rotation} gradients as one 48 B
+        // record (summed across ranks) and the clamp-masked dL_dRGB in this rank's slot; dL_dsh is rebuilt by
+        // every receiver (exchange.cu).  16 B multimem operations only; culled rows are not touched.
+        if (fact) {
             if (visible) {
-                const float3 dm = sh_backward<false>(ws + lane * PB_STRIDE_SCALAR, sh_row, p.D, dir_orig, dL_dRGB);
+                const float3 dm = sh_backward_smem<false>(ws, lane, lay, p.D, dir_orig, dL_dRGB);
                 dL_dmean.x += dm.x; dL_dmean.y += dm.y; dL_dmean.z += dm.z;
             }
+            if (blockIdx.x == 0 && threadIdx.x == 0)
+                out4<MM>(io.xchg_campos, make_float4(s_cam[0], s_cam[1], s_cam[2], 1.f));
+            if (!mine) return;
+            if (io.dL_dmeans2D) {
+                io.dL_dmeans2D[3 * idx] = dL_dmean2D.x; io.dL_dmeans2D[3 * idx + 1] = dL_dmean2D.y; io.dL_dmeans2D[3 * idx + 2] = 0.f;
+            }
+            if (visible) {
+                float* r = io.xchg_records + 12 * (size_t)idx;
+                out4<MM>(r, make_float4(dL_dmean.x, dL_dmean.y, dL_dmean.z, dL_dopacity));
+                out4<MM>(r + 4, make_float4(dL_dscale.x, dL_dscale.y, dL_dscale.z, 0.f));
+                out4<MM>(r + 8, dL_drot);
+                out4<MM>(io.xchg_rgb + 4 * (size_t)idx, make_float4(dL_dRGB[0], dL_dRGB[1], dL_dRGB[2], 0.f));
+            }
+            return;
         }
-        if (blockIdx.x == 0 && threadIdx.x == 0)
-            out4<MM>(io.xchg_campos, make_float4(s_cam[0], s_cam[1], s_cam[2], 1.f));
-        if (!mine) return;
-        if (io.dL_dmeans2D) {
-            io.dL_dmeans2D[3 * idx] = dL_dmean2D.x; io.dL_dmeans2D[3 * idx + 1] = dL_dmean2D.y; io.dL_dmeans2D[3 * idx + 2] = 0.f;
-        }
+        // ---- SH backward in place; dL_dsh rows leave coalesced ----
         if (visible) {
-            float* r = io.xchg_records + 12 * (size_t)idx;
-            out4<MM>(r, make_float4(dL_dmean.x, dL_dmean.y, dL_dmean.z, dL_dopacity));
-            out4<MM>(r + 4, make_float4(dL_dscale.x, dL_dscale.y, dL_dscale.z, 0.f));
-            out4<MM>(r + 8, dL_drot);
-            out4<MM>(io.xchg_rgb + 4 * (size_t)idx, make_float4(dL_dRGB[0], dL_dRGB[1], dL_dRGB[2], 0.f));
+            const float3 dm = sh_backward_smem<true>(ws, lane, lay, p.D, dir_orig, dL_dRGB);
+            dL_dmean.x += dm.x; dL_dmean.y += dm.y; dL_dmean.z += dm.z;
+        } else {
+            row_zero(ws, lane, lay);
         }
-        return;
-    }
-
-    // ---- SH backward; dL_dsh rows leave coalesced (bulk store or transposed scalar stores) ----
-    if (p.shs != nullptr && io.dL_dsh != nullptr) {
-        const int L = 3 * (p.D + 1) * (p.D + 1);
-        const int row = sh_row;
-        float* ws = sh_smem[warp];
-        float dL_dRGB[3];
-#pragma unroll
-        for (int c = 0; c < 3; c++) dL_dRGB[c] = ((clamped_bits >> c) & 1) ? 0.f : dL_dcolor[c];
-        const float3 dir_orig = {mean.x - s_cam[0], mean.y - s_cam[1], mean.z - s_cam[2]};
-        float* dst = io.dL_dsh + (size_t)warp_base * row;
-        if (VEC) {
-            if (vis_mask != 0) mbar_wait(smem_u32(&s_bar[warp]), 0);
-            float* myrow = ws + lane * row;
-            if (visible) {
-                const float3 dm = sh_backward_vec(myrow, row, p.D, dir_orig, dL_dRGB);
-                dL_dmean.x += dm.x; dL_dmean.y += dm.y; dL_dmean.z += dm.z;
-            } else {
-                for (int k = 0; k < (row >> 2); k++) reinterpret_cast<float4*>(myrow)[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (VEC && MM && LIST) {
+            // 16 B multimem reductions, 12 consecutive lanes per (scattered) Gaussian row
+            __syncwarp();
+            const int row4 = sh_row >> 2;
+            for (int f = lane; f < 32 * row4; f += 32) {
+                const int gl = f / row4, k = f - gl * row4;
+                const int gid = __shfl_sync(0xffffffffu, idx, gl);
+                if ((vis_mask >> gl) & 1u)
+                    out4<true>(io.dL_dsh + (size_t)gid * sh_row + 4 * k, reinterpret_cast<const float4*>(ws)[f]);
             }
-            if (MM && LIST) {
-                // 16 B multimem reductions, 12 consecutive lanes per (scattered) Gaussian row
-                __syncwarp();
-                const int row4 = row >> 2;
-                for (int f = lane; f < 32 * row4; f += 32) {
-                    const int gl = f / row4, k = f - gl * row4;
-                    const int gid = __shfl_sync(0xffffffffu, idx, gl);
-                    if ((vis_mask >> gl) & 1u)
-                        out4<true>(io.dL_dsh + (size_t)gid * row + 4 * k, reinterpret_cast<const float4*>(ws)[f]);
-                }
-            } else if (MM) {
-                // rows of this warp are contiguous: 16 B multimem reductions, coalesced across lanes
-                __syncwarp();
-                const int n4 = (int)(sh_bytes >> 4);
-                for (int f = lane; f < n4; f += 32)
-                    out4<true>(dst + 4 * f, reinterpret_cast<const float4*>(ws)[f]);
+        } else if (VEC && (MM || !bulk_ok)) {
+            // the warp's rows are contiguous in global memory: coalesced 16 B (or, ragged split tail, 4 B) outputs
+            __syncwarp();
+            float* d0 = split ? io.dL_dsh_dc + (size_t)warp_base * 3 : io.dL_dsh + (size_t)warp_base * sh_row;
+            const int n0 = split ? nvalid * 3 : nvalid * sh_row;
+            float* d1 = io.dL_dsh + (size_t)warp_base * rest_row;
+            const int n1 = split ? nvalid * rest_row : 0;
+            if (bulk_ok) {
+                for (int f = lane; f < (n0 >> 2); f += 32) out4<MM>(d0 + 4 * f, reinterpret_cast<const float4*>(ws)[f]);
+                for (int f = lane; f < (n1 >> 2); f += 32) out4<MM>(d1 + 4 * f, reinterpret_cast<const float4*>(ws + SPLIT_REST_OFF)[f]);
             } else {
-                fence_proxy_async_smem();
-                __syncwarp();
-                if (lane == 0 && sh_bytes != 0) {
-                    bulk_s2g(dst, smem_u32(ws), sh_bytes);
-                    bulk_commit();
+                for (int f = lane; f < n0; f += 32) out1<MM>(d0 + f, ws[f]);
+                for (int f = lane; f < n1; f += 32) out1<MM>(d1 + f, ws[SPLIT_REST_OFF + f]);
+            }
+        } else if (VEC) {
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0 && sh_bytes != 0) {
+                if (split) {
+                    bulk_s2g(io.dL_dsh_dc + (size_t)warp_base * 3, smem_u32(ws), (uint32_t)nvalid * 12u);
+                    bulk_s2g(io.dL_dsh + (size_t)warp_base * rest_row, smem_u32(ws + SPLIT_REST_OFF), (uint32_t)(nvalid * rest_row) * 4u);
+                } else {
+                    bulk_s2g(io.dL_dsh + (size_t)warp_base * sh_row, smem_u32(ws), sh_bytes);
                 }
+                bulk_commit();
             }
         } else {
-            if (vis_mask != 0) {
-                const float* src = p.shs + (size_t)warp_base * row;
-                for (int i = lane; i < 32 * L; i += 32) {
-                    int g = i / L, k = i - g * L;
-                    if ((vis_mask >> g) & 1u) ws[g * PB_STRIDE_SCALAR + k] = __ldg(src + (size_t)g * row + k);
-                }
-            }
             __syncwarp();
-            float* myrow = ws + lane * PB_STRIDE_SCALAR;
-            if (visible) {
-                const float3 dm = sh_backward(myrow, row, p.D, dir_orig, dL_dRGB);
-                dL_dmean.x += dm.x; dL_dmean.y += dm.y; dL_dmean.z += dm.z;
-            } else {
-                for (int k = 0; k < row; k++) myrow[k] = 0.f;
-            }
-            __syncwarp();
-            const int nvalid = min(32, p.P - warp_base);
-            for (int i = lane; i < nvalid * row; i += 32) {
-                int g = i / row, k = i - g * row;
-                out1<MM>(dst + i, ws[g * PB_STRIDE_SCALAR + k]);
+            for (int i = lane; i < nvalid * sh_row; i += 32) {
+                const int g = i / sh_row, k = i - g * sh_row;
+                const size_t gi = (size_t)(warp_base + g);
+                float* dst = !split ? io.dL_dsh + gi * sh_row + k
+                                    : (k < 3 ? io.dL_dsh_dc + gi * 3 + k : io.dL_dsh + gi * rest_row + (k - 3));
+                out1<MM>(dst, ws[g * PB_STRIDE_SCALAR + k]);
             }
         }
     }
@@ -625,9 +671,13 @@ int launch_preprocess_backward(const GsrParams& p, GeomState g, Scratch s, const
     StageTimer tm(GSR_STAGE_PREPROCESS_BWD, st);
     // vector path: SH rows are whole float4s (M in {4, 8, 12, 16}) and 16 B aligned
     const bool fact = io.xchg_records != nullptr;
-    const bool vec = p.shs != nullptr && (fact || io.dL_dsh != nullptr) && (p.M & 3) == 0 &&
-                     (reinterpret_cast<uintptr_t>(p.shs) & 15) == 0 &&
-                     (fact || (reinterpret_cast<uintptr_t>(io.dL_dsh) & 15) == 0);
+    const auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+    // vector path: SH rows are whole float4s (M in {4, 8, 12, 16}) and 16 B aligned; split storage: any M, both
+    // blocks (and both gradient blocks) 16 B aligned
+    const bool split = p.sh_dc != nullptr;
+    const bool vec = p.shs != nullptr && (fact || io.dL_dsh != nullptr) && al16(p.shs) &&
+                     (split ? al16(p.sh_dc) && (fact || (al16(io.dL_dsh) && al16(io.dL_dsh_dc)))
+                            : (p.M & 3) == 0 && (fact || al16(io.dL_dsh)));
     const bool mm = io.multimem_reduce != 0;
 #define PB_LAUNCH(V, M) GSR_LAUNCH((preprocess_bwd_kernel<V, M>), blocks, PB_THREADS, 0, st, p, focal_x, focal_y, g.rec, \
                                    radii, s.acc, have_invdepth, io, blist, s.band_ctl, band)

@@ -115,7 +115,7 @@ def _f32c(t, name):
 
 
 def _params(P, M, rs, bg, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
-            viewmatrix, projmatrix, campos):
+            viewmatrix, projmatrix, campos, sh_dc=None):
     p = GsrParams()
     p.P, p.D, p.M = P, int(rs.sh_degree), M
     p.W, p.H = int(rs.image_width), int(rs.image_height)
@@ -126,15 +126,17 @@ def _params(P, M, rs, bg, means3D, sh, colors_precomp, opacities, scales, rotati
     p.colors_precomp, p.opacities = _ptr(colors_precomp), _ptr(opacities)
     p.scales, p.rotations, p.cov3D_precomp = _ptr(scales), _ptr(rotations), _ptr(cov3Ds_precomp)
     p.viewmatrix, p.projmatrix, p.campos = _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos)
+    p.sh_dc = _ptr(sh_dc)
     return p
 
 
 def _forward_native(rs, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
-                    state_out=None):
+                    state_out=None, dc=None):
     """Role of _C.rasterize_gaussians (ext.cpp:16 -> rasterize_points.cu:45-146).
 
     Returns (num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, invdepths).
-    state_out: optional dict that receives views of the binning / image state (parity tests)."""
+    state_out: optional dict that receives views of the binning / image state (parity tests).
+    dc: split SH storage — degree-0 coefficients (P,1,3); `sh` then holds coefficients 1..M-1."""
     lib = _lib.load()
     if means3D.ndim != 2 or means3D.shape[1] != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
@@ -162,9 +164,10 @@ def _forward_native(rs, means3D, sh, colors_precomp, opacities, scales, rotation
         viewmatrix = _f32c(rs.viewmatrix, "viewmatrix")
         projmatrix = _f32c(rs.projmatrix, "projmatrix")
         campos = _f32c(rs.campos, "campos")
-        M = sh.shape[1] if sh is not None else 0
+        dc = _f32c(dc, "dc")
+        M = (sh.shape[1] if sh is not None else 0) + (1 if dc is not None else 0)
         p = _params(P, M, rs, bg, means3D, sh, colors_precomp, opacities, scales, rotations,
-                    cov3Ds_precomp, viewmatrix, projmatrix, campos)
+                    cov3Ds_precomp, viewmatrix, projmatrix, campos, dc)
 
         ws = _workspace(device)
         stream = torch.cuda.current_stream(device)
@@ -227,21 +230,23 @@ def _present(t):
     return t is not None and t.numel() > 0
 
 
-def _grad_layout(P, M, colors_precomp, cov3Ds_precomp, sh, scales, rotations):
-    """Names and shapes of the per-Gaussian gradient tensors the backward kernel writes."""
+def _grad_layout(P, M, colors_precomp, cov3Ds_precomp, sh, scales, rotations, split=False):
+    """Names and shapes of the per-Gaussian gradient tensors the backward kernel writes.
+    M counts all SH coefficients; split: coefficient 0 has its own tensor ("sh_dc"), "sh" holds the rest."""
     want = [("means3D", (P, 3), True), ("opacity", (P, 1), True),
             ("colors", (P, 3), _present(colors_precomp)), ("cov3D", (P, 6), _present(cov3Ds_precomp)),
-            ("sh", (P, M, 3), _present(sh)), ("scales", (P, 3), _present(scales)),
-            ("rotations", (P, 4), _present(rotations))]
+            ("sh", (P, M - 1 if split else M, 3), _present(sh)), ("scales", (P, 3), _present(scales)),
+            ("rotations", (P, 4), _present(rotations)), ("sh_dc", (P, 1, 3), split)]
     return [n for n, _, on in want if on], [shp for _, shp, on in want if on]
 
 
 def _backward_native(rs, means3D, radii, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
-                     grad_out_color, grad_out_depth, sh, geom, R, binb, img):
+                     grad_out_color, grad_out_depth, sh, geom, R, binb, img, dc=None):
     """Role of _C.rasterize_gaussians_backward (rasterize_points.cu:149-248).
 
     Returns (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales,
-    dL_drotations); entries for absent inputs are None."""
+    dL_drotations); entries for absent inputs are None.  With split SH storage (`dc`), dL_dsh covers
+    coefficients 1..M-1 and a ninth entry dL_ddc (P,1,3) is appended."""
     lib = _lib.load()
     device = means3D.device
     P = means3D.shape[0]
@@ -249,10 +254,13 @@ def _backward_native(rs, means3D, radii, colors_precomp, opacities, scales, rota
     f32 = dict(dtype=torch.float32, device=device)
     with torch.cuda.device(device):
         sh_c = _f32c(sh, "sh")
-        M = sh_c.shape[1] if sh_c is not None else 0
+        dc_c = _f32c(dc, "dc")
+        split = dc_c is not None
+        M = (sh_c.shape[1] if sh_c is not None else 0) + (1 if split else 0)
         if P == 0:
             z = lambda *s: torch.zeros(*s, **f32)
-            return z(0, 3), z(0, 3), z(0, 1), z(0, 3), z(0, 6), z(0, M, 3), z(0, 3), z(0, 4)
+            r0 = (z(0, 3), z(0, 3), z(0, 1), z(0, 3), z(0, 6), z(0, M - 1 if split else M, 3), z(0, 3), z(0, 4))
+            return r0 + (z(0, 1, 3),) if split else r0
         means3D = _f32c(means3D, "means3D")
         colors_precomp = _f32c(colors_precomp, "colors_precomp")
         opacities = _f32c(opacities, "opacities")
@@ -268,7 +276,7 @@ def _backward_native(rs, means3D, radii, colors_precomp, opacities, scales, rota
         if grad_out_color is None:
             grad_out_color = torch.zeros((3, H, W), **f32)
         p = _params(P, M, rs, bg, means3D, sh_c, colors_precomp, opacities, scales, rotations,
-                    cov3Ds_precomp, viewmatrix, projmatrix, campos)
+                    cov3Ds_precomp, viewmatrix, projmatrix, campos, dc_c)
 
         ws = _workspace(device)
         stream = torch.cuda.current_stream(device)
@@ -281,7 +289,7 @@ def _backward_native(rs, means3D, radii, colors_precomp, opacities, scales, rota
         buf.num_rendered_host = ws.pinned.data_ptr()
 
         dL_dmeans2D = torch.empty((P, 3), **f32)
-        names, shapes = _grad_layout(P, M, colors_precomp, cov3Ds_precomp, sh_c, scales, rotations)
+        names, shapes = _grad_layout(P, M, colors_precomp, cov3Ds_precomp, sh_c, scales, rotations, split)
         red = _gradient_reducer
         exchange = red is not None and hasattr(red, "use_exchange") and red.use_exchange(names)
         if red is None or exchange:
@@ -301,13 +309,13 @@ def _backward_native(rs, means3D, radii, colors_precomp, opacities, scales, rota
             red.begin()
             io = GsrBackwardIO(grad_out_color.data_ptr(), _ptr(grad_out_depth), None, dL_dmeans2D.data_ptr(),
                                None, None, None, None, None, None, int(getattr(red, "multicast", True)), 0,
-                               mcast["records"], mcast["rgb"], mcast["campos"])
+                               mcast["records"], mcast["rgb"], mcast["campos"], None)
             _lib.check(lib.gsr_backward(C.byref(p), C.byref(buf), R, radii.data_ptr(), C.byref(io),
                                         stream.cuda_stream))
             red.end()
             _lib.check(lib.gsr_exchange_expand(C.byref(p), red.world, local["records"], local["rgb"], local["campos"],
                                                addr["means3D"], addr["opacity"], addr["sh"], addr["scales"],
-                                               addr["rotations"], stream.cuda_stream))
+                                               addr["rotations"], addr.get("sh_dc"), stream.cuda_stream))
         else:
             if red is not None:
                 red.begin()
@@ -315,7 +323,7 @@ def _backward_native(rs, means3D, radii, colors_precomp, opacities, scales, rota
                                dL_dmeans2D.data_ptr(), addr["opacity"], addr.get("colors"), addr.get("cov3D"),
                                addr.get("sh"), addr.get("scales"), addr.get("rotations"),
                                0 if red is None else 1, 0 if red is None else int(getattr(red, "bands", 0)),
-                               None, None, None)
+                               None, None, None, addr.get("sh_dc"))
             _lib.check(lib.gsr_backward(C.byref(p), C.byref(buf), R, radii.data_ptr(), C.byref(io),
                                         stream.cuda_stream))
             if red is not None:
@@ -323,32 +331,37 @@ def _backward_native(rs, means3D, radii, colors_precomp, opacities, scales, rota
         dL_dmeans3D, dL_dopacity = outs["means3D"], outs["opacity"]
         dL_dcolors, dL_dcov3D, dL_dsh = outs.get("colors"), outs.get("cov3D"), outs.get("sh")
         dL_dscales, dL_drotations = outs.get("scales"), outs.get("rotations")
-    return dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations
+    ret = (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations)
+    return ret + (outs["sh_dc"],) if split else ret
 
 
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
-                        raster_settings):
+                        raster_settings, dc=None):
     return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
-                                     cov3Ds_precomp, raster_settings)
+                                     cov3Ds_precomp, raster_settings, dc)
 
 
 class _RasterizeGaussians(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
-                raster_settings):
+                raster_settings, dc=None):
+        """The reference's nine arguments (__init__.py:49-62) + `dc`: split SH storage (degree-0 coefficients
+        (P,1,3) separate from `sh` = coefficients 1..M-1), read by the kernels in place — no concatenation."""
+        split = dc is not None
         red = _gradient_reducer
         if red is not None and any(ctx.needs_input_grad) and means3D.shape[0] > 0 and hasattr(red, "prepare"):
             # view-parallel: clear the symmetric gradient buffer + rank barrier overlap the forward
-            M = sh.shape[1] if _present(sh) else 0
-            names, shapes = _grad_layout(means3D.shape[0], M, colors_precomp, cov3Ds_precomp, sh, scales, rotations)
+            M = (sh.shape[1] if _present(sh) else 0) + (1 if split else 0)
+            names, shapes = _grad_layout(means3D.shape[0], M, colors_precomp, cov3Ds_precomp, sh, scales, rotations, split)
             xchg = hasattr(red, "use_exchange") and red.use_exchange(names)
             red.prepare(shapes, means3D.device, exchange_P=means3D.shape[0] if xchg else None)
         num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, invdepths = _forward_native(
-            raster_settings, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp)
+            raster_settings, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, dc=dc)
         ctx.raster_settings = raster_settings
         ctx.num_rendered = num_rendered
+        ctx.split = split
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, opacities,
-                              geomBuffer, binningBuffer, imgBuffer)
+                              geomBuffer, binningBuffer, imgBuffer, *((dc,) if split else ()))
         ctx.mark_non_differentiable(radii)
         return color, radii, invdepths
 
@@ -357,11 +370,12 @@ class _RasterizeGaussians(torch.autograd.Function):
         num_rendered = ctx.num_rendered
         raster_settings = ctx.raster_settings
         (colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, opacities,
-         geomBuffer, binningBuffer, imgBuffer) = ctx.saved_tensors
+         geomBuffer, binningBuffer, imgBuffer, *rest) = ctx.saved_tensors
+        dc = rest[0] if ctx.split else None
         (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh,
-         grad_scales, grad_rotations) = _backward_native(
+         grad_scales, grad_rotations, *grad_dc) = _backward_native(
             raster_settings, means3D, radii, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
-            grad_out_color, grad_out_depth, sh, geomBuffer, num_rendered, binningBuffer, imgBuffer)
+            grad_out_color, grad_out_depth, sh, geomBuffer, num_rendered, binningBuffer, imgBuffer, dc=dc)
         grads = (
             grad_means3D,
             grad_means2D,
@@ -372,6 +386,7 @@ class _RasterizeGaussians(torch.autograd.Function):
             grad_rotations,
             grad_cov3Ds_precomp,
             None,
+            grad_dc[0] if grad_dc else None,
         )
         return grads
 
@@ -411,7 +426,10 @@ class GaussianRasterizer(nn.Module):
         if dc is not None:
             if colors_precomp is not None:
                 raise Exception('Please provide exactly one of either SHs or precomputed colors!')
-            shs = dc if shs is None or shs.numel() == 0 else torch.cat((dc, shs), dim=1)
+            if shs is None or shs.numel() == 0:
+                shs, dc = dc, None               # degree-0 model: dc alone is the dense layout
+            elif dc.dim() != 3 or dc.shape[1] != 1 or dc.shape[0] != shs.shape[0]:
+                raise Exception('dc must have dimensions (num_points, 1, 3)')
 
         if (shs is None and colors_precomp is None) or (shs is not None and colors_precomp is not None):
             raise Exception('Please provide exactly one of either SHs or precomputed colors!')
@@ -442,4 +460,5 @@ class GaussianRasterizer(nn.Module):
             rotations,
             cov3D_precomp,
             raster_settings,
+            dc,
         )

@@ -178,7 +178,7 @@ class FusedGradientReducer:
 
     def use_exchange(self, names) -> bool:
         """Factored exchange (csrc/exchange.cu): SH + scale/rotation inputs, i.e. the training configuration."""
-        return self.factored and list(names) == self.EXCHANGE_NAMES
+        return self.factored and [n for n in names if n != "sh_dc"] == self.EXCHANGE_NAMES
 
     def exchange_buffers(self, P, device):
         """Symmetric buffer of the factored exchange: records [P][12] | rgb [world][P][4] | campos [world][4].

@@ -77,6 +77,11 @@ typedef struct GsrParams {
     const float* viewmatrix;     /* 16, column-major W2V   (auxiliary.h:75-95) */
     const float* projmatrix;     /* 16, column-major Proj*W2V */
     const float* campos;         /* 3 */
+    /* Split SH storage (the reference's separate_sh call, gaussian_renderer/__init__.py:115-125: `dc=` and `shs=`
+     * are separate tensors, as scene/gaussian_model.py keeps _features_dc / _features_rest).  When sh_dc != NULL,
+     * coefficient 0 of every Gaussian is read from sh_dc [P][3] and `shs` holds coefficients 1..M-1 as
+     * [P][M-1][3]; M still counts all coefficients (M >= 2).  No concatenated copy is ever made. */
+    const float* sh_dc;
 } GsrParams;
 
 /* Caller-owned state and scratch.  geom/img/bin are kept alive by the caller
@@ -128,6 +133,7 @@ typedef struct GsrBackwardIO {
     float* xchg_records;   /* P*12: {dL_dmeans3D xyz, dL_dopacity, dL_dscales xyz, 0, dL_drotations wxyz}, summed over ranks */
     float* xchg_rgb;       /* this rank's slot of [world][P][4]: {dL_dR, dL_dG, dL_dB, 0} */
     float* xchg_campos;    /* this rank's slot of [world][4]:    {campos xyz, 1} */
+    float* dL_dsh_dc;      /* split SH storage (GsrParams.sh_dc): P*3; dL_dsh then is P*(M-1)*3 */
 } GsrBackwardIO;
 
 int         gsr_version(void);
@@ -170,7 +176,8 @@ int gsr_backward(const GsrParams* p, const GsrBuffers* buf, int64_t R,
 int gsr_exchange_expand(const GsrParams* p, int32_t world, const float* records /* P*12 */,
                         const float* rgb /* world*P*4 */, const float* campos /* world*4 */,
                         float* dL_dmeans3D, float* dL_dopacity, float* dL_dsh, float* dL_dscales,
-                        float* dL_drotations, void* stream);
+                        float* dL_drotations, float* dL_dsh_dc /* split SH storage: P*3, dL_dsh is P*(M-1)*3; else NULL */,
+                        void* stream);
 
 /* present[i] = (W2V * p_i).z > 0.2   (rasterizer_impl.cu:56-73). present is P bytes (bool). */
 int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,

@@ -54,7 +54,7 @@ def test_struct_layouts_match_header():
             fields.append(first)
             fields += [n.strip() for n in names[1:]]
         assert fields == [f[0] for f in cls._fields_], name
-    assert C.sizeof(_lib.GsrParams) == 12 * 4 + 11 * 8
+    assert C.sizeof(_lib.GsrParams) == 12 * 4 + 12 * 8
     assert C.sizeof(_lib.GsrBuffers) == 9 * 8
     assert C.sizeof(_lib.GsrSsimParams) == 2 * 8 + 8 * 4        # 7 ints/floats + tail padding
 

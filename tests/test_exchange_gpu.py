@@ -30,7 +30,7 @@ class LocalExchange:
         self.begun = self.ended = self.prepared = 0
 
     def use_exchange(self, names):
-        return list(names) == ["means3D", "opacity", "sh", "scales", "rotations"]
+        return [n for n in names if n != "sh_dc"] == ["means3D", "opacity", "sh", "scales", "rotations"]
 
     def exchange_buffers(self, P, device):
         n = 12 * P + 4 * P + 4
@@ -124,7 +124,7 @@ def test_exchange_two_views_emulated():
     p.P, p.D, p.M, p.means3D = P, 3, 16, leaves["means3D"].data_ptr()
     _lib.check(lib.gsr_exchange_expand(C.byref(p), 2, records.data_ptr(), rgb.data_ptr(), campos.data_ptr(),
                                        outs["means3D"].data_ptr(), outs["opacities"].data_ptr(), outs["shs"].data_ptr(),
-                                       outs["scales"].data_ptr(), outs["rotations"].data_ptr(),
+                                       outs["scales"].data_ptr(), outs["rotations"].data_ptr(), None,
                                        torch.cuda.current_stream().cuda_stream))
     for k, t in outs.items():
         assert rel_err(t.cpu().numpy(), want[k].reshape(t.shape)) < 1e-5, k
@@ -140,11 +140,11 @@ def test_exchange_argument_checks():
     p.P, p.D, p.M = 10, 3, 16
     buf = torch.zeros(1024, device="cuda")
     a = buf.data_ptr()
-    assert lib.gsr_exchange_expand(C.byref(p), 0, a, a, a, a, a, None, a, a, None) == _lib.GSR_ERR_INVALID_ARG
-    assert lib.gsr_exchange_expand(C.byref(p), 2, a + 4, a, a, a, a, None, a, a, None) == _lib.GSR_ERR_INVALID_ARG
+    assert lib.gsr_exchange_expand(C.byref(p), 0, a, a, a, a, a, None, a, a, None, None) == _lib.GSR_ERR_INVALID_ARG
+    assert lib.gsr_exchange_expand(C.byref(p), 2, a + 4, a, a, a, a, None, a, a, None, None) == _lib.GSR_ERR_INVALID_ARG
     assert b"aligned" in lib.gsr_last_error()
     p.D, p.M = 3, 4
-    assert lib.gsr_exchange_expand(C.byref(p), 2, a, a, a, a, a, None, a, a, None) == _lib.GSR_ERR_INVALID_ARG
+    assert lib.gsr_exchange_expand(C.byref(p), 2, a, a, a, a, a, None, a, a, None, None) == _lib.GSR_ERR_INVALID_ARG
     p.P = 0
     p.M = 16
-    assert lib.gsr_exchange_expand(C.byref(p), 1, None, None, None, None, None, None, None, None, None) == _lib.GSR_OK
+    assert lib.gsr_exchange_expand(C.byref(p), 1, None, None, None, None, None, None, None, None, None, None) == _lib.GSR_OK
