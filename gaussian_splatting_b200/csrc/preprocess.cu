@@ -14,11 +14,14 @@ constexpr int PRE_THREADS = 128;
 constexpr int PRE_WARPS = PRE_THREADS / 32;
 constexpr int SH_ROW = 48;            // floats per Gaussian at degree 3
 constexpr int SH_ROW_PAD = SH_ROW + 1; // conflict-free per-lane row reads
+constexpr int SPLIT_OFF = 96;            // split SH storage: the rest block follows the 32 x 3 dc block
 
 // SH -> RGB for one colour channel; `sh` points at coefficient 0 of this Gaussian in
 // shared memory with channel stride 3.  Summation order of forward.cu:36-66.
-__device__ __forceinline__ float sh_channel(const float* sh, int deg, float x, float y, float z) {
-    float result = GSR_SH_C0 * sh[0];
+// `lo` points at coefficient 0 of the channel, `sh` is the base for coefficients 1.. (sh[3k] = coefficient k);
+// dense rows: lo == sh.  Split storage: lo in the dc block, sh = rest row - 3.
+__device__ __forceinline__ float sh_channel(const float* lo, const float* sh, int deg, float x, float y, float z) {
+    float result = GSR_SH_C0 * lo[0];
     if (deg > 0) {
         result = result - GSR_SH_C1 * y * sh[3] + GSR_SH_C1 * z * sh[6] - GSR_SH_C1 * x * sh[9];
         if (deg > 1) {
@@ -49,7 +52,7 @@ __global__ void __launch_bounds__(PRE_THREADS)
 preprocess_fwd_kernel(GsrParams p, float focal_x, float focal_y, int gx, int gy,
                       GsRecord* __restrict__ rec, uint2* __restrict__ rects,
                       uint64_t* __restrict__ depth_keys, int32_t* __restrict__ radii) {
-    __shared__ float sh_smem[PRE_WARPS][32 * SH_ROW_PAD];
+    __shared__ __align__(16) float sh_smem[PRE_WARPS][32 * SH_ROW_PAD];
     __shared__ float s_view[16], s_proj[16], s_cam[3];
     if (threadIdx.x < 16) {
         s_view[threadIdx.x] = p.viewmatrix[threadIdx.x];
@@ -138,26 +141,33 @@ preprocess_fwd_kernel(GsrParams p, float focal_x, float focal_y, int gx, int gy,
             const int row = 3 * p.M;                      // floats stored per Gaussian
             float* ws = sh_smem[warp];
             const float* src = p.shs + (size_t)warp_base * row;
-            if (p.sh_dc != nullptr) {
-                // split storage: coefficient 0 from sh_dc [P][3], coefficients 1.. from shs [P][M-1][3]; both
-                // blocks of the warp's 32 Gaussians are contiguous, so the scalar loads stay coalesced
-                const int rrow = row - 3;
+            const bool split = p.sh_dc != nullptr;
+            const int rrow = row - 3;                     // split storage: floats per rest row
+            if (split) {
+                // split storage: coefficient 0 from sh_dc [P][3], coefficients 1.. from shs [P][M-1][3].  The two
+                // blocks of the warp's 32 Gaussians are contiguous in global memory and are kept FLAT in shared
+                // memory (dc block, then the rest block at SPLIT_OFF): a lane reads its rest row at stride
+                // rrow (odd: conflict-free), so no transposition is needed.
+                const int nvalid = min(32, p.P - warp_base);
                 const float* dc = p.sh_dc + (size_t)warp_base * 3;
                 const float* rest = p.shs + (size_t)warp_base * rrow;
-                for (int i = lane; i < 32 * 3; i += 32) {
-                    int g = i / 3, k = i - g * 3;
-                    if ((vis_mask >> g) & 1u) ws[g * SH_ROW_PAD + k] = __ldg(dc + i);
-                }
-                const int Lr = L - 3;
-                if (Lr == rrow) {                 // all stored coefficients are active: one flat, contiguous sweep
-                    for (int i = lane; i < 32 * rrow; i += 32) {
-                        int g = i / rrow, k = i - g * rrow;
-                        if ((vis_mask >> g) & 1u) ws[g * SH_ROW_PAD + 3 + k] = __ldg(rest + i);
+                const bool al = ((reinterpret_cast<uintptr_t>(p.sh_dc) | reinterpret_cast<uintptr_t>(p.shs)) & 15) == 0 &&
+                                (nvalid & 3) == 0;
+                if (al && __popc(vis_mask) >= 12) {       // mostly visible: whole blocks, 16 B accesses
+                    const int n0 = (nvalid * 3) >> 2, n1 = (nvalid * rrow) >> 2;
+                    for (int i = lane; i < n0; i += 32)
+                        reinterpret_cast<float4*>(ws)[i] = __ldg(reinterpret_cast<const float4*>(dc) + i);
+                    for (int i = lane; i < n1; i += 32)
+                        reinterpret_cast<float4*>(ws + SPLIT_OFF)[i] = __ldg(reinterpret_cast<const float4*>(rest) + i);
+                } else {                                  // sparse: only the rows of visible Gaussians
+                    for (int i = lane; i < 32 * 3; i += 32) {
+                        const int g = i / 3;
+                        if ((vis_mask >> g) & 1u) ws[i] = __ldg(dc + i);
                     }
-                } else {
-                    for (int i = lane; i < 32 * Lr; i += 32) {
-                        int g = i / Lr, k = i - g * Lr;
-                        if ((vis_mask >> g) & 1u) ws[g * SH_ROW_PAD + 3 + k] = __ldg(rest + (size_t)g * rrow + k);
+                    const int Lr = L - 3;
+                    for (unsigned m = vis_mask; m != 0; m &= m - 1) {
+                        const int g = __ffs(m) - 1;
+                        for (int k = lane; k < Lr; k += 32) ws[SPLIT_OFF + g * rrow + k] = __ldg(rest + (size_t)g * rrow + k);
                     }
                 }
             } else if ((L & 3) == 0 && (row & 3) == 0) {
@@ -182,10 +192,11 @@ preprocess_fwd_kernel(GsrParams p, float focal_x, float focal_y, int gx, int gy,
                 float dx = p_orig.x - s_cam[0], dy = p_orig.y - s_cam[1], dz = p_orig.z - s_cam[2];
                 float len = sqrtf(dx * dx + dy * dy + dz * dz);
                 dx = dx / len; dy = dy / len; dz = dz / len;
-                const float* mysh = ws + lane * SH_ROW_PAD;
+                const float* lo = split ? ws + lane * 3 : ws + lane * SH_ROW_PAD;
+                const float* hi = split ? ws + SPLIT_OFF + lane * rrow - 3 : lo;
 #pragma unroll
                 for (int c = 0; c < 3; c++) {
-                    float v = sh_channel(mysh + c, p.D, dx, dy, dz);
+                    float v = sh_channel(lo + c, hi + c, p.D, dx, dy, dz);
                     if (v < 0.f) clamped_bits |= (1 << c);
                     rgb[c] = fmaxf(v, 0.0f);
                 }
