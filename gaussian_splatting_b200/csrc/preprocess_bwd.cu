@@ -168,14 +168,14 @@ struct RowLayout { int kind; int rowlen; };
 constexpr int SPLIT_REST_OFF = 96;
 
 // SH backward for this lane's row, through registers.  STORE: write the coefficient gradients back in place.
-template <bool STORE>
+template <bool STORE, int KIND>
 __device__ __forceinline__ float3 sh_backward_smem(float* ws, int lane, RowLayout lay, int deg, float3 dir_orig,
                                                    const float dL_dRGB[3]) {
-    if (lay.kind == 0) return sh_backward<STORE>(ws + lane * PB_STRIDE_SCALAR, lay.rowlen, deg, dir_orig, dL_dRGB);
+    if (KIND == 0) return sh_backward<STORE>(ws + lane * PB_STRIDE_SCALAR, lay.rowlen, deg, dir_orig, dL_dRGB);
     float sh[PB_ROW];
     const int rowlen = lay.rowlen, rest = rowlen - 3;
     float4* row4 = reinterpret_cast<float4*>(ws + lane * rowlen);
-    if (lay.kind == 1) {
+    if (KIND == 1) {
 #pragma unroll
         for (int m = 0; m < PB_ROW / 4; m++) {
             const float4 v = row4[m];
@@ -189,7 +189,7 @@ __device__ __forceinline__ float3 sh_backward_smem(float* ws, int lane, RowLayou
     }
     const float3 r = sh_backward<STORE>(sh, rowlen, deg, dir_orig, dL_dRGB);
     if (STORE) {
-        if (lay.kind == 1) {
+        if (KIND == 1) {
             const int n4 = rowlen >> 2;
 #pragma unroll
             for (int m = 0; m < PB_ROW / 4; m++)
@@ -206,11 +206,12 @@ __device__ __forceinline__ float3 sh_backward_smem(float* ws, int lane, RowLayou
 }
 
 // zero gradient row of a culled Gaussian
+template <int KIND>
 __device__ __forceinline__ void row_zero(float* ws, int lane, RowLayout lay) {
     const int rowlen = lay.rowlen;
-    if (lay.kind == 0) {
+    if (KIND == 0) {
         for (int k = 0; k < rowlen; k++) ws[lane * PB_STRIDE_SCALAR + k] = 0.f;
-    } else if (lay.kind == 1) {
+    } else if (KIND == 1) {
         for (int k = 0; k < (rowlen >> 2); k++) reinterpret_cast<float4*>(ws + lane * rowlen)[k] = make_float4(0.f, 0.f, 0.f, 0.f);
     } else {
         for (int k = 0; k < 3; k++) ws[lane * 3 + k] = 0.f;
@@ -254,7 +255,9 @@ __device__ __forceinline__ void cov3D_backward(float3 scale, float mod, float4 r
     dL_drot->w = 2 * r * (D.m[0][1] - D.m[1][0]) + 2 * x * (D.m[2][0] + D.m[0][2]) + 2 * y * (D.m[1][2] + D.m[2][1]) - 4 * z * (D.m[1][1] + D.m[0][0]);
 }
 
-template <bool VEC, bool MM>
+// SPLIT: split SH storage (GsrParams.sh_dc).  A template parameter so that the dense instantiation carries none
+// of the split layout's code (the runtime-flag version cost the dense path 16 %).
+template <bool VEC, bool MM, bool SPLIT>
 __global__ void __launch_bounds__(PB_THREADS, PB_MIN_BLOCKS)
 preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord* __restrict__ rec,
                       const int32_t* __restrict__ radii, const float* __restrict__ acc,
@@ -298,7 +301,7 @@ preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord*
     const uint32_t sh_bytes = (uint32_t)(nvalid * sh_row) * 4u;
     // Split SH storage (GsrParams.sh_dc): the warp's 32 dc rows (96 floats) and 32 rest rows are two contiguous
     // blocks; in shared memory the dc block comes first, the rest block follows at SPLIT_REST_OFF.
-    const bool split = p.sh_dc != nullptr;
+    constexpr bool split = SPLIT;
     const int rest_row = sh_row - 3;
     // bulk copies need 16 B multiples: a ragged last warp (nvalid % 4 != 0) of the split layout is copied by the lanes
     const bool bulk_ok = !split || (nvalid & 3) == 0;
@@ -447,7 +450,8 @@ preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord*
     const bool fact = io.xchg_records != nullptr;
     if (has_sh && (fact || io.dL_dsh != nullptr)) {
         float* ws = sh_smem[warp];
-        const RowLayout lay = {VEC ? (split ? 2 : 1) : 0, sh_row};
+        constexpr int KIND = VEC ? (SPLIT ? 2 : 1) : 0;
+        const RowLayout lay = {KIND, sh_row};
         float dL_dRGB[3];
 #pragma unroll
         for (int c = 0; c < 3; c++) dL_dRGB[c] = ((clamped_bits >> c) & 1) ? 0.f : dL_dcolor[c];
@@ -478,7 +482,7 @@ preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord*
         // every receiver (exchange.cu).  16 B multimem operations only; culled rows are not touched.
         if (fact) {
             if (visible) {
-                const float3 dm = sh_backward_smem<false>(ws, lane, lay, p.D, dir_orig, dL_dRGB);
+                const float3 dm = sh_backward_smem<false, KIND>(ws, lane, lay, p.D, dir_orig, dL_dRGB);
                 dL_dmean.x += dm.x; dL_dmean.y += dm.y; dL_dmean.z += dm.z;
             }
             if (blockIdx.x == 0 && threadIdx.x == 0)
@@ -498,10 +502,10 @@ preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord*
         }
         // ---- SH backward in place; dL_dsh rows leave coalesced ----
         if (visible) {
-            const float3 dm = sh_backward_smem<true>(ws, lane, lay, p.D, dir_orig, dL_dRGB);
+            const float3 dm = sh_backward_smem<true, KIND>(ws, lane, lay, p.D, dir_orig, dL_dRGB);
             dL_dmean.x += dm.x; dL_dmean.y += dm.y; dL_dmean.z += dm.z;
         } else {
-            row_zero(ws, lane, lay);
+            row_zero<KIND>(ws, lane, lay);
         }
         if (VEC && MM && LIST) {
             // 16 B multimem reductions, 12 consecutive lanes per (scattered) Gaussian row
@@ -679,12 +683,14 @@ int launch_preprocess_backward(const GsrParams& p, GeomState g, Scratch s, const
                      (split ? al16(p.sh_dc) && (fact || (al16(io.dL_dsh) && al16(io.dL_dsh_dc)))
                             : (p.M & 3) == 0 && (fact || al16(io.dL_dsh)));
     const bool mm = io.multimem_reduce != 0;
-#define PB_LAUNCH(V, M) GSR_LAUNCH((preprocess_bwd_kernel<V, M>), blocks, PB_THREADS, 0, st, p, focal_x, focal_y, g.rec, \
-                                   radii, s.acc, have_invdepth, io, blist, s.band_ctl, band)
-    if (vec && mm) PB_LAUNCH(true, true);
-    else if (vec) PB_LAUNCH(true, false);
-    else if (mm) PB_LAUNCH(false, true);
-    else PB_LAUNCH(false, false);
+#define PB_LAUNCH(V, M, S) GSR_LAUNCH((preprocess_bwd_kernel<V, M, S>), blocks, PB_THREADS, 0, st, p, focal_x, focal_y, g.rec, \
+                                      radii, s.acc, have_invdepth, io, blist, s.band_ctl, band)
+#define PB_LAUNCH2(V, M) do { if (split) PB_LAUNCH(V, M, true); else PB_LAUNCH(V, M, false); } while (0)
+    if (vec && mm) PB_LAUNCH2(true, true);
+    else if (vec) PB_LAUNCH2(true, false);
+    else if (mm) PB_LAUNCH2(false, true);
+    else PB_LAUNCH2(false, false);
+#undef PB_LAUNCH2
 #undef PB_LAUNCH
     return check_stage("preprocess backward", p.debug, st);
 }

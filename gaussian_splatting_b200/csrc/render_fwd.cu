@@ -102,27 +102,33 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
 
         const uint8_t* sl = s_list[warp];
         const uint32_t base = (uint32_t)k * RF_BATCH;
-        for (int jj = 0; !done && jj < cntw; jj++) {
+        // Warp-uniform loop, branch-free body: the reference's rejections (power > 0, alpha < 1/255, pixel
+        // already saturated; forward.cu:468-487) zero the blend weight instead of skipping, which leaves C, T
+        // and last_contributor bit-identical (fma(T, 0, C) == C).
+        for (int jj = 0; jj < cntw; jj++) {
             const int j = sl[jj];
             const float4 q0 = sr[j * 3 + 0];      // x, y, conic.x, conic.y
             const float4 q1 = sr[j * 3 + 1];      // conic.z, opacity, r, g
             const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
             const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
-            if (power > 0.0f) continue;
             const float alpha = fminf(0.99f, q1.y * expf(power));
-            if (alpha < 1.0f / 255.0f) continue;
+            bool ok = !done && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
             const float test_T = T * (1 - alpha);
-            if (test_T < 0.0001f) {
-                done = true;
+            const bool stop = ok && test_T < 0.0001f;
+            done = done || stop;
+            ok = ok && !stop;
+            if (!__any_sync(0xffffffffu, ok)) {
+                if (__all_sync(0xffffffffu, done)) break;
                 continue;
             }
             const float4 q2 = sr[j * 3 + 2];      // b, 1/depth, depth, radius
-            C[0] += q1.z * alpha * T;
-            C[1] += q1.w * alpha * T;
-            C[2] += q2.x * alpha * T;
-            expected_invdepth += q2.y * alpha * T;
-            T = test_T;
-            last_contributor = base + j + 1;
+            const float a = ok ? alpha : 0.f;
+            C[0] += q1.z * a * T;
+            C[1] += q1.w * a * T;
+            C[2] += q2.x * a * T;
+            expected_invdepth += q2.y * a * T;
+            T = ok ? test_T : T;
+            last_contributor = ok ? base + j + 1 : last_contributor;
         }
         __syncwarp();                              // s_list is rebuilt next round
     }
