@@ -305,8 +305,10 @@ def rooflines(stage_ms, work, peaks, sm_mhz):
 
 def ncu_evidence(stage):
     """DRAM traffic per launch and issue-slot utilisation of a stage's kernel from the committed
-    `ncu --set full` capture of this same workload (profiles/r01f_kernels.json); None if absent."""
-    path = os.path.join(ROOT, "profiles", "r01f_kernels.json")
+    `ncu --set full` capture of this same workload (newest profiles/r*_kernels.json); None if absent."""
+    import glob
+    found = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_kernels.json")))
+    path = found[-1] if found else ""
     kernel = {"render_bwd": "render_bwd_kernel", "render_fwd": "render_fwd_kernel",
               "preprocess_bwd": "preprocess_bwd_kernel", "preprocess": "preprocess_fwd_kernel"}.get(stage)
     if kernel is None or not os.path.exists(path):
@@ -314,7 +316,8 @@ def ncu_evidence(stage):
     for k in json.load(open(path)):
         if k["kernel"].startswith(kernel):
             return dict(traffic=int((k["dram_read_MB"] + k["dram_write_MB"]) * 1e6),
-                        issue_active=round(k["issue_active_pct"] / 100.0, 3), source="profiles/r01f_kernels.json")
+                        issue_active=round(k["issue_active_pct"] / 100.0, 3),
+                        source="profiles/" + os.path.basename(path))
     return None
 
 

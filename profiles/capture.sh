@@ -4,7 +4,7 @@
 # Usage: bash profiles/capture.sh <tag> [kernel-regex] [skip] [count]
 set -u
 TAG=${1:-r01}
-RX=${2:-render_}
+RX=${2:-"^(render|preprocess|onesweep|radix|scan|emit|tile_ranges)"}
 SKIP=${3:-1}
 COUNT=${4:-3}
 CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-e2e"
