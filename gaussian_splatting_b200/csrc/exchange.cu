@@ -58,7 +58,7 @@ __device__ __forceinline__ void sh_basis(int deg, float3 dir_orig, float (&w)[16
 template <bool BULK>
 __global__ void __launch_bounds__(XE_THREADS)
 exchange_expand_kernel(int P, int D, int M, int world, const float* __restrict__ means3D,
-                       const float4* __restrict__ records, const float4* __restrict__ rgb,
+                       float4* __restrict__ records, float4* __restrict__ rgb,
                        const float4* __restrict__ campos, float* __restrict__ dL_dmeans3D,
                        float* __restrict__ dL_dopacity, float* __restrict__ dL_dsh, float* __restrict__ dL_dscales,
                        float* __restrict__ dL_drotations, float* __restrict__ dL_dsh_dc) {
@@ -76,6 +76,13 @@ exchange_expand_kernel(int P, int D, int M, int world, const float* __restrict__
     for (int k = 0; k < XE_ROW; k++) sh[k] = 0.f;
     if (mine) {
         const float4 r0 = records[3 * (size_t)idx], r1 = records[3 * (size_t)idx + 1], r2 = records[3 * (size_t)idx + 2];
+        // Leave the exchange buffers clean for the next step: only rows that received something are rewritten,
+        // so no per-step memset of the whole buffer is needed (the sender skips zeros, multimem.red adds).
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        const auto nz = [](const float4& v) { return v.x != 0.f || v.y != 0.f || v.z != 0.f || v.w != 0.f; };
+        if (nz(r0)) records[3 * (size_t)idx] = z4;
+        if (nz(r1)) records[3 * (size_t)idx + 1] = z4;
+        if (nz(r2)) records[3 * (size_t)idx + 2] = z4;
         if (dL_dmeans3D) {
             dL_dmeans3D[3 * idx] = r0.x; dL_dmeans3D[3 * idx + 1] = r0.y; dL_dmeans3D[3 * idx + 2] = r0.z;
         }
@@ -89,6 +96,7 @@ exchange_expand_kernel(int P, int D, int M, int world, const float* __restrict__
             for (int r = 0; r < world; r++) {
                 const float4 c = rgb[(size_t)r * P + idx];
                 if (c.x == 0.f && c.y == 0.f && c.z == 0.f) continue;
+                rgb[(size_t)r * P + idx] = z4;
                 const float4 cam = s_cam[r];
                 float w[16];
                 sh_basis(D, make_float3(mean.x - cam.x, mean.y - cam.y, mean.z - cam.z), w);
@@ -143,7 +151,7 @@ exchange_expand_kernel(int P, int D, int M, int world, const float* __restrict__
 
 }  // namespace gsr
 
-extern "C" int gsr_exchange_expand(const GsrParams* p, int32_t world, const float* records, const float* rgb,
+extern "C" int gsr_exchange_expand(const GsrParams* p, int32_t world, float* records, float* rgb,
                                    const float* campos, float* dL_dmeans3D, float* dL_dopacity, float* dL_dsh,
                                    float* dL_dscales, float* dL_drotations, float* dL_dsh_dc, void* stream) {
     using namespace gsr;
@@ -171,7 +179,7 @@ extern "C" int gsr_exchange_expand(const GsrParams* p, int32_t world, const floa
     const bool bulk = dL_dsh && p->M == 16 && !misaligned(dL_dsh) && !misaligned(dL_dsh_dc);
     StageTimer tm(GSR_STAGE_PREPROCESS_BWD, st);      // accounted with the per-Gaussian backward
 #define XE_LAUNCH(B) GSR_LAUNCH(exchange_expand_kernel<B>, blocks, XE_THREADS, 0, st, p->P, p->D, p->M, (int)world, \
-                                p->means3D, reinterpret_cast<const float4*>(records), reinterpret_cast<const float4*>(rgb), \
+                                p->means3D, reinterpret_cast<float4*>(records), reinterpret_cast<float4*>(rgb), \
                                 reinterpret_cast<const float4*>(campos), dL_dmeans3D, dL_dopacity, dL_dsh, dL_dscales, \
                                 dL_drotations, dL_dsh_dc)
     if (bulk) XE_LAUNCH(true);

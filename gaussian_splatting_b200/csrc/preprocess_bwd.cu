@@ -485,8 +485,8 @@ preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord*
                 const float3 dm = sh_backward_smem<false, KIND>(ws, lane, lay, p.D, dir_orig, dL_dRGB);
                 dL_dmean.x += dm.x; dL_dmean.y += dm.y; dL_dmean.z += dm.z;
             }
-            if (blockIdx.x == 0 && threadIdx.x == 0)
-                out4<MM>(io.xchg_campos, make_float4(s_cam[0], s_cam[1], s_cam[2], 1.f));
+            if (blockIdx.x == 0 && threadIdx.x == 0)     // a plain store to a multicast address reaches every replica
+                *reinterpret_cast<float4*>(io.xchg_campos) = make_float4(s_cam[0], s_cam[1], s_cam[2], 1.f);
             if (!mine) return;
             if (io.dL_dmeans2D) {
                 io.dL_dmeans2D[3 * idx] = dL_dmean2D.x; io.dL_dmeans2D[3 * idx + 1] = dL_dmean2D.y; io.dL_dmeans2D[3 * idx + 2] = 0.f;

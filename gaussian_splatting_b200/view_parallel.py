@@ -135,6 +135,7 @@ class FusedGradientReducer:
         self.factored = os.environ.get("GSR_REDUCE_FACTORED", "1") != "0"
         self._side = self._ready = None
         self._prepared = False
+        self.self_cleaning = False
 
     @staticmethod
     def available() -> bool:
@@ -165,6 +166,7 @@ class FusedGradientReducer:
             if not self.hdl.multicast_ptr:
                 raise RuntimeError("NVLink multicast (NVLS) is not available for this group: use FlatGradients")
             self.key, self.offs, self.total = key, offs, total
+            self.self_cleaning = False
         views, addrs = [], []
         for shp, off in zip(shapes, self.offs):
             n = 1
@@ -196,6 +198,9 @@ class FusedGradientReducer:
             if not self.hdl.multicast_ptr:
                 raise RuntimeError("NVLink multicast (NVLS) is not available for this group: use FlatGradients")
             self.key, self.offs, self.total = key, [0, o_rgb, o_cam], total
+            # zeroed ONCE: afterwards the expand pass resets exactly the rows that received something
+            self.flat.zero_()
+            self.self_cleaning = True
         rank = dist.get_rank(self.group)
         base, mc = self.flat.data_ptr(), self.hdl.multicast_ptr
         o_rec, o_rgb, o_cam = self.offs
@@ -220,7 +225,8 @@ class FusedGradientReducer:
             self._ready = torch.cuda.Event()
         self._side.wait_stream(main)
         with torch.cuda.stream(self._side):
-            self.flat.zero_()
+            if not self.self_cleaning:
+                self.flat.zero_()
             self.hdl.barrier(channel=0)
             self._ready.record(self._side)
         self._prepared = True
@@ -232,7 +238,8 @@ class FusedGradientReducer:
             torch.cuda.current_stream(self.flat.device).wait_event(self._ready)
             self._prepared = False
             return
-        self.flat.zero_()
+        if not self.self_cleaning:
+            self.flat.zero_()
         self.hdl.barrier(channel=0)
 
     def end(self):

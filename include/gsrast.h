@@ -132,7 +132,7 @@ typedef struct GsrBackwardIO {
      * zeroes the buffers beforehand.  With multimem_reduce = 1 the three pointers are multicast addresses. */
     float* xchg_records;   /* P*12: {dL_dmeans3D xyz, dL_dopacity, dL_dscales xyz, 0, dL_drotations wxyz}, summed over ranks */
     float* xchg_rgb;       /* this rank's slot of [world][P][4]: {dL_dR, dL_dG, dL_dB, 0} */
-    float* xchg_campos;    /* this rank's slot of [world][4]:    {campos xyz, 1} */
+    float* xchg_campos;    /* this rank's slot of [world][4]:    {campos xyz, 1}; stored, not added */
     float* dL_dsh_dc;      /* split SH storage (GsrParams.sh_dc): P*3; dL_dsh then is P*(M-1)*3 */
 } GsrBackwardIO;
 
@@ -172,9 +172,11 @@ int gsr_backward(const GsrParams* p, const GsrBuffers* buf, int64_t R,
 /* Second half of the factored exchange: after every rank's gsr_backward has landed (rank barrier), turn this
  * rank's replica of the exchange buffers into the dense gradient tensors, summed over ranks:
  *   dL_dsh[g] = sum_r basis_D(means3D[g] - campos[r]) x rgb[r][g]   (fixed order r = 0..world-1, deterministic),
- * the other four straight from the records.  Uses p->P, D, M, means3D.  Every output row is written. */
-int gsr_exchange_expand(const GsrParams* p, int32_t world, const float* records /* P*12 */,
-                        const float* rgb /* world*P*4 */, const float* campos /* world*4 */,
+ * the other four straight from the records.  Uses p->P, D, M, means3D.  Every output row is written.
+ * Rows of `records` / `rgb` that held something are reset to zero on the way, so the buffers are clean for the
+ * next step without a memset (the camera slots are plain stores and need no reset). */
+int gsr_exchange_expand(const GsrParams* p, int32_t world, float* records /* P*12 */,
+                        float* rgb /* world*P*4 */, const float* campos /* world*4 */,
                         float* dL_dmeans3D, float* dL_dopacity, float* dL_dsh, float* dL_dscales,
                         float* dL_drotations, float* dL_dsh_dc /* split SH storage: P*3, dL_dsh is P*(M-1)*3; else NULL */,
                         void* stream);

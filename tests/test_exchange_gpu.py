@@ -102,11 +102,15 @@ def test_exchange_two_views_emulated():
         R, color, radii, geom, binb, img, invd = rasterizer._forward_native(
             rs, leaves["means3D"], leaves["shs"], e, leaves["opacities"], leaves["scales"], leaves["rotations"], e)
         rec_v = torch.zeros(P, 12, device=dev)
+        dummy = torch.zeros(P * 16 + 4, device=dev)     # what this "rank" expands locally: nothing
 
         class OneView(LocalExchange):
             def exchange_buffers(self, P_, device):
-                loc = dict(records=rec_v.data_ptr(), rgb=rgb[v].data_ptr(), campos=campos[v].data_ptr())
-                return loc, loc
+                # the kernel publishes into this view's slots ("multicast" side); the rasterizer's own expand
+                # call reads the dummy replica, so the published data survives for the emulated reduction below
+                pub = dict(records=rec_v.data_ptr(), rgb=rgb[v].data_ptr(), campos=campos[v].data_ptr())
+                b = dummy.data_ptr()
+                return dict(records=b, rgb=b + 48 * P_, campos=b + 64 * P_), pub
 
             def begin(self):
                 self.begun += 1
@@ -119,6 +123,9 @@ def test_exchange_two_views_emulated():
             rasterizer.set_gradient_reducer(None)
         records += rec_v                                  # what multimem.red.add does across ranks
     assert torch.allclose(campos[:, :3].cpu(), torch.stack([s["campos"] for _, s in views])) and (campos[:, 3] == 1).all()
+    # a Gaussian seen by both views really gets two contributions
+    both = ((rgb[0, :, :3].abs().sum(1) > 0) & (rgb[1, :, :3].abs().sum(1) > 0)).sum().item()
+    assert both > 50
     outs = {k: torch.empty_like(leaves[k]) for k in ("means3D", "opacities", "shs", "scales", "rotations")}
     p = _lib.GsrParams()
     p.P, p.D, p.M, p.means3D = P, 3, 16, leaves["means3D"].data_ptr()
@@ -128,9 +135,8 @@ def test_exchange_two_views_emulated():
                                        torch.cuda.current_stream().cuda_stream))
     for k, t in outs.items():
         assert rel_err(t.cpu().numpy(), want[k].reshape(t.shape)) < 1e-5, k
-    # a Gaussian seen by both views really got two contributions
-    both = ((rgb[0, :, :3].abs().sum(1) > 0) & (rgb[1, :, :3].abs().sum(1) > 0)).sum().item()
-    assert both > 50
+    # the expand pass leaves the exchange buffers clean for the next step (no per-step memset)
+    assert not records.any() and not rgb.any()
 
 
 def test_exchange_argument_checks():
