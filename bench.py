@@ -419,7 +419,12 @@ def run_gpu_arm(args, module, impl, rank, world, local):
             _lib.profile_enable(True)
             mark["l0"] = _lib.launch_count()
 
-    ms, t0, t1 = timed_loop(step, args.steps, args.warmup, world, device, on_start)
+    from gaussian_splatting_b200 import rasterizer as _rz
+    def on_start_all():
+        on_start()
+        _rz.trace_reset()
+    ms, t0, t1 = timed_loop(step, args.steps, args.warmup, world, device, on_start_all)
+    trace = _rz.trace_summary() if ours else {}
     clocks = sampler.stop(t0, t1)
     line = base_line(args, wl, world, impl)
     if reduce_mode:
@@ -446,8 +451,18 @@ def run_gpu_arm(args, module, impl, rank, world, local):
         peaks = load_peaks()
         stages = rooflines(stage_ms, work, peaks, clocks.get("sm_mhz"))
         line["gpu_launches"] = int(launches)
+        if trace:
+            line["trace_ms"] = trace          # GSR_TRACE_EVENTS=1: mean gaps between phase boundaries on this rank
         line["work"] = work
         line["stages"] = stages
+        if world > 1:
+            # every rank's own kernel time per step (sum of its stages): separates the work imbalance between
+            # the cameras of the ring from waiting at the two rank barriers (value uses the max over ranks)
+            mine = torch.tensor([sum(s["ms"] for s in stages), float(work["R"])], device=device, dtype=torch.float64)
+            allr = [torch.zeros_like(mine) for _ in range(world)]
+            dist.all_gather(allr, mine)
+            line["per_rank"] = {"kernel_ms_per_step": [round(float(t[0]), 3) for t in allr],
+                                "num_rendered": [int(t[1]) for t in allr]}
         top = stages[0]
         line["roofline"] = {"kernel": top["stage"], "bound": top["bound"], "achieved": top["achieved"],
                             "peak": top["peak"], "unit": top["unit"], "frac": top["frac"], "traffic": None,

@@ -11,6 +11,7 @@ path lives in libgsrast.so.  There is no CPU or eager fallback: non-CUDA tensors
 library raise.
 """
 import ctypes as C
+import os
 from typing import NamedTuple
 
 import torch
@@ -96,6 +97,33 @@ def _ptr(t):
 # View-parallel fused reduction (view_parallel.FusedGradientReducer): when set, the backward kernel
 # adds its gradients into NVLink-multicast buffers instead of storing them locally.
 _gradient_reducer = None
+
+
+# Optional timeline probe (GSR_TRACE_EVENTS=1): CUDA events at the phase boundaries of a step on the current
+# stream; trace_summary() turns them into mean gaps.  Diagnostic for the multi-GPU overhead, off by default.
+_TRACE = os.environ.get("GSR_TRACE_EVENTS", "0") == "1"
+_trace_events = []
+
+
+def _trace(name, device):
+    if _TRACE:
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record(torch.cuda.current_stream(device))
+        _trace_events.append((name, ev))
+
+
+def trace_reset():
+    _trace_events.clear()
+
+
+def trace_summary():
+    """{'a->b': mean ms} over consecutive recorded events (call after a device synchronize)."""
+    acc = {}
+    for (n0, e0), (n1, e1) in zip(_trace_events, _trace_events[1:]):
+        k = f"{n0}->{n1}"
+        t, c = acc.get(k, (0.0, 0))
+        acc[k] = (t + e0.elapsed_time(e1), c + 1)
+    return {k: round(t / c, 4) for k, (t, c) in acc.items()}
 
 
 def set_gradient_reducer(reducer):
@@ -306,16 +334,21 @@ def _backward_native(rs, means3D, radii, colors_precomp, opacities, scales, rota
             # factored exchange: the kernel publishes 64 B per contributing Gaussian through the multicast
             # address; after the rank barrier the expand pass rebuilds the dense, summed gradients locally
             local, mcast = red.exchange_buffers(P, device)
+            _trace("bwd0", device)
             red.begin()
+            _trace("begun", device)
             io = GsrBackwardIO(grad_out_color.data_ptr(), _ptr(grad_out_depth), None, dL_dmeans2D.data_ptr(),
                                None, None, None, None, None, None, int(getattr(red, "multicast", True)), 0,
                                mcast["records"], mcast["rgb"], mcast["campos"], None)
             _lib.check(lib.gsr_backward(C.byref(p), C.byref(buf), R, radii.data_ptr(), C.byref(io),
                                         stream.cuda_stream))
+            _trace("sent", device)
             red.end()
+            _trace("barrier", device)
             _lib.check(lib.gsr_exchange_expand(C.byref(p), red.world, local["records"], local["rgb"], local["campos"],
                                                addr["means3D"], addr["opacity"], addr["sh"], addr["scales"],
                                                addr["rotations"], addr.get("sh_dc"), stream.cuda_stream))
+            _trace("expanded", device)
         else:
             if red is not None:
                 red.begin()
@@ -348,6 +381,7 @@ class _RasterizeGaussians(torch.autograd.Function):
         """The reference's nine arguments (__init__.py:49-62) + `dc`: split SH storage (degree-0 coefficients
         (P,1,3) separate from `sh` = coefficients 1..M-1), read by the kernels in place — no concatenation."""
         split = dc is not None
+        _trace("fwd0", means3D.device)
         red = _gradient_reducer
         if red is not None and any(ctx.needs_input_grad) and means3D.shape[0] > 0 and hasattr(red, "prepare"):
             # view-parallel: clear the symmetric gradient buffer + rank barrier overlap the forward
@@ -363,6 +397,7 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, opacities,
                               geomBuffer, binningBuffer, imgBuffer, *((dc,) if split else ()))
         ctx.mark_non_differentiable(radii)
+        _trace("fwd1", means3D.device)
         return color, radii, invdepths
 
     @staticmethod
