@@ -63,6 +63,32 @@ class GsrSsimParams(C.Structure):
     ]
 
 
+DENSIFY_COPY, DENSIFY_MOMENT, DENSIFY_XYZ, DENSIFY_SCALING = 0, 1, 2, 3
+DENSIFY_MAX_TENSORS = 24
+
+
+class GsrDensifyPlanArgs(C.Structure):
+    _fields_ = [
+        ("P", C.c_int32), ("use_screen_size", C.c_int32),
+        ("grad_threshold", C.c_float), ("dense_extent", C.c_float), ("min_opacity", C.c_float),
+        ("max_screen_size", C.c_float), ("world_extent_limit", C.c_float), ("reserved", C.c_int32),
+        ("xyz_gradient_accum", _fp), ("denom", _fp), ("scaling", _fp), ("opacity", _fp), ("prune_mask", _fp),
+    ]
+
+
+class GsrDensifyTensor(C.Structure):
+    _fields_ = [("src", _fp), ("dst", _fp), ("width", C.c_int32), ("kind", C.c_int32)]
+
+
+class GsrDensifyApplyArgs(C.Structure):
+    _fields_ = [
+        ("P", C.c_int32), ("A", C.c_int32), ("B", C.c_int32), ("C", C.c_int32),
+        ("n_tensors", C.c_int32), ("reserved", C.c_int32),
+        ("scaling", _fp), ("rotation", _fp), ("noise", _fp), ("noise_stride", C.c_int64),
+        ("tensors", GsrDensifyTensor * DENSIFY_MAX_TENSORS),
+    ]
+
+
 # every symbol include/gsrast.h declares (tests check that the library exports all of them)
 EXPORTS = (
     "gsr_version", "gsr_last_error", "gsr_geom_bytes", "gsr_img_bytes", "gsr_bin_bytes",
@@ -71,6 +97,8 @@ EXPORTS = (
     "gsr_debug_count_work",
     "gsr_profile_enable", "gsr_profile_collect", "gsr_stage_name", "gsr_launch_count", "gsr_adam_update",
     "gsr_ssim_partials", "gsr_ssim_forward", "gsr_ssim_backward", "gsr_exchange_expand",
+    "gsr_densify_plan_words", "gsr_densify_plan", "gsr_densify_apply", "gsr_densify_stats", "gsr_reset_opacity",
+    "gsr_ply_pack", "gsr_ply_unpack",
 )
 STAGE_COUNT = 9
 
@@ -134,6 +162,20 @@ def load():
     lib.gsr_ssim_forward.argtypes = [PS] + [C.c_void_p] * 7
     lib.gsr_ssim_backward.restype = C.c_int
     lib.gsr_ssim_backward.argtypes = [PS] + [C.c_void_p] * 7
+    lib.gsr_densify_plan_words.restype = C.c_int64
+    lib.gsr_densify_plan_words.argtypes = [C.c_int32]
+    lib.gsr_densify_plan.restype = C.c_int
+    lib.gsr_densify_plan.argtypes = [C.POINTER(GsrDensifyPlanArgs), C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.gsr_densify_apply.restype = C.c_int
+    lib.gsr_densify_apply.argtypes = [C.POINTER(GsrDensifyApplyArgs), C.c_void_p, C.c_void_p]
+    lib.gsr_densify_stats.restype = C.c_int
+    lib.gsr_densify_stats.argtypes = [C.c_int32] + [C.c_void_p] * 7
+    lib.gsr_reset_opacity.restype = C.c_int
+    lib.gsr_reset_opacity.argtypes = [C.c_int32] + [C.c_void_p] * 4
+    lib.gsr_ply_pack.restype = C.c_int
+    lib.gsr_ply_pack.argtypes = [C.c_int32, C.c_int32] + [C.c_void_p] * 8
+    lib.gsr_ply_unpack.restype = C.c_int
+    lib.gsr_ply_unpack.argtypes = [C.c_int32, C.c_int32] + [C.c_void_p] * 8
     _lib = lib
     return lib
 

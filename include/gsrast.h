@@ -221,6 +221,86 @@ int gsr_ssim_backward(const GsrSsimParams* p, const float* dL_dmap, const float*
                       const float* dm_dmu1, const float* dm_dsigma1_sq, const float* dm_dsigma12,
                       float* dL_dimg1, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Adaptive density control on the device.  Replaces the tensor surgery of
+ * GaussianModel.densify_and_prune / densify_and_clone / densify_and_split / prune_points /
+ * cat_tensors_to_optimizer / _prune_optimizer (scene/gaussian_model.py:414-621), reset_opacity
+ * (:323-327) and add_densification_stats (:630-633, with train.py:212-213) — in the reference ~150
+ * torch kernels with a host synchronisation per boolean-mask index — by a plan/apply pair:
+ *   gsr_densify_plan   one pass over the P Gaussians decides keep / clone / split / prune for every
+ *                      row the reference would produce and scans the decisions into destination rows;
+ *   gsr_densify_apply  ONE launch moves every parameter tensor and both Adam moments to their final
+ *                      rows, computing the children's position and scale on the way.
+ * Result layout = the reference's: [surviving originals][clones][first children][second children],
+ * each in source order (cat at :470-484, prune at :549-550 and :611).
+ *
+ * `plan` is caller-owned device scratch of gsr_densify_plan_words(P) 32-bit words; `counts_host` is pinned host
+ * memory for 4 int32 {A = surviving originals, B = clones, C = split sources whose children survive,
+ * P_new = A + B + 2C}, written by an async copy on `stream`: the caller waits for the stream, allocates
+ * the P_new-row outputs and calls gsr_densify_apply with the same plan and the counts. */
+typedef struct GsrDensifyPlanArgs {
+    int32_t P;
+    int32_t use_screen_size;         /* `if max_screen_size:` (gaussian_model.py:600) */
+    float grad_threshold;            /* max_grad */
+    float dense_extent;              /* percent_dense * scene_extent, rounded to fp32 (:515,555) */
+    float min_opacity;               /* :598 */
+    float max_screen_size;           /* :601: compared with max_radii2D, which :508 has just zeroed */
+    float world_extent_limit;        /* 0.1 * extent (:602) */
+    int32_t reserved;
+    const float* xyz_gradient_accum; /* P   (:589)  NULL with prune_mask */
+    const float* denom;              /* P */
+    const float* scaling;            /* P*3 raw (pre-exp) */
+    const float* opacity;            /* P   raw (pre-sigmoid) */
+    const uint8_t* prune_mask;       /* non-NULL: plain prune_points(mask) (:433-451): row i survives iff !mask[i];
+                                        every other input is ignored */
+} GsrDensifyPlanArgs;
+
+#define GSR_DENSIFY_COPY     0   /* parameter or statistic: copied to every row derived from the source */
+#define GSR_DENSIFY_MOMENT   1   /* Adam moment: copied for surviving originals, zero for new rows (:462-466) */
+#define GSR_DENSIFY_XYZ      2   /* children: R(rotation) * (exp(scaling) * noise) + xyz   (:519-523) */
+#define GSR_DENSIFY_SCALING  3   /* children: log(exp(scaling) / (0.8 * 2))                (:524) */
+#define GSR_DENSIFY_MAX_TENSORS 24
+
+typedef struct GsrDensifyTensor {
+    const float* src;    /* P x width */
+    float* dst;          /* P_new x width */
+    int32_t width;       /* floats per Gaussian */
+    int32_t kind;        /* GSR_DENSIFY_* */
+} GsrDensifyTensor;
+
+typedef struct GsrDensifyApplyArgs {
+    int32_t P, A, B, C;              /* the counts gsr_densify_plan reported */
+    int32_t n_tensors;
+    int32_t reserved;
+    const float* scaling;            /* P*3 raw, of the SOURCE model (for GSR_DENSIFY_XYZ rows) */
+    const float* rotation;           /* P*4 raw */
+    const float* noise;              /* 2 x noise_stride x 3 standard-normal numbers, [copy][source Gaussian][axis]:
+                                        the draw of torch.normal (:521) as an input; may be NULL when C == 0 */
+    int64_t noise_stride;            /* >= P */
+    GsrDensifyTensor tensors[GSR_DENSIFY_MAX_TENSORS];
+} GsrDensifyApplyArgs;
+
+int64_t gsr_densify_plan_words(int32_t P);
+int gsr_densify_plan(const GsrDensifyPlanArgs* a, uint32_t* plan, int32_t* counts_host, void* stream);
+int gsr_densify_apply(const GsrDensifyApplyArgs* a, const uint32_t* plan, void* stream);
+/* add_densification_stats (:630-633) fused with train.py:212-213: for visible[i] != 0:
+ * max_radii2D[i] = max(max_radii2D[i], radii[i]) (skipped when either is NULL);
+ * xyz_gradient_accum[i] += ||viewspace_grad[i, 0:2]||; denom[i] += 1.   viewspace_grad is P x 3. */
+int gsr_densify_stats(int32_t P, const float* viewspace_grad, const uint8_t* visible, const int32_t* radii,
+                      float* xyz_gradient_accum, float* denom, float* max_radii2D, void* stream);
+/* reset_opacity (:323-327): opacity = inverse_sigmoid(min(sigmoid(opacity), 0.01)) in place; both moments
+ * zeroed (replace_tensor_to_optimizer, :400-412; either may be NULL). */
+int gsr_reset_opacity(int32_t P, float* opacity, float* exp_avg, float* exp_avg_sq, void* stream);
+
+/* Gaussian file format: rows of the binary_little_endian PLY that save_ply writes
+ * (gaussian_model.py:285-321): x y z nx ny nz f_dc_0..2 f_rest_0..3K-1 opacity scale_0..2 rot_0..3 as
+ * fp32, with f_rest channel-major (the transpose(1, 2) at :309).  pack: model tensors -> rows
+ * [P][17 + 3K]; unpack: rows -> model tensors (load_ply, :329-380).  All device pointers. */
+int gsr_ply_pack(int32_t P, int32_t K_rest, const float* xyz, const float* f_dc, const float* f_rest,
+                 const float* opacity, const float* scaling, const float* rotation, float* rows, void* stream);
+int gsr_ply_unpack(int32_t P, int32_t K_rest, const float* rows, float* xyz, float* f_dc, float* f_rest,
+                   float* opacity, float* scaling, float* rotation, void* stream);
+
 /* Test/inspection hooks (bit-exact parity of the binning stage):
  * rebuild the reference's sorted 64-bit key list (tile<<32 | depth bits) and
  * expose point_list / ranges held in the state buffers.  Device pointers. */

@@ -41,7 +41,8 @@ def test_struct_layouts_match_header():
     h = _header()
     for name, cls in (("GsrParams", _lib.GsrParams), ("GsrBuffers", _lib.GsrBuffers),
                       ("GsrForwardOut", _lib.GsrForwardOut), ("GsrBackwardIO", _lib.GsrBackwardIO),
-                      ("GsrSsimParams", _lib.GsrSsimParams)):
+                      ("GsrSsimParams", _lib.GsrSsimParams), ("GsrDensifyPlanArgs", _lib.GsrDensifyPlanArgs),
+                      ("GsrDensifyTensor", _lib.GsrDensifyTensor), ("GsrDensifyApplyArgs", _lib.GsrDensifyApplyArgs)):
         body = re.search(r"typedef struct %s \{(.*?)\} %s;" % (name, name), h, re.S).group(1)
         body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
         fields = []
@@ -53,10 +54,17 @@ def test_struct_layouts_match_header():
             first = names[0].split()[-1]
             fields.append(first)
             fields += [n.strip() for n in names[1:]]
+        fields = [f.split("[")[0] for f in fields]          # array members: name[COUNT]
         assert fields == [f[0] for f in cls._fields_], name
     assert C.sizeof(_lib.GsrParams) == 12 * 4 + 12 * 8
     assert C.sizeof(_lib.GsrBuffers) == 9 * 8
     assert C.sizeof(_lib.GsrSsimParams) == 2 * 8 + 8 * 4        # 7 ints/floats + tail padding
+    assert C.sizeof(_lib.GsrDensifyPlanArgs) == 8 * 4 + 5 * 8
+    assert C.sizeof(_lib.GsrDensifyTensor) == 24
+    n = int(re.search(r"#define GSR_DENSIFY_MAX_TENSORS (\d+)", h).group(1))
+    assert n == _lib.DENSIFY_MAX_TENSORS and C.sizeof(_lib.GsrDensifyApplyArgs) == 6 * 4 + 3 * 8 + 8 + 24 * n
+    for k in ("COPY", "MOMENT", "XYZ", "SCALING"):
+        assert int(re.search(r"#define GSR_DENSIFY_%s\s+(\d+)" % k, h).group(1)) == getattr(_lib, "DENSIFY_" + k)
 
 
 def test_workspace_size_queries(lib):

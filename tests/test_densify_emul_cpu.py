@@ -1,0 +1,225 @@
+"""Kernel-logic check of the density-control path in the GPU-less container.
+
+The per-element functions of csrc/densify.cu live in csrc/densify_core.cuh; tests/host_emul/densify_emul.cpp compiles
+the SAME header with g++ and replaces the block scans / grid-stride loops by serial loops.  Here the product's host
+code (gaussian_splatting_b200/densify.py, plyio.py) is driven on CPU tensors with its native calls redirected to that
+emulation (monkeypatched in this test only — the product has no CPU path), and the result is compared with the
+golden vectors of the reference's own GaussianModel (tests/golden/densify_golden.npz) and with the oracle.
+The -m gpu tests (tests/test_zz_densify_gpu.py) run the real kernels against the same vectors."""
+import contextlib
+import ctypes as C
+import os
+import subprocess
+import types
+
+import numpy as np
+import pytest
+import torch
+from torch import nn
+
+from gaussian_splatting_b200 import _lib, densify
+from oracle import densify_ref as dr
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+GOLD = np.load(os.path.join(HERE, "golden", "densify_golden.npz"))
+ATTR = densify._ATTR
+VP = C.c_void_p
+
+
+@pytest.fixture(scope="module")
+def emul():
+    src = os.path.join(HERE, "host_emul", "densify_emul.cpp")
+    out = os.path.join(HERE, "host_emul", "libdensify_emul.so")
+    if not os.path.exists(out) or os.path.getmtime(out) < max(
+            os.path.getmtime(src), os.path.getmtime(os.path.join(HERE, "..", "gaussian_splatting_b200", "csrc",
+                                                                 "densify_core.cuh"))):
+        subprocess.check_call(["g++", "-O2", "-shared", "-fPIC", "-ffp-contract=off", "-o", out, src])
+    lib = C.CDLL(out)
+    lib.emul_densify_plan.argtypes = [C.POINTER(_lib.GsrDensifyPlanArgs), VP, VP, VP, VP]
+    lib.emul_densify_apply.argtypes = [C.POINTER(_lib.GsrDensifyApplyArgs), VP, VP, VP]
+    lib.emul_densify_stats.argtypes = [C.c_int32] + [VP] * 6
+    lib.emul_reset_opacity.argtypes = [C.c_int32] + [VP] * 3
+    lib.emul_ply_rows.argtypes = [C.c_int, C.c_int32, C.c_int32] + [VP] * 7
+    return lib
+
+
+class FakeLib:
+    """The C-ABI entry points of csrc/densify.cu, served by the CPU emulation (same structs, host pointers)."""
+
+    def __init__(self, emul):
+        self.e = emul
+
+    def gsr_densify_plan_words(self, P):
+        return 3 * P + 8
+
+    def gsr_densify_plan(self, args, plan, counts, stream):
+        P = args._obj.P
+        return self.e.emul_densify_plan(args, plan, plan + 4 * P, plan + 8 * P, counts)
+
+    def gsr_densify_apply(self, args, plan, stream):
+        P = args._obj.P
+        return self.e.emul_densify_apply(args, plan, plan + 4 * P, plan + 8 * P)
+
+    def gsr_densify_stats(self, P, grad, vis, radii, accum, denom, maxr, stream):
+        return self.e.emul_densify_stats(P, grad, vis, radii, accum, denom, maxr)
+
+    def gsr_reset_opacity(self, P, op, m, v, stream):
+        return self.e.emul_reset_opacity(P, op, m, v)
+
+    def gsr_ply_pack(self, P, K, xyz, f_dc, f_rest, op, sc, rot, rows, stream):
+        return self.e.emul_ply_rows(1, P, K, xyz, f_dc, f_rest, op, sc, rot, rows)
+
+    def gsr_ply_unpack(self, P, K, rows, xyz, f_dc, f_rest, op, sc, rot, stream):
+        return self.e.emul_ply_rows(0, P, K, xyz, f_dc, f_rest, op, sc, rot, rows)
+
+    def gsr_last_error(self):
+        return b"emulation"
+
+
+@pytest.fixture()
+def on_cpu(emul, monkeypatch):
+    fake = FakeLib(emul)
+    monkeypatch.setattr(_lib, "load", lambda: fake)
+    for mod in (densify,):
+        monkeypatch.setattr(mod, "_require_cuda", lambda t, what: None)
+        monkeypatch.setattr(mod, "_device_ctx", lambda d: contextlib.nullcontext())
+        monkeypatch.setattr(mod, "_stream", lambda d: None)
+        monkeypatch.setattr(mod, "_wait", lambda d: None)
+        monkeypatch.setattr(mod, "_pinned_counts", lambda: torch.zeros(4, dtype=torch.int32))
+    return fake
+
+
+def make_model(prefix, with_state=True):
+    """A stand-in with the attribute / optimizer-group layout of the reference's GaussianModel (:228-245)."""
+    gm = types.SimpleNamespace()
+    groups = []
+    for g in dr.GROUPS:
+        p = nn.Parameter(torch.from_numpy(GOLD[f"{prefix}{g}"].copy()))
+        setattr(gm, ATTR[g], p)
+        groups.append({"params": [p], "lr": 1e-3, "name": g})
+    gm.optimizer = torch.optim.Adam(groups, lr=0.0, eps=1e-15)
+    if with_state:
+        for g in dr.GROUPS:
+            p = getattr(gm, ATTR[g])
+            gm.optimizer.state[p] = {"step": torch.tensor(3.0),
+                                     "exp_avg": torch.from_numpy(GOLD[f"{prefix}m_{g}"].copy()),
+                                     "exp_avg_sq": torch.from_numpy(GOLD[f"{prefix}v_{g}"].copy())}
+    gm.xyz_gradient_accum = torch.from_numpy(GOLD[f"{prefix}xyz_gradient_accum"].copy())
+    gm.denom = torch.from_numpy(GOLD[f"{prefix}denom"].copy())
+    gm.max_radii2D = torch.from_numpy(GOLD[f"{prefix}max_radii2D"].copy())
+    gm.percent_dense = 0.01
+    return gm
+
+
+def assert_model(gm, prefix, recomputed=(), with_state=True):
+    names = {g["name"]: g for g in gm.optimizer.param_groups}
+    for g in dr.GROUPS:
+        p = getattr(gm, ATTR[g])
+        assert isinstance(p, nn.Parameter) and p.requires_grad and names[g]["params"][0] is p
+        tensors = [("", p.detach())]
+        if with_state:
+            st = gm.optimizer.state[p]
+            assert float(st["step"]) == 3.0 and len(gm.optimizer.state) == 6
+            tensors += [("m_", st["exp_avg"]), ("v_", st["exp_avg_sq"])]
+        for pre, t in tensors:
+            want = GOLD[f"{prefix}{pre}{g}"]
+            assert tuple(t.shape) == want.shape, (pre + g, t.shape, want.shape)
+            if pre == "" and g in recomputed:
+                np.testing.assert_allclose(t.numpy(), want, rtol=2e-6, atol=2e-6, err_msg=g)
+            else:
+                assert np.array_equal(t.numpy(), want), pre + g
+    for k in ("xyz_gradient_accum", "denom", "max_radii2D"):
+        assert np.array_equal(getattr(gm, k).numpy(), GOLD[prefix + k]), k
+
+
+@pytest.mark.parametrize("case", ("a", "b", "c", "d", "e"))
+def test_densify_and_prune_matches_reference(on_cpu, case):
+    gm = make_model(f"{case}_in_")
+    max_grad, min_opacity, extent, size_thr, pd = GOLD[f"{case}_args"]
+    gm.percent_dense = float(pd)
+    info = densify.densify_and_prune(gm, float(max_grad), float(min_opacity), float(extent),
+                                     float(size_thr) if size_thr else None, torch.from_numpy(GOLD[f"{case}_radii"]),
+                                     noise=torch.from_numpy(GOLD[f"{case}_noise"].copy()))
+    assert_model(gm, f"{case}_out_", recomputed=("xyz", "scaling"))
+    assert info["P"] == GOLD[f"{case}_out_xyz"].shape[0] == info["kept"] + info["clones"] + 2 * info["split"]
+    assert gm.tmp_radii is None
+
+
+def test_densify_without_optimizer_state(on_cpu):
+    # before the first optimizer step the reference's state.get() returns None (:417,:426-428,:458,:478-481)
+    gm = make_model("a_in_", with_state=False)
+    max_grad, min_opacity, extent, size_thr, pd = GOLD["a_args"]
+    densify.densify_and_prune(gm, float(max_grad), float(min_opacity), float(extent), float(size_thr), None,
+                              noise=torch.from_numpy(GOLD["a_noise"].copy()))
+    assert_model(gm, "a_out_", recomputed=("xyz", "scaling"), with_state=False)
+    assert len(gm.optimizer.state) == 0
+
+
+def test_reset_opacity_and_prune_points_match_reference(on_cpu):
+    gm = make_model("a_out_")
+    old = gm._opacity
+    densify.reset_opacity(gm)
+    assert gm._opacity is not old and old not in gm.optimizer.state
+    assert_model(gm, "a_reset_", recomputed=("opacity",))
+    gm.tmp_radii = torch.arange(gm._xyz.shape[0], dtype=torch.float32)
+    mask = torch.from_numpy(GOLD["a_prune_mask"])
+    densify.prune_points(gm, mask)
+    assert_model(gm, "a_pruned_", recomputed=("opacity",))
+    assert torch.equal(gm.tmp_radii, torch.arange(mask.numel(), dtype=torch.float32)[~mask])
+
+
+@pytest.mark.parametrize("case", ("a", "c"))
+def test_statistics_match_reference(on_cpu, case):
+    P = GOLD[f"{case}_in_xyz"].shape[0]
+    gm = types.SimpleNamespace(xyz_gradient_accum=torch.zeros(P, 1), denom=torch.zeros(P, 1), max_radii2D=torch.zeros(P))
+    for v in range(4):
+        vsp = types.SimpleNamespace(grad=torch.from_numpy(GOLD[f"{case}_view{v}_grad"].copy()))
+        densify.add_densification_stats(gm, vsp, torch.from_numpy(GOLD[f"{case}_view{v}_vis"]),
+                                        radii=torch.from_numpy(GOLD[f"{case}_view{v}_radii"]))
+    np.testing.assert_allclose(gm.xyz_gradient_accum.numpy(), GOLD[f"{case}_in_xyz_gradient_accum"], rtol=3e-7, atol=0)
+    assert np.array_equal(gm.denom.numpy(), GOLD[f"{case}_in_denom"])
+    assert np.array_equal(gm.max_radii2D.numpy(), GOLD[f"{case}_in_max_radii2D"])
+
+
+def test_random_models_against_the_oracle(on_cpu):
+    """Sizes that cross the plan kernels' block boundary (1024 Gaussians), against oracle/densify_ref.py."""
+    rng = np.random.default_rng(7)
+    for P, K in ((1023, 0), (1025, 3), (5000, 15)):
+        s = {"xyz": rng.normal(size=(P, 3)), "f_dc": rng.normal(size=(P, 1, 3)), "f_rest": rng.normal(size=(P, K, 3)),
+             "opacity": rng.normal(size=(P, 1)) * 2.5 - 2, "scaling": rng.normal(size=(P, 3)) * 0.9 - 3,
+             "rotation": rng.normal(size=(P, 4))}
+        s = {k: v.astype(np.float32) for k, v in s.items()}
+        for g in dr.GROUPS:
+            s["m_" + g] = rng.normal(size=s[g].shape).astype(np.float32)
+            s["v_" + g] = rng.random(size=s[g].shape).astype(np.float32)
+        s["denom"] = rng.integers(0, 4, size=(P, 1)).astype(np.float32)
+        s["xyz_gradient_accum"] = (rng.random(size=(P, 1)) * 0.0006 * s["denom"]).astype(np.float32)
+        s["max_radii2D"] = rng.random(size=(P,)).astype(np.float32) * 50
+        noise = rng.normal(size=(2, P, 3)).astype(np.float32)
+        want, info = dr.densify_and_prune(s, 0.0002, 0.005, 5.0, 20, np.zeros(P, np.int32), 0.01, noise)
+        assert info["n_clone"] > 0 and info["n_split"] > 0
+        gm = types.SimpleNamespace(percent_dense=0.01)
+        groups = []
+        for g in dr.GROUPS:
+            p = nn.Parameter(torch.from_numpy(s[g].copy()))
+            setattr(gm, ATTR[g], p)
+            groups.append({"params": [p], "name": g})
+        gm.optimizer = torch.optim.Adam(groups, lr=0.0, eps=1e-15)
+        for g in dr.GROUPS:
+            gm.optimizer.state[getattr(gm, ATTR[g])] = {"step": torch.tensor(1.0),
+                                                        "exp_avg": torch.from_numpy(s["m_" + g].copy()),
+                                                        "exp_avg_sq": torch.from_numpy(s["v_" + g].copy())}
+        gm.xyz_gradient_accum = torch.from_numpy(s["xyz_gradient_accum"].copy())
+        gm.denom = torch.from_numpy(s["denom"].copy())
+        gm.max_radii2D = torch.from_numpy(s["max_radii2D"].copy())
+        densify.densify_and_prune(gm, 0.0002, 0.005, 5.0, 20, None, noise=torch.from_numpy(noise))
+        for g in dr.GROUPS:
+            p = getattr(gm, ATTR[g])
+            st = gm.optimizer.state[p]
+            assert tuple(p.shape) == want[g].shape, g
+            if g in ("xyz", "scaling"):
+                np.testing.assert_allclose(p.detach().numpy(), want[g], rtol=2e-6, atol=2e-6)
+            else:
+                assert np.array_equal(p.detach().numpy(), want[g]), g
+            assert np.array_equal(st["exp_avg"].numpy(), want["m_" + g])
+            assert np.array_equal(st["exp_avg_sq"].numpy(), want["v_" + g])
