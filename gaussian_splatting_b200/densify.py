@@ -106,6 +106,8 @@ def _apply(gm, lib, device, plan, P, A, B, Cn, Pn, groups, extra=(), noise=None,
         width = 1
         for d in src.shape[1:]:
             width *= int(d)
+        if width == 0:                      # e.g. f_rest at SH degree 0: nothing to move
+            return dst
         if n >= _lib.DENSIFY_MAX_TENSORS:
             raise RuntimeError("too many tensors for one gsr_densify_apply call")
         args.tensors[n].src, args.tensors[n].dst = src.data_ptr(), dst.data_ptr()
