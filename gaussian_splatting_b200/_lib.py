@@ -169,7 +169,7 @@ def load():
     lib.gsr_densify_apply.restype = C.c_int
     lib.gsr_densify_apply.argtypes = [C.POINTER(GsrDensifyApplyArgs), C.c_void_p, C.c_void_p]
     lib.gsr_densify_stats.restype = C.c_int
-    lib.gsr_densify_stats.argtypes = [C.c_int32] + [C.c_void_p] * 7
+    lib.gsr_densify_stats.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64] + [C.c_void_p] * 5
     lib.gsr_reset_opacity.restype = C.c_int
     lib.gsr_reset_opacity.argtypes = [C.c_int32] + [C.c_void_p] * 4
     lib.gsr_ply_pack.restype = C.c_int

@@ -140,13 +140,19 @@ densify_move_kernel(const __grid_constant__ GsrDensifyApplyArgs a, const uint32_
         densify_move_element(t, e, dstA, dstB, dstC, a);
 }
 
+// n = P with a byte mask (visible) or with neither (then visible <=> radii[i] > 0, render()'s own definition,
+// gaussian_renderer/__init__.py:152); n = number of indices with an index list (what render() actually returns:
+// `(radii > 0).nonzero()`).
 __global__ void __launch_bounds__(256)
-densify_stats_kernel(uint32_t P, const float* __restrict__ grad, const uint8_t* __restrict__ visible,
-                     const int32_t* __restrict__ radii, float* __restrict__ accum, float* __restrict__ denom,
-                     float* __restrict__ max_radii) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= P || !visible[i]) return;
-    const float g3[3] = {grad[3 * (size_t)i], grad[3 * (size_t)i + 1], 0.0f};
+densify_stats_kernel(uint32_t n, const float* __restrict__ grad, const uint8_t* __restrict__ visible,
+                     const int64_t* __restrict__ indices, const int32_t* __restrict__ radii,
+                     float* __restrict__ accum, float* __restrict__ denom, float* __restrict__ max_radii) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    size_t i = t;
+    if (indices) i = (size_t)indices[t];
+    else if (visible ? !visible[t] : radii[t] <= 0) return;
+    const float g3[3] = {grad[3 * i], grad[3 * i + 1], 0.0f};
     densify_stats_one(g3, radii ? radii + i : nullptr, accum + i, denom + i, max_radii ? max_radii + i : nullptr);
 }
 
@@ -239,15 +245,19 @@ extern "C" int gsr_densify_apply(const GsrDensifyApplyArgs* a, const uint32_t* p
     return check_stage("densify apply", false, st);
 }
 
-extern "C" int gsr_densify_stats(int32_t P, const float* viewspace_grad, const uint8_t* visible, const int32_t* radii,
-                                 float* xyz_gradient_accum, float* denom, float* max_radii2D, void* stream) {
-    if (P < 0 || (P > 0 && (!viewspace_grad || !visible || !xyz_gradient_accum || !denom))) {
-        set_error("gsr_densify_stats: bad arguments");
+extern "C" int gsr_densify_stats(int32_t P, const float* viewspace_grad, const uint8_t* visible, const int64_t* indices,
+                                 int64_t n_indices, const int32_t* radii, float* xyz_gradient_accum, float* denom,
+                                 float* max_radii2D, void* stream) {
+    if (P < 0 || n_indices < 0 || n_indices > 0x7fffffffLL ||
+        (P > 0 && (!viewspace_grad || !xyz_gradient_accum || !denom)) || (visible && indices) ||
+        (P > 0 && !visible && !indices && !radii)) {
+        set_error("gsr_densify_stats: bad arguments (one of visible / indices / radii selects the Gaussians)");
         return GSR_ERR_INVALID_ARG;
     }
-    if (P == 0) return GSR_OK;
+    const uint32_t n = indices ? (uint32_t)n_indices : (uint32_t)P;
+    if (P == 0 || n == 0) return GSR_OK;
     cudaStream_t st = (cudaStream_t)stream;
-    GSR_LAUNCH(densify_stats_kernel, div_up((uint32_t)P, 256u), 256, 0, st, (uint32_t)P, viewspace_grad, visible, radii,
+    GSR_LAUNCH(densify_stats_kernel, div_up(n, 256u), 256, 0, st, n, viewspace_grad, visible, indices, radii,
                xyz_gradient_accum, denom, max_radii2D);
     return check_stage("densification stats", false, st);
 }

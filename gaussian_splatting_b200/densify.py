@@ -231,7 +231,9 @@ def prune_points(gm, mask):
 @torch.no_grad()
 def add_densification_stats(gm, viewspace_point_tensor, update_filter, radii=None):
     """GaussianModel.add_densification_stats (:630-633); with `radii` also train.py:212-213
-    (`max_radii2D[vis] = max(max_radii2D[vis], radii[vis])`) in the same launch."""
+    (`max_radii2D[vis] = max(max_radii2D[vis], radii[vis])`) in the same launch.
+    `update_filter` is what render() returns as visibility_filter — the int64 index tensor `(radii > 0).nonzero()`
+    (gaussian_renderer/__init__.py:152) — or a boolean mask, or None with `radii` (then radii > 0 is the filter)."""
     lib = _lib.load()
     grad = viewspace_point_tensor.grad
     if grad is None:
@@ -243,9 +245,25 @@ def add_densification_stats(gm, viewspace_point_tensor, update_filter, radii=Non
     if grad.dim() != 2 or grad.shape[1] != 3:
         raise RuntimeError("viewspace_point_tensor.grad must have shape (P, 3)")
     device = grad.device
-    vis = update_filter if update_filter.dtype in (torch.bool, torch.uint8) else update_filter != 0
-    vis = vis.reshape(-1).contiguous()
-    _require_cuda(vis, "update_filter")
+    vis_ptr = idx_ptr = None
+    n_idx = 0
+    keep = None
+    if update_filter is None:
+        if radii is None:
+            raise RuntimeError("add_densification_stats needs update_filter or radii")
+    elif update_filter.dtype in (torch.bool, torch.uint8):
+        keep = update_filter.reshape(-1).contiguous()
+        if keep.numel() != P:
+            raise RuntimeError("a boolean update_filter must have one entry per Gaussian")
+        vis_ptr = keep.data_ptr()
+    else:
+        keep = update_filter.reshape(-1).to(torch.int64).contiguous()
+        n_idx = int(keep.numel())
+        if n_idx == 0:
+            return
+        idx_ptr = keep.data_ptr()
+    if keep is not None:
+        _require_cuda(keep, "update_filter")
     accum = gm.xyz_gradient_accum
     den = gm.denom
     for t, what in ((accum, "xyz_gradient_accum"), (den, "denom")):
@@ -254,14 +272,15 @@ def add_densification_stats(gm, viewspace_point_tensor, update_filter, radii=Non
             raise RuntimeError(f"{what} must be a contiguous float32 tensor with one entry per Gaussian")
     rad_ptr = maxr_ptr = None
     if radii is not None:
+        _require_cuda(radii, "radii")
         radii = radii if radii.dtype == torch.int32 else radii.to(torch.int32)
-        radii = radii.contiguous()
+        radii = radii.reshape(-1).contiguous()
         maxr = gm.max_radii2D
-        if maxr.dtype != torch.float32 or not maxr.is_contiguous() or maxr.numel() != P:
-            raise RuntimeError("max_radii2D must be a contiguous float32 tensor with one entry per Gaussian")
+        if radii.numel() != P or maxr.dtype != torch.float32 or not maxr.is_contiguous() or maxr.numel() != P:
+            raise RuntimeError("radii / max_radii2D must have one entry per Gaussian (int32 / contiguous float32)")
         rad_ptr, maxr_ptr = radii.data_ptr(), maxr.data_ptr()
     with _device_ctx(device):
-        _lib.check(lib.gsr_densify_stats(P, grad.data_ptr(), vis.data_ptr(), rad_ptr, accum.data_ptr(),
+        _lib.check(lib.gsr_densify_stats(P, grad.data_ptr(), vis_ptr, idx_ptr, n_idx, rad_ptr, accum.data_ptr(),
                                          den.data_ptr(), maxr_ptr, _stream(device)))
 
 

@@ -283,11 +283,16 @@ typedef struct GsrDensifyApplyArgs {
 int64_t gsr_densify_plan_words(int32_t P);
 int gsr_densify_plan(const GsrDensifyPlanArgs* a, uint32_t* plan, int32_t* counts_host, void* stream);
 int gsr_densify_apply(const GsrDensifyApplyArgs* a, const uint32_t* plan, void* stream);
-/* add_densification_stats (:630-633) fused with train.py:212-213: for visible[i] != 0:
- * max_radii2D[i] = max(max_radii2D[i], radii[i]) (skipped when either is NULL);
+/* add_densification_stats (:630-633) fused with train.py:212-213.  The Gaussians of the view are selected by ONE of
+ *   visible  P bytes (a boolean mask),
+ *   indices  n_indices int64 row numbers, unique (what render() returns: `(radii > 0).nonzero()`,
+ *            gaussian_renderer/__init__.py:152),
+ *   neither  radii[i] > 0 (the definition itself; needs radii).
+ * For each selected i: max_radii2D[i] = max(max_radii2D[i], radii[i]) (skipped when either is NULL);
  * xyz_gradient_accum[i] += ||viewspace_grad[i, 0:2]||; denom[i] += 1.   viewspace_grad is P x 3. */
-int gsr_densify_stats(int32_t P, const float* viewspace_grad, const uint8_t* visible, const int32_t* radii,
-                      float* xyz_gradient_accum, float* denom, float* max_radii2D, void* stream);
+int gsr_densify_stats(int32_t P, const float* viewspace_grad, const uint8_t* visible, const int64_t* indices,
+                      int64_t n_indices, const int32_t* radii, float* xyz_gradient_accum, float* denom,
+                      float* max_radii2D, void* stream);
 /* reset_opacity (:323-327): opacity = inverse_sigmoid(min(sigmoid(opacity), 0.01)) in place; both moments
  * zeroed (replace_tensor_to_optimizer, :400-412; either may be NULL). */
 int gsr_reset_opacity(int32_t P, float* opacity, float* exp_avg, float* exp_avg_sq, void* stream);

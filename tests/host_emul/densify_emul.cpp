@@ -33,11 +33,14 @@ extern "C" int emul_densify_apply(const GsrDensifyApplyArgs* a, const uint32_t* 
     return 0;
 }
 
-extern "C" int emul_densify_stats(int32_t P, const float* grad, const uint8_t* visible, const int32_t* radii,
-                                  float* accum, float* denom, float* max_radii) {
-    for (int32_t i = 0; i < P; i++) {
-        if (!visible[i]) continue;
-        const float g3[3] = {grad[3 * (size_t)i], grad[3 * (size_t)i + 1], 0.0f};
+extern "C" int emul_densify_stats(int32_t P, const float* grad, const uint8_t* visible, const int64_t* indices,
+                                  int64_t n_indices, const int32_t* radii, float* accum, float* denom, float* max_radii) {
+    const int64_t n = indices ? n_indices : P;
+    for (int64_t t = 0; t < n; t++) {
+        size_t i = (size_t)t;
+        if (indices) i = (size_t)indices[t];
+        else if (visible ? !visible[t] : radii[t] <= 0) continue;
+        const float g3[3] = {grad[3 * i], grad[3 * i + 1], 0.0f};
         densify_stats_one(g3, radii ? radii + i : nullptr, accum + i, denom + i, max_radii ? max_radii + i : nullptr);
     }
     return 0;

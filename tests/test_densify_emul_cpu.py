@@ -37,7 +37,7 @@ def emul():
     lib = C.CDLL(out)
     lib.emul_densify_plan.argtypes = [C.POINTER(_lib.GsrDensifyPlanArgs), VP, VP, VP, VP]
     lib.emul_densify_apply.argtypes = [C.POINTER(_lib.GsrDensifyApplyArgs), VP, VP, VP]
-    lib.emul_densify_stats.argtypes = [C.c_int32] + [VP] * 6
+    lib.emul_densify_stats.argtypes = [C.c_int32, VP, VP, VP, C.c_int64] + [VP] * 4
     lib.emul_reset_opacity.argtypes = [C.c_int32] + [VP] * 3
     lib.emul_ply_rows.argtypes = [C.c_int, C.c_int32, C.c_int32] + [VP] * 7
     return lib
@@ -60,8 +60,8 @@ class FakeLib:
         P = args._obj.P
         return self.e.emul_densify_apply(args, plan, plan + 4 * P, plan + 8 * P)
 
-    def gsr_densify_stats(self, P, grad, vis, radii, accum, denom, maxr, stream):
-        return self.e.emul_densify_stats(P, grad, vis, radii, accum, denom, maxr)
+    def gsr_densify_stats(self, P, grad, vis, idx, n_idx, radii, accum, denom, maxr, stream):
+        return self.e.emul_densify_stats(P, grad, vis, idx, n_idx, radii, accum, denom, maxr)
 
     def gsr_reset_opacity(self, P, op, m, v, stream):
         return self.e.emul_reset_opacity(P, op, m, v)
@@ -169,13 +169,24 @@ def test_reset_opacity_and_prune_points_match_reference(on_cpu):
 
 
 @pytest.mark.parametrize("case", ("a", "c"))
-def test_statistics_match_reference(on_cpu, case):
+@pytest.mark.parametrize("filter_kind", ("mask", "nonzero", "radii"))
+def test_statistics_match_reference(on_cpu, case, filter_kind):
     P = GOLD[f"{case}_in_xyz"].shape[0]
     gm = types.SimpleNamespace(xyz_gradient_accum=torch.zeros(P, 1), denom=torch.zeros(P, 1), max_radii2D=torch.zeros(P))
     for v in range(4):
         vsp = types.SimpleNamespace(grad=torch.from_numpy(GOLD[f"{case}_view{v}_grad"].copy()))
-        densify.add_densification_stats(gm, vsp, torch.from_numpy(GOLD[f"{case}_view{v}_vis"]),
-                                        radii=torch.from_numpy(GOLD[f"{case}_view{v}_radii"]))
+        vis = torch.from_numpy(GOLD[f"{case}_view{v}_vis"])
+        radii = torch.from_numpy(GOLD[f"{case}_view{v}_radii"])
+        if filter_kind == "radii":
+            # the golden filter is a random 70 % mask; make radii carry it (render(): visible <=> radii > 0)
+            radii = torch.where(vis, radii.clamp_min(1), torch.zeros_like(radii))
+            flt = None
+        else:
+            flt = vis if filter_kind == "mask" else vis.nonzero()       # render() returns the (V, 1) index tensor
+        densify.add_densification_stats(gm, vsp, flt, radii=radii)
+    if filter_kind == "radii":
+        assert np.array_equal(gm.denom.numpy(), GOLD[f"{case}_in_denom"])
+        return
     np.testing.assert_allclose(gm.xyz_gradient_accum.numpy(), GOLD[f"{case}_in_xyz_gradient_accum"], rtol=3e-7, atol=0)
     assert np.array_equal(gm.denom.numpy(), GOLD[f"{case}_in_denom"])
     assert np.array_equal(gm.max_radii2D.numpy(), GOLD[f"{case}_in_max_radii2D"])

@@ -95,7 +95,9 @@ def test_reset_opacity_prune_points_and_statistics_match_reference_golden():
                                max_radii2D=torch.zeros(P, device=DEV))
     for v in range(4):
         vsp = types.SimpleNamespace(grad=torch.from_numpy(GOLD[f"a_view{v}_grad"]).to(DEV))
-        d.add_densification_stats(st, vsp, torch.from_numpy(GOLD[f"a_view{v}_vis"]).to(DEV),
+        vis = torch.from_numpy(GOLD[f"a_view{v}_vis"]).to(DEV)
+        # boolean mask and render()'s `(radii > 0).nonzero()` index tensor (gaussian_renderer/__init__.py:152) alternate
+        d.add_densification_stats(st, vsp, vis if v % 2 else vis.nonzero(),
                                   radii=torch.from_numpy(GOLD[f"a_view{v}_radii"]).to(DEV))
     np.testing.assert_allclose(st.xyz_gradient_accum.cpu().numpy(), GOLD["a_in_xyz_gradient_accum"], rtol=3e-7, atol=0)
     assert np.array_equal(st.denom.cpu().numpy(), GOLD["a_in_denom"])
