@@ -88,6 +88,45 @@ def reduce_densification_stats(viewspace_grad: torch.Tensor, radii: torch.Tensor
     return stats[:, 0:1], stats[:, 1:2], mx
 
 
+def accumulate_densification_stats(gm, viewspace_grad: torch.Tensor, radii: torch.Tensor,
+                                   group: Optional[dist.ProcessGroup] = None):
+    """train.py:212-215 for all views of a view-parallel step at once: every rank adds the statistics of ALL ranks'
+    cameras to its replica's accumulators, so the replicas stay identical."""
+    nsum, den, mx = reduce_densification_stats(viewspace_grad, radii, group)
+    gm.xyz_gradient_accum += nsum
+    gm.denom += den
+    gm.max_radii2D = torch.max(gm.max_radii2D, mx.to(gm.max_radii2D.dtype))
+
+
+def replica_generator(device, seed: int, iteration: int) -> torch.Generator:
+    """The generator every rank seeds identically for the split offsets of one densification
+    (the reference draws them with the global CUDA generator, gaussian_model.py:521)."""
+    g = torch.Generator(device=device)
+    g.manual_seed((int(seed) * 1000003 + int(iteration)) & 0x7FFFFFFFFFFFFFFF)
+    return g
+
+
+def densify_and_prune_replicated(gm, max_grad, min_opacity, extent, max_screen_size, radii, seed: int, iteration: int,
+                                 group: Optional[dist.ProcessGroup] = None, verify: bool = True):
+    """GaussianModel.densify_and_prune (gaussian_model.py:572-621) on every replica of a view-parallel job.
+    No exchange is needed: parameters, optimizer state and (reduced) statistics are identical on all ranks and the
+    one random draw comes from `replica_generator`, so every rank takes the same decisions and ends with bit-identical
+    tensors.  `verify` cross-checks the four row counts over the ranks (one 32-byte all-reduce) and raises if a
+    replica diverged (e.g. statistics accumulated without reduce_densification_stats)."""
+    from . import densify
+    device = gm._xyz.device
+    info = densify.densify_and_prune(gm, max_grad, min_opacity, extent, max_screen_size, radii,
+                                     generator=replica_generator(device, seed, iteration))
+    if verify and dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        c = torch.tensor([info["kept"], info["clones"], info["split"], info["P"]], dtype=torch.int64, device=device)
+        both = torch.cat((c, -c))
+        dist.all_reduce(both, op=dist.ReduceOp.MAX, group=group)     # max(c) and -min(c) in one collective
+        if not torch.equal(both[:4], -both[4:]):
+            raise RuntimeError(f"view-parallel replicas diverged in densify_and_prune: rank counts {c.tolist()}, "
+                               f"max {both[:4].tolist()}, min {(-both[4:]).tolist()}")
+    return info
+
+
 class FusedGradientReducer:
     """All-reduce of the rasterizer's input gradients INSIDE the backward kernel (NVLS multicast).
 

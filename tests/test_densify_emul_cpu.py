@@ -26,8 +26,8 @@ ATTR = densify._ATTR
 VP = C.c_void_p
 
 
-@pytest.fixture(scope="module")
-def emul():
+def load_emul():
+    """Builds (if stale) and binds tests/host_emul/libdensify_emul.so."""
     src = os.path.join(HERE, "host_emul", "densify_emul.cpp")
     out = os.path.join(HERE, "host_emul", "libdensify_emul.so")
     if not os.path.exists(out) or os.path.getmtime(out) < max(
@@ -41,6 +41,11 @@ def emul():
     lib.emul_reset_opacity.argtypes = [C.c_int32] + [VP] * 3
     lib.emul_ply_rows.argtypes = [C.c_int, C.c_int32, C.c_int32] + [VP] * 7
     return lib
+
+
+@pytest.fixture(scope="module")
+def emul():
+    return load_emul()
 
 
 class FakeLib:
@@ -234,3 +239,68 @@ def test_random_models_against_the_oracle(on_cpu):
                 assert np.array_equal(p.detach().numpy(), want[g]), g
             assert np.array_equal(st["exp_avg"].numpy(), want["m_" + g])
             assert np.array_equal(st["exp_avg_sq"].numpy(), want["v_" + g])
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/scene"), reason="needs the reference tree (authoring container)")
+def test_install_on_the_reference_class_matches_its_own_methods(on_cpu, monkeypatch):
+    """densify.install(GaussianModel) on the REFERENCE's class: the patched methods and the reference's originals run on
+    two copies of the same model (CPU tensors; `plyfile` / `simple_knn` stubbed, device="cuda" redirected and
+    torch.normal replaced by the stored table exactly as in tests/golden/make_densify_golden.py)."""
+    import copy
+    import importlib.util
+    import sys
+    spec = importlib.util.spec_from_file_location("make_densify_golden", os.path.join(HERE, "golden", "make_densify_golden.py"))
+    saved = {n: getattr(torch, n) for n in ("zeros", "ones", "eye", "tensor", "empty", "normal")}
+    saved_mods = {k: sys.modules.get(k) for k in ("plyfile", "simple_knn", "simple_knn._C", "scene", "scene.gaussian_model",
+                                                  "utils", "utils.general_utils")}
+    saved_path = list(sys.path)
+    try:
+        mk = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mk)                       # installs the stand-ins and imports the reference class
+        gen = torch.Generator().manual_seed(77)
+        ref = mk.make_model(300, gen)
+        out = {}
+        radii = mk.stats_steps(ref, gen, out, "t_")
+        ours = copy.deepcopy(ref)
+        Patched = type("Patched", (mk.GaussianModel,), {})
+        densify.install(Patched)
+        ours.__class__ = Patched
+        Z = torch.randn(2, 600, 3, generator=gen)
+        mk.NOISE["Z"], mk.NOISE["model"] = Z, ref
+        ref.densify_and_prune(0.0002, 0.005, 5.0, 20, radii)
+        ours.densify_and_prune(0.0002, 0.005, 5.0, 20, radii, noise=Z)
+        ref.reset_opacity()
+        ours.reset_opacity()
+        mask = torch.rand(ref.get_xyz.shape[0], generator=gen) < 0.25
+        ref.tmp_radii = torch.zeros(ref.get_xyz.shape[0])
+        ref.prune_points(mask)
+        ours.prune_points(mask)
+        vsp = types.SimpleNamespace(grad=torch.randn(ref.get_xyz.shape[0], 3, generator=gen))
+        flt = (torch.rand(ref.get_xyz.shape[0], generator=gen) < 0.5).nonzero()
+        ref.add_densification_stats(vsp, flt)
+        ours.add_densification_stats(vsp, flt)
+        assert ours.get_xyz.shape == ref.get_xyz.shape and ref.get_xyz.shape[0] not in (0, 300)
+        for a in ("_xyz", "_features_dc", "_features_rest", "_opacity", "_scaling", "_rotation", "xyz_gradient_accum",
+                  "denom", "max_radii2D"):
+            assert torch.allclose(getattr(ours, a), getattr(ref, a), rtol=2e-6, atol=2e-6), a
+        for go, gr in zip(ours.optimizer.param_groups, ref.optimizer.param_groups):
+            so, sr = ours.optimizer.state[go["params"][0]], ref.optimizer.state[gr["params"][0]]
+            assert go["name"] == gr["name"] and float(so["step"]) == float(sr["step"])
+            assert torch.equal(so["exp_avg"], sr["exp_avg"]) and torch.equal(so["exp_avg_sq"], sr["exp_avg_sq"])
+        # the activations of the reference class keep working on the rebound parameters
+        assert ours.get_scaling.shape == ours._scaling.shape and ours.get_opacity.max() <= 0.0100001
+        # and an optimizer step still updates the new parameter objects
+        ours._xyz.grad = torch.ones_like(ours._xyz)
+        before = ours._xyz.detach().clone()
+        ours.optimizer.param_groups[0]["lr"] = 1e-3
+        ours.optimizer.step()
+        assert not torch.equal(ours._xyz.detach(), before)
+    finally:
+        for n, f in saved.items():
+            setattr(torch, n, f)
+        sys.path[:] = saved_path
+        for k, m in saved_mods.items():
+            if m is None:
+                sys.modules.pop(k, None)
+            else:
+                sys.modules[k] = m

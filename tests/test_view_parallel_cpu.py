@@ -69,6 +69,57 @@ def test_flat_gradient_allreduce_world2():
     assert dict(out) == {0: True, 1: True}
 
 
+def _densify_worker(rank, world, port, out, diverge):
+    """Replicated density control on 2 ranks (kernels served by the CPU emulation, as in test_densify_emul_cpu.py)."""
+    import contextlib
+    from gaussian_splatting_b200 import _lib, densify
+    from gaussian_splatting_b200.view_parallel import accumulate_densification_stats, densify_and_prune_replicated
+    from tests import test_densify_emul_cpu as E
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        fake = E.FakeLib(E.load_emul())
+        _lib.load = lambda: fake
+        densify._require_cuda = lambda t, what: None
+        densify._device_ctx = lambda d: contextlib.nullcontext()
+        densify._stream = lambda d: None
+        densify._wait = lambda d: None
+        densify._pinned_counts = lambda: torch.zeros(4, dtype=torch.int32)
+        gm = E.make_model("a_in_")                         # identical replicas
+        P = gm._xyz.shape[0]
+        gm.xyz_gradient_accum.zero_(), gm.denom.zero_(), gm.max_radii2D.zero_()
+        # each rank saw a different camera: per-view gradients and radii differ, the reduced statistics do not
+        g = torch.Generator().manual_seed(50 + rank)
+        radii = (torch.rand(P, generator=g) * 30).to(torch.int32) * (torch.rand(P, generator=g) < 0.8)
+        vgrad = torch.randn(P, 3, generator=g) * 0.0006
+        accumulate_densification_stats(gm, vgrad, radii)
+        if diverge and rank == 1:
+            gm.xyz_gradient_accum += 1.0                   # a replica whose statistics were not reduced
+        try:
+            info = densify_and_prune_replicated(gm, 0.0002, 0.005, 5.0, 20, radii, seed=0, iteration=600)
+        except RuntimeError as e:
+            out[rank] = "diverged" if "diverged" in str(e) else repr(e)
+            return
+        sums = torch.tensor([float(p.detach().double().sum()) for p in (gm._xyz, gm._scaling, gm._features_rest)] +
+                            [float(info["P"])], dtype=torch.float64)
+        gathered = [torch.zeros_like(sums) for _ in range(world)]
+        dist.all_gather(gathered, sums)
+        out[rank] = bool(all(torch.equal(gathered[0], t) for t in gathered) and info["split"] > 0 and info["clones"] > 0)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_replicated_densification_world2():
+    from tests.test_densify_emul_cpu import load_emul
+    load_emul()                                            # build the emulation library before the ranks race for it
+    for diverge, want in ((False, {0: True, 1: True}), (True, {0: "diverged", 1: "diverged"})):
+        mgr = mp.Manager()
+        out = mgr.dict()
+        mp.spawn(_densify_worker, args=(2, _free_port(), out, diverge), nprocs=2, join=True)
+        assert dict(out) == want
+
+
 def test_camera_partition():
     for G in (1, 2, 4, 8):
         seen = sorted(sum((cameras_for_rank(8, r, G) for r in range(G)), []))
