@@ -5,7 +5,7 @@
 //   apply: ONE launch that moves every parameter tensor and both Adam moments (grid.y = tensor)
 // Per-element arithmetic lives in densify_core.cuh (shared with the CPU emulation test).
 //
-// HBM-bound.  Algorithmic bytes: plan 28*P read + 13*P written (+ 13*P re-read); apply reads every source
+// HBM-bound.  Algorithmic bytes: plan 25*P read + 13*P written; apply reads every source
 // element once (708 B per Gaussian at SH degree 3 with both moments) and writes 708 B per result row.
 #include <algorithm>
 #include "common.cuh"

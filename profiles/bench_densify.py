@@ -10,7 +10,7 @@
 
 Per model size P (SH degree 3, both moments): ms per call (CUDA events around the whole call, host wait included —
 it is part of the operation), the stage split of ours (plan / apply from the library's launch counter and events),
-algorithmic bytes (28 P + 13 P for the plan; 708 B read per source Gaussian + 708 B written per result row for the
+algorithmic bytes (25 P + 13 P for the plan; 708 B read per source Gaussian + 708 B written per result row for the
 apply) and the fraction of the measured HBM copy peak (MEASURED_PEAKS.json, else 6552 GB/s).
 Usage (GPU box): python profiles/bench_densify.py > gpurun_out/densify.json
 """
@@ -150,7 +150,7 @@ def main():
                         lambda: model_from(s), 5)
         ms_torch = timed(lambda _: torch_formulation(s), lambda: None, 5)
         bytes_apply = 4 * FLOATS * 3 * (P + info["P"])
-        bytes_plan = 54 * P
+        bytes_plan = 38 * P
         gm = model_from(s)
         ms_pack = timed(lambda m: plyio.pack_rows(m), lambda: gm, 10)
         out["sizes"].append({
