@@ -129,15 +129,34 @@ densify_dst_kernel(const uint8_t* __restrict__ codes, uint32_t P, const uint32_t
 }
 
 // Apply: grid.y = tensor; grid-stride over the tensor's source elements (coalesced reads; writes are
-// coalesced within each run of surviving rows because every segment keeps source order).
+// coalesced within each run of surviving rows because every segment keeps source order).  The element -> (row,
+// column) split is a division by the row width: compile-time for the widths of the Gaussian model (1, 3, 4, 45 =
+// 15 x 3 higher-order SH floats) so that it is a multiply-shift, 32-bit whenever P * width < 2^32.
+template <int WIDTH, typename index_t>
+__device__ __forceinline__ void densify_move_rows(const GsrDensifyTensor& t, const GsrDensifyApplyArgs& a,
+                                                  const uint32_t* __restrict__ dstA, const uint32_t* __restrict__ dstB,
+                                                  const uint32_t* __restrict__ dstC) {
+    const index_t w = WIDTH ? (index_t)WIDTH : (index_t)t.width;
+    const index_t total = (index_t)a.P * w;
+    const index_t stride = (index_t)gridDim.x * blockDim.x;
+    for (index_t e = (index_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += stride) {
+        const index_t i = e / w;
+        densify_move_element(t, (long long)i, (int)(e - i * w), dstA, dstB, dstC, a);
+    }
+}
+
+template <typename index_t>
 __global__ void __launch_bounds__(256)
 densify_move_kernel(const __grid_constant__ GsrDensifyApplyArgs a, const uint32_t* __restrict__ dstA,
                     const uint32_t* __restrict__ dstB, const uint32_t* __restrict__ dstC) {
-    const GsrDensifyTensor t = a.tensors[blockIdx.y];
-    const long long total = (long long)a.P * t.width;
-    const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += stride)
-        densify_move_element(t, e, dstA, dstB, dstC, a);
+    const GsrDensifyTensor& t = a.tensors[blockIdx.y];
+    switch (t.width) {                       // uniform per block
+        case 1:  densify_move_rows<1, index_t>(t, a, dstA, dstB, dstC); break;
+        case 3:  densify_move_rows<3, index_t>(t, a, dstA, dstB, dstC); break;
+        case 4:  densify_move_rows<4, index_t>(t, a, dstA, dstB, dstC); break;
+        case 45: densify_move_rows<45, index_t>(t, a, dstA, dstB, dstC); break;
+        default: densify_move_rows<0, index_t>(t, a, dstA, dstB, dstC); break;
+    }
 }
 
 // n = P with a byte mask (visible) or with neither (then visible <=> radii[i] > 0, render()'s own definition,
@@ -167,16 +186,16 @@ reset_opacity_kernel(uint32_t P, float* __restrict__ opacity, float* __restrict_
 
 // ---------------------------------------------------------------- PLY rows
 // One thread per row element: the row side is fully coalesced, the model side touches every float exactly once.
-template <bool PACK>
+template <bool PACK, typename index_t>
 __global__ void __launch_bounds__(256)
-ply_rows_kernel(long long total, int K, float* __restrict__ xyz, float* __restrict__ f_dc, float* __restrict__ f_rest,
+ply_rows_kernel(index_t total, int K, float* __restrict__ xyz, float* __restrict__ f_dc, float* __restrict__ f_rest,
                 float* __restrict__ opacity, float* __restrict__ scaling, float* __restrict__ rotation,
                 float* __restrict__ rows) {
-    const int Wd = ply_row_floats(K);
-    const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += stride) {
-        const long long i = e / Wd;
-        float* cell = ply_cell(i, (int)(e - i * Wd), K, xyz, f_dc, f_rest, opacity, scaling, rotation);
+    const index_t Wd = (index_t)ply_row_floats(K);
+    const index_t stride = (index_t)gridDim.x * blockDim.x;
+    for (index_t e = (index_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += stride) {
+        const index_t i = e / Wd;
+        float* cell = ply_cell((long long)i, (int)(e - i * Wd), K, xyz, f_dc, f_rest, opacity, scaling, rotation);
         if (PACK) rows[e] = cell ? *cell : 0.0f;
         else if (cell) *cell = rows[e];
     }
@@ -241,7 +260,10 @@ extern "C" int gsr_densify_apply(const GsrDensifyApplyArgs* a, const uint32_t* p
     const uint32_t* dstC = plan + 2 * (size_t)P;
     const long long widest = (long long)P * max_width;
     const unsigned gx = (unsigned)std::min<long long>((widest + 255) / 256, 148LL * 8);
-    GSR_LAUNCH(densify_move_kernel, dim3(gx, (unsigned)a->n_tensors), 256, 0, st, *a, dstA, dstB, dstC);
+    if (widest + 256LL * gx < (1LL << 32))      // element index + one grid stride fits in 32 bits
+        GSR_LAUNCH(densify_move_kernel<uint32_t>, dim3(gx, (unsigned)a->n_tensors), 256, 0, st, *a, dstA, dstB, dstC);
+    else
+        GSR_LAUNCH(densify_move_kernel<long long>, dim3(gx, (unsigned)a->n_tensors), 256, 0, st, *a, dstA, dstB, dstC);
     return check_stage("densify apply", false, st);
 }
 
@@ -283,10 +305,12 @@ static int ply_rows(bool pack, int32_t P, int32_t K, float* xyz, float* f_dc, fl
     cudaStream_t st = (cudaStream_t)stream;
     const long long total = (long long)P * ply_row_floats(K);
     const unsigned gx = (unsigned)std::min<long long>((total + 255) / 256, 148LL * 16);
-    if (pack)
-        GSR_LAUNCH(ply_rows_kernel<true>, gx, 256, 0, st, total, (int)K, xyz, f_dc, f_rest, opacity, scaling, rotation, rows);
-    else
-        GSR_LAUNCH(ply_rows_kernel<false>, gx, 256, 0, st, total, (int)K, xyz, f_dc, f_rest, opacity, scaling, rotation, rows);
+#define PLY_LAUNCH(PACK, T) GSR_LAUNCH((ply_rows_kernel<PACK, T>), gx, 256, 0, st, (T)total, (int)K, xyz, f_dc, f_rest, \
+                                       opacity, scaling, rotation, rows)
+    const bool small = total + 256LL * gx < (1LL << 32);
+    if (pack) { if (small) PLY_LAUNCH(true, uint32_t); else PLY_LAUNCH(true, long long); }
+    else      { if (small) PLY_LAUNCH(false, uint32_t); else PLY_LAUNCH(false, long long); }
+#undef PLY_LAUNCH
     return check_stage(pack ? "ply pack" : "ply unpack", false, st);
 }
 

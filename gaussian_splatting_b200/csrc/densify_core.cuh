@@ -74,13 +74,11 @@ GSD_HD float densify_child_xyz(int k, float xyz_k, const float* scaling3, const 
 
 GSD_HD float densify_child_scaling(float scaling_raw) { return logf(expf(scaling_raw) * SPLIT_SCALE); }
 
-// Moves element e (row i = e / width, column k) of one tensor to every destination row derived from source
-// row i.  dstA/dstB/dstC: rank of the row inside its segment or DENSIFY_NONE.
-GSD_HD void densify_move_element(const GsrDensifyTensor& t, long long e, const uint32_t* dstA, const uint32_t* dstB,
+// Moves column k of source row i of one tensor to every destination row derived from source row i.
+// dstA/dstB/dstC: rank of the row inside its segment or DENSIFY_NONE.
+GSD_HD void densify_move_element(const GsrDensifyTensor& t, long long i, int k, const uint32_t* dstA, const uint32_t* dstB,
                                  const uint32_t* dstC, const GsrDensifyApplyArgs& a) {
-    const long long i = e / t.width;
-    const int k = (int)(e - i * t.width);
-    const float v = t.src[e];
+    const float v = t.src[i * t.width + k];
     const uint32_t da = dstA[i], db = dstB[i], dc = dstC[i];
     const bool moment = t.kind == GSR_DENSIFY_MOMENT;
     if (da != DENSIFY_NONE) t.dst[(long long)da * t.width + k] = v;

@@ -27,8 +27,8 @@ extern "C" int emul_densify_apply(const GsrDensifyApplyArgs* a, const uint32_t* 
                                   const uint32_t* dstC) {
     for (int t = 0; t < a->n_tensors; t++) {
         const GsrDensifyTensor& e = a->tensors[t];
-        const long long total = (long long)a->P * e.width;
-        for (long long i = 0; i < total; i++) densify_move_element(e, i, dstA, dstB, dstC, *a);
+        for (long long i = 0; i < a->P; i++)
+            for (int k = 0; k < e.width; k++) densify_move_element(e, i, k, dstA, dstB, dstC, *a);
     }
     return 0;
 }
