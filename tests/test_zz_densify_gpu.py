@@ -257,3 +257,80 @@ def test_errors_are_loud():
     cpu.optimizer = torch.optim.Adam([{"params": [p], "name": n} for n in ("xyz",)], lr=0.0)
     with pytest.raises(RuntimeError):
         d.densify_and_prune(cpu, 0.0002, 0.005, 5.0, 20, None)
+
+
+def test_training_slice_render_stats_step_densify_save_load(tmp_path):
+    """The callers either side of the rasterizer in one piece (train.py:143-251 without datasets): render -> L1 ->
+    backward -> statistics from render()'s visibility filter -> SparseGaussianAdam -> densify_and_prune -> render with
+    the new count -> save_ply -> load_ply -> identical image."""
+    import diff_gaussian_rasterization as dgr
+    from gaussian_splatting_b200 import plyio
+    from tests.helpers import settings_for, small_scene
+    d = _densify()
+    W, H = 128, 96
+    gs, s = small_scene(P=4000, W=W, H=H, seed=3, sh_degree=3, scale_mult=2.0, behind_fraction=0.05)
+    gm = types.SimpleNamespace(percent_dense=0.01, max_sh_degree=3, active_sh_degree=3)
+    raw = {"xyz": gs["means3D"], "f_dc": gs["shs"][:, :1], "f_rest": gs["shs"][:, 1:],
+           "opacity": torch.logit(gs["opacities"].clamp(1e-4, 1 - 1e-4)), "scaling": torch.log(gs["scales"]),
+           "rotation": gs["rotations"]}
+    lrs = {"xyz": 1.6e-4, "f_dc": 2.5e-3, "f_rest": 1.25e-4, "opacity": 0.025, "scaling": 0.005, "rotation": 0.001}
+    groups = []
+    for name in dr.GROUPS:
+        p = nn.Parameter(raw[name].contiguous().to(DEV))
+        setattr(gm, d._ATTR[name], p)
+        groups.append({"params": [p], "lr": lrs[name], "name": name})
+    gm.optimizer = dgr.SparseGaussianAdam(groups, lr=0.0, eps=1e-15)
+    P = gm._xyz.shape[0]
+    gm.xyz_gradient_accum = torch.zeros(P, 1, device=DEV)
+    gm.denom = torch.zeros(P, 1, device=DEV)
+    gm.max_radii2D = torch.zeros(P, device=DEV)
+    target = torch.rand(3, H, W, generator=torch.Generator().manual_seed(0)).to(DEV)
+    rast = dgr.GaussianRasterizer(settings_for(dgr, s, DEV))
+
+    def render(model):
+        means2D = torch.zeros_like(model._xyz, requires_grad=True)          # screenspace_points (render():36-40)
+        color, radii, invd = rast(means3D=model._xyz, means2D=means2D, opacities=torch.sigmoid(model._opacity),
+                                  dc=model._features_dc, shs=model._features_rest, scales=torch.exp(model._scaling),
+                                  rotations=torch.nn.functional.normalize(model._rotation))
+        return color, radii, means2D
+
+    for _ in range(3):
+        color, radii, means2D = render(gm)
+        (color - target).abs().mean().backward()
+        d.add_densification_stats(gm, means2D, (radii > 0).nonzero(), radii=radii)
+        gm.optimizer.step(radii > 0, radii.shape[0])
+        gm.optimizer.zero_grad(set_to_none=True)
+    vis = radii > 0
+    assert int(vis.sum()) > 1000 and float(gm.denom.max()) == 3.0
+    assert torch.equal(gm.max_radii2D[vis] >= radii[vis].float(), torch.ones_like(vis[vis]))
+    # thresholds from the data so that every branch is taken
+    g = torch.nan_to_num(gm.xyz_gradient_accum / gm.denom, nan=0.0)[:, 0]
+    max_grad = float(g[g > 0].median())
+    extent = float(torch.exp(gm._scaling.detach()).max(1).values.median()) / 0.01
+    info = d.densify_and_prune(gm, max_grad, 0.005, extent, 20, radii)
+    Pn = info["P"]
+    assert info["clones"] > 0 and info["split"] > 0 and Pn != P and gm._xyz.shape[0] == Pn
+    assert gm.xyz_gradient_accum.shape == (Pn, 1) and gm.max_radii2D.shape == (Pn,)
+    # the new model renders, trains on (optimizer state was re-keyed and resized) and reports statistics
+    color, radii, means2D = render(gm)
+    assert color.shape == (3, H, W) and radii.shape == (Pn,) and bool(torch.isfinite(color).all())
+    (color - target).abs().mean().backward()
+    before = gm._xyz.detach().clone()
+    gm.optimizer.step(radii > 0, Pn)
+    assert not torch.equal(gm._xyz.detach(), before)
+    assert gm.optimizer.state[gm._xyz]["exp_avg"].shape == (Pn, 3) and len(gm.optimizer.state) == 6
+    d.add_densification_stats(gm, means2D, (radii > 0).nonzero(), radii=radii)
+    assert float(gm.denom.sum()) == float((radii > 0).sum())
+    gm.optimizer.zero_grad(set_to_none=True)
+    d.reset_opacity(gm)
+    assert float(torch.sigmoid(gm._opacity).max()) <= 0.0100001
+    # file round trip: the loaded model renders the same image bit for bit
+    with torch.no_grad():
+        want, _, _ = render(gm)
+    path = str(tmp_path / "point_cloud.ply")
+    plyio.save_ply(gm, path)
+    loaded = types.SimpleNamespace(max_sh_degree=3)
+    plyio.load_ply(loaded, path, device=DEV)
+    with torch.no_grad():
+        got, _, _ = render(loaded)
+    assert torch.equal(got, want)
