@@ -59,10 +59,10 @@ def _to_device(host, device):
 
 
 # ------------------------------------------------------------------ generic PLY table reader / writer (host)
-def write_ply_table(path, names, types, table):
-    """`table`: structured or plain 2-D array with one column per property, written as element `vertex`."""
+def write_ply_table(path, names, types, table, element="vertex"):
+    """`table`: structured or plain 2-D array with one column per property, written as one element."""
     count = int(table.shape[0])
-    lines = ["ply", "format binary_little_endian 1.0", f"element vertex {count}"]
+    lines = ["ply", "format binary_little_endian 1.0", f"element {element} {count}"]
     lines += [f"property {_PLY_NAMES[t]} {n}" for n, t in zip(names, types)]
     lines.append("end_header")
     with open(path, "wb") as f:

@@ -27,7 +27,7 @@ REF = "/root/reference"
 # ---- stand-ins (see the docstring) --------------------------------------------------------------
 ply = types.ModuleType("plyfile")
 ply.PlyData = ply.PlyElement = object
-sys.modules["plyfile"] = ply
+sys.modules.setdefault("plyfile", ply)      # (tests may have installed gaussian_splatting_b200.plyfile_compat)
 knn = types.ModuleType("simple_knn")
 knn_c = types.ModuleType("simple_knn._C")
 knn_c.distCUDA2 = None

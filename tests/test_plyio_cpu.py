@@ -138,3 +138,69 @@ def test_checkpoint_round_trip(tmp_path):
     assert it == 7000 and len(params) == 12 and params[0] == 0 and params[11] == 1.5
     assert torch.equal(params[1], gm._xyz) and torch.equal(params[9], gm.denom)
     assert params[10]["param_groups"][0]["name"] == "xyz" and float(params[10]["state"][0]["step"]) == 1.0
+
+
+@pytest.mark.skipif(not __import__("os").path.isdir("/root/reference/scene"), reason="needs the reference tree")
+def test_reference_save_and_load_ply_through_plyfile_compat(on_cpu, tmp_path):  # noqa: F811
+    """The REFERENCE's own save_ply / load_ply / storePly / fetchPly (unmodified) running on plyfile_compat: its row
+    assembly (gaussian_model.py:303-321) must give the bytes plyio.save_ply and the oracle give, and its load_ply
+    (:329-380) must read back what plyio.load_ply reads."""
+    import importlib.util
+    import os
+    import sys
+    from gaussian_splatting_b200 import plyfile_compat
+    saved = {n: getattr(torch, n) for n in ("zeros", "ones", "eye", "tensor", "empty", "normal")}
+    names = ("plyfile", "simple_knn", "simple_knn._C", "scene", "scene.gaussian_model", "scene.dataset_readers", "utils",
+             "utils.general_utils", "utils.system_utils", "utils.sh_utils", "utils.graphics_utils")
+    saved_mods = {k: sys.modules.get(k) for k in names}
+    saved_path = list(sys.path)
+    try:
+        sys.modules.pop("plyfile", None)
+        assert plyfile_compat.install() is plyfile_compat
+        here = os.path.dirname(os.path.abspath(__file__))
+        spec = importlib.util.spec_from_file_location("mk_golden", os.path.join(here, "golden", "make_densify_golden.py"))
+        mk = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mk)                       # device="cuda" redirect + the reference's GaussianModel
+        gm = model(23, 3, seed=5)
+        ref = mk.GaussianModel(3)
+        for a in ("_xyz", "_features_dc", "_features_rest", "_opacity", "_scaling", "_rotation"):
+            setattr(ref, a, getattr(gm, a))
+        p_ref, p_ours = str(tmp_path / "ref" / "pc.ply"), str(tmp_path / "ours" / "pc.ply")
+        ref.save_ply(p_ref)                               # the reference's code, compat writer
+        plyio.save_ply(gm, p_ours)
+        data = open(p_ref, "rb").read()
+        assert data == open(p_ours, "rb").read() == ply_ref.save_ply_bytes(*arrays(gm))
+        back = mk.GaussianModel(3)
+        back.load_ply(p_ours)                             # the reference's code, compat reader
+        ours = types.SimpleNamespace(max_sh_degree=3)
+        plyio.load_ply(ours, p_ref, device="cpu")
+        for a in ("_xyz", "_features_dc", "_features_rest", "_opacity", "_scaling", "_rotation"):
+            assert torch.equal(getattr(back, a).detach(), getattr(ours, a).detach()), a
+            assert torch.equal(getattr(back, a).detach(), getattr(gm, a).detach()), a
+        assert back.active_sh_degree == ours.active_sh_degree == 3
+    finally:
+        for n, f in saved.items():
+            setattr(torch, n, f)
+        sys.path[:] = saved_path
+        for k, m in saved_mods.items():
+            if m is None:
+                sys.modules.pop(k, None)
+            else:
+                sys.modules[k] = m
+
+
+def test_plyfile_compat_api(tmp_path):
+    from gaussian_splatting_b200.plyfile_compat import PlyData, PlyElement
+    dtype = [("x", "f4"), ("y", "f4"), ("z", "f4"), ("red", "u1")]
+    el = np.zeros(3, dtype)
+    el["x"], el["red"] = [1, 2, 3], [7, 8, 9]
+    path = str(tmp_path / "t.ply")
+    PlyData([PlyElement.describe(el, "vertex")]).write(path)
+    back = PlyData.read(path)
+    assert [p.name for p in back.elements[0].properties] == ["x", "y", "z", "red"]
+    assert np.array_equal(back["vertex"]["x"], el["x"]) and np.array_equal(back.elements[0]["red"], el["red"])
+    assert len(back.elements[0]) == 3
+    with pytest.raises(KeyError):
+        back["face"]
+    with pytest.raises(TypeError):
+        PlyElement.describe(np.zeros((3, 2)), "vertex")
