@@ -105,6 +105,25 @@ STAGE_COUNT = 9
 _lib = None
 
 
+def bind_densify(lib):
+    """Signatures of the density-control and PLY-row entry points."""
+    lib.gsr_densify_plan_words.restype = C.c_int64
+    lib.gsr_densify_plan_words.argtypes = [C.c_int32]
+    lib.gsr_densify_plan.restype = C.c_int
+    lib.gsr_densify_plan.argtypes = [C.POINTER(GsrDensifyPlanArgs), C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.gsr_densify_apply.restype = C.c_int
+    lib.gsr_densify_apply.argtypes = [C.POINTER(GsrDensifyApplyArgs), C.c_void_p, C.c_void_p]
+    lib.gsr_densify_stats.restype = C.c_int
+    lib.gsr_densify_stats.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64] + [C.c_void_p] * 5
+    lib.gsr_reset_opacity.restype = C.c_int
+    lib.gsr_reset_opacity.argtypes = [C.c_int32] + [C.c_void_p] * 4
+    lib.gsr_ply_pack.restype = C.c_int
+    lib.gsr_ply_pack.argtypes = [C.c_int32, C.c_int32] + [C.c_void_p] * 8
+    lib.gsr_ply_unpack.restype = C.c_int
+    lib.gsr_ply_unpack.argtypes = [C.c_int32, C.c_int32] + [C.c_void_p] * 8
+    return lib
+
+
 def load():
     """Load libgsrast.so once; raises RuntimeError (never falls back) if it is unavailable."""
     global _lib
@@ -162,20 +181,7 @@ def load():
     lib.gsr_ssim_forward.argtypes = [PS] + [C.c_void_p] * 7
     lib.gsr_ssim_backward.restype = C.c_int
     lib.gsr_ssim_backward.argtypes = [PS] + [C.c_void_p] * 7
-    lib.gsr_densify_plan_words.restype = C.c_int64
-    lib.gsr_densify_plan_words.argtypes = [C.c_int32]
-    lib.gsr_densify_plan.restype = C.c_int
-    lib.gsr_densify_plan.argtypes = [C.POINTER(GsrDensifyPlanArgs), C.c_void_p, C.c_void_p, C.c_void_p]
-    lib.gsr_densify_apply.restype = C.c_int
-    lib.gsr_densify_apply.argtypes = [C.POINTER(GsrDensifyApplyArgs), C.c_void_p, C.c_void_p]
-    lib.gsr_densify_stats.restype = C.c_int
-    lib.gsr_densify_stats.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64] + [C.c_void_p] * 5
-    lib.gsr_reset_opacity.restype = C.c_int
-    lib.gsr_reset_opacity.argtypes = [C.c_int32] + [C.c_void_p] * 4
-    lib.gsr_ply_pack.restype = C.c_int
-    lib.gsr_ply_pack.argtypes = [C.c_int32, C.c_int32] + [C.c_void_p] * 8
-    lib.gsr_ply_unpack.restype = C.c_int
-    lib.gsr_ply_unpack.argtypes = [C.c_int32, C.c_int32] + [C.c_void_p] * 8
+    bind_densify(lib)
     _lib = lib
     return lib
 

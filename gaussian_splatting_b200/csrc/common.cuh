@@ -178,11 +178,19 @@ int  check_stage(const char* stage, bool debug, cudaStream_t stream);
 
 // ---- measurement hooks (api.cu) ---------------------------------------------
 extern unsigned long long g_launches;
+#ifndef GSR_HOST_EMUL
 #define GSR_LAUNCH(kernel, grid, block, smem, st, ...)              \
     do {                                                            \
         kernel<<<(grid), (block), (smem), (st)>>>(__VA_ARGS__);     \
         ++gsr::g_launches;                                          \
     } while (0)
+#else   // tests/host_emul: the same kernel functions run as fibers on the CPU (cuda_emul/cuda_runtime.h)
+#define GSR_LAUNCH(kernel, grid, block, smem, st, ...)                          \
+    do {                                                                        \
+        emu::launch((grid), (block), [&]() { kernel(__VA_ARGS__); });           \
+        ++gsr::g_launches;                                                      \
+    } while (0)
+#endif
 
 void profile_begin(int stage, cudaStream_t st);
 void profile_end(int stage, cudaStream_t st);

@@ -1,0 +1,188 @@
+// emul.cpp — cooperative fiber scheduler behind tests/host_emul/cuda_emul/cuda_runtime.h (TEST INFRASTRUCTURE).
+// One block at a time; its threads are ucontext fibers resumed round-robin.  A fiber runs until it finishes or
+// blocks in a barrier (block-wide: __syncthreads; warp-wide: every *_sync primitive).  Threads that have exited no
+// longer count for barriers (CUDA semantics).  If no fiber can make progress the emulation aborts (a barrier that
+// not all live threads reach is a bug in the kernel on the GPU too).
+#include <stdio.h>
+#include <stdlib.h>
+#include <ucontext.h>
+
+#include <vector>
+
+#include "cuda_runtime.h"
+
+namespace emu {
+
+Idx g_threadIdx, g_blockIdx, g_blockDim, g_gridDim;
+
+namespace {
+constexpr size_t STACK = 256 * 1024;
+
+struct Warp {
+    uint32_t alive = 0;            // lanes that have not exited
+    uint32_t arrived = 0;          // lanes waiting in the current warp barrier
+    uint32_t gen = 0;
+    uint32_t slot[32];
+    uint32_t ballot = 0, ballot_out = 0;
+};
+
+struct Fiber {
+    ucontext_t ctx;
+    char* stack = nullptr;
+    bool done = false;
+    Idx tid;
+    unsigned linear = 0;
+};
+
+struct Block {
+    std::vector<Fiber> fibers;
+    std::vector<Warp> warps;
+    ucontext_t sched;
+    unsigned cur = 0, alive = 0;
+    unsigned bar_arrived = 0, bar_gen = 0;
+    int bar_count = 0, bar_count_out = 0;
+    unsigned long long progress = 0;
+    const std::function<void()>* body = nullptr;
+};
+
+Block* g_blk = nullptr;
+
+void yield() {
+    Block* b = g_blk;
+    swapcontext(&b->fibers[b->cur].ctx, &b->sched);
+}
+
+void trampoline() {
+    Block* b = g_blk;
+    (*b->body)();
+    Fiber& f = b->fibers[b->cur];
+    f.done = true;
+    b->alive--;
+    b->warps[f.linear >> 5].alive &= ~(1u << (f.linear & 31));
+    b->progress++;
+    swapcontext(&f.ctx, &b->sched);
+}
+
+// Warp barrier over the live lanes of `mask`; `last` runs once, by the lane that completes the barrier.
+template <typename F> void warp_barrier(uint32_t mask, F last) {
+    Block* b = g_blk;
+    const unsigned lin = b->fibers[b->cur].linear;
+    Warp& w = b->warps[lin >> 5];
+    const uint32_t me = 1u << (lin & 31);
+    const uint32_t gen = w.gen;
+    w.arrived |= me;
+    b->progress++;
+    for (;;) {
+        const uint32_t need = mask & w.alive;
+        if (w.gen != gen) return;
+        if ((w.arrived & need) == need) {
+            last(w);
+            w.arrived = 0;
+            w.gen++;
+            b->progress++;
+            return;
+        }
+        yield();
+    }
+}
+}  // namespace
+
+unsigned lane_id() { return g_blk->fibers[g_blk->cur].linear & 31u; }
+
+void warp_sync(uint32_t mask) { warp_barrier(mask, [](Warp&) {}); }
+
+uint32_t warp_shfl(uint32_t mask, uint32_t value, int src_lane) {
+    Block* b = g_blk;
+    const unsigned lin = b->fibers[b->cur].linear;
+    Warp& w = b->warps[lin >> 5];
+    w.slot[lin & 31] = value;
+    warp_barrier(mask, [](Warp&) {});
+    const uint32_t r = w.slot[src_lane & 31];
+    warp_barrier(mask, [](Warp&) {});          // nobody overwrites a slot before every lane has read
+    return r;
+}
+
+uint32_t warp_ballot(uint32_t mask, int pred) {
+    Block* b = g_blk;
+    const unsigned lin = b->fibers[b->cur].linear;
+    Warp& w = b->warps[lin >> 5];
+    if (pred) w.ballot |= 1u << (lin & 31);
+    warp_barrier(mask, [](Warp& x) { x.ballot_out = x.ballot; x.ballot = 0; });
+    const uint32_t r = w.ballot_out & mask;
+    warp_barrier(mask, [](Warp&) {});
+    return r;
+}
+
+void syncthreads() { (void)syncthreads_count(0); }
+
+int syncthreads_count(int pred) {
+    Block* b = g_blk;
+    const unsigned gen = b->bar_gen;
+    b->bar_arrived++;
+    if (pred) b->bar_count++;
+    b->progress++;
+    for (;;) {
+        if (b->bar_gen != gen) return b->bar_count_out;
+        if (b->bar_arrived >= b->alive) {
+            b->bar_count_out = b->bar_count;
+            b->bar_count = 0;
+            b->bar_arrived = 0;
+            b->bar_gen++;
+            b->progress++;
+            return b->bar_count_out;
+        }
+        yield();
+    }
+}
+
+void launch(dim3 grid, dim3 block, const std::function<void()>& body) {
+    const unsigned n = block.x * block.y * block.z;
+    Block blk;
+    blk.body = &body;
+    blk.fibers.resize(n);
+    for (auto& f : blk.fibers) f.stack = (char*)malloc(STACK);
+    g_blockDim = {block.x, block.y, block.z};
+    g_gridDim = {grid.x, grid.y, grid.z};
+    Block* outer = g_blk;
+    g_blk = &blk;
+    for (unsigned bz = 0; bz < grid.z; bz++)
+        for (unsigned by = 0; by < grid.y; by++)
+            for (unsigned bx = 0; bx < grid.x; bx++) {
+                g_blockIdx = {bx, by, bz};
+                blk.warps.assign((n + 31) / 32, Warp());
+                blk.alive = n;
+                blk.bar_arrived = blk.bar_gen = 0;
+                blk.bar_count = 0;
+                for (unsigned t = 0; t < n; t++) {
+                    Fiber& f = blk.fibers[t];
+                    f.done = false;
+                    f.linear = t;
+                    f.tid = {t % block.x, (t / block.x) % block.y, t / (block.x * block.y)};
+                    blk.warps[t >> 5].alive |= 1u << (t & 31);
+                    getcontext(&f.ctx);
+                    f.ctx.uc_stack.ss_sp = f.stack;
+                    f.ctx.uc_stack.ss_size = STACK;
+                    f.ctx.uc_link = nullptr;
+                    makecontext(&f.ctx, trampoline, 0);
+                }
+                while (blk.alive) {
+                    const unsigned long long before = blk.progress;
+                    for (unsigned t = 0; t < n; t++) {
+                        Fiber& f = blk.fibers[t];
+                        if (f.done) continue;
+                        blk.cur = t;
+                        g_threadIdx = f.tid;
+                        swapcontext(&blk.sched, &f.ctx);
+                    }
+                    if (blk.progress == before) {
+                        fprintf(stderr, "cuda_emul: deadlock in block (%u,%u,%u): %u live threads wait at barriers "
+                                        "that not all of them reach\n", bx, by, bz, blk.alive);
+                        abort();
+                    }
+                }
+            }
+    g_blk = outer;
+    for (auto& f : blk.fibers) free(f.stack);
+}
+
+}  // namespace emu

@@ -1,11 +1,15 @@
-"""Kernel-logic check of the density-control path in the GPU-less container.
+"""Kernel-logic check of the density-control path in the GPU-less container, with two emulation back-ends:
 
-The per-element functions of csrc/densify.cu live in csrc/densify_core.cuh; tests/host_emul/densify_emul.cpp compiles
-the SAME header with g++ and replaces the block scans / grid-stride loops by serial loops.  Here the product's host
-code (gaussian_splatting_b200/densify.py, plyio.py) is driven on CPU tensors with its native calls redirected to that
-emulation (monkeypatched in this test only — the product has no CPU path), and the result is compared with the
-golden vectors of the reference's own GaussianModel (tests/golden/densify_golden.npz) and with the oracle.
-The -m gpu tests (tests/test_zz_densify_gpu.py) run the real kernels against the same vectors."""
+  "per-element"  csrc/densify_core.cuh (the per-element functions of csrc/densify.cu) compiled with g++ by
+                 tests/host_emul/densify_emul.cpp, block scans / grid-stride loops replaced by serial loops;
+  "kernels"      csrc/densify.cu ITSELF compiled as C++ against tests/host_emul/cuda_emul (a stand-in cuda_runtime.h and
+                 a fiber scheduler: every CUDA thread of a block is a fiber, __syncthreads / __shfl_*_sync are scheduling
+                 points): the real kernels, block scans, launch configurations and C-ABI argument checks run on the CPU.
+
+The product's host code (gaussian_splatting_b200/densify.py, plyio.py) is driven on CPU tensors with its native calls
+redirected to the emulation (monkeypatched in this test only — the product has no CPU path), and the result is compared
+with the golden vectors of the reference's own GaussianModel (tests/golden/densify_golden.npz) and with the oracle.
+The -m gpu tests (tests/test_zz_densify_gpu.py) run the same kernels on the device against the same vectors."""
 import contextlib
 import ctypes as C
 import os
@@ -43,9 +47,34 @@ def load_emul():
     return lib
 
 
+def load_kernel_emul():
+    """Builds (if stale) tests/host_emul/libgsrast_emul.so: the product's .cu sources compiled as C++ (-DGSR_HOST_EMUL)
+    against the CUDA stand-in of tests/host_emul/cuda_emul; exports the same C-ABI as libgsrast.so for those files."""
+    emu_dir = os.path.join(HERE, "host_emul", "cuda_emul")
+    csrc = os.path.join(HERE, "..", "gaussian_splatting_b200", "csrc")
+    out = os.path.join(HERE, "host_emul", "libgsrast_emul.so")
+    units = [os.path.join(csrc, "densify.cu")]
+    deps = units + [os.path.join(emu_dir, f) for f in os.listdir(emu_dir)] + \
+        [os.path.join(csrc, f) for f in ("common.cuh", "block_scan.cuh", "densify_core.cuh")]
+    if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(d) for d in deps):
+        cmd = ["g++", "-std=c++17", "-O1", "-shared", "-fPIC", "-ffp-contract=off", "-DGSR_HOST_EMUL", "-I" + emu_dir]
+        for u in units:
+            cmd += ["-x", "c++", u]
+        cmd += ["-x", "c++", os.path.join(emu_dir, "emul.cpp"), os.path.join(emu_dir, "api_stub.cpp"), "-o", out]
+        subprocess.check_call(cmd)
+    lib = _lib.bind_densify(C.CDLL(out))
+    lib.gsr_last_error.restype = C.c_char_p
+    return lib
+
+
 @pytest.fixture(scope="module")
 def emul():
     return load_emul()
+
+
+@pytest.fixture(scope="module")
+def kernel_emul():
+    return load_kernel_emul()
 
 
 class FakeLib:
@@ -81,9 +110,9 @@ class FakeLib:
         return b"emulation"
 
 
-@pytest.fixture()
-def on_cpu(emul, monkeypatch):
-    fake = FakeLib(emul)
+@pytest.fixture(params=("per-element", "kernels"))
+def on_cpu(request, emul, kernel_emul, monkeypatch):
+    fake = FakeLib(emul) if request.param == "per-element" else kernel_emul
     monkeypatch.setattr(_lib, "load", lambda: fake)
     for mod in (densify,):
         monkeypatch.setattr(mod, "_require_cuda", lambda t, what: None)
