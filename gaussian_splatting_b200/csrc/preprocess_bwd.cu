@@ -37,7 +37,11 @@ __device__ __forceinline__ float sq(float x) { return x * x; }
 template <bool MM>
 __device__ __forceinline__ void out1(float* p, float v) {
     if (MM) {
+#ifndef GSR_HOST_EMUL
         if (v != 0.f) asm volatile("multimem.red.relaxed.sys.global.add.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+#else
+        *p += v;                         // CPU emulation: one rank, the "multicast" buffer is the local one
+#endif
     } else {
         *p = v;
     }
@@ -45,9 +49,13 @@ __device__ __forceinline__ void out1(float* p, float v) {
 template <bool MM>
 __device__ __forceinline__ void out4(float* p, float4 v) {
     if (MM) {
+#ifndef GSR_HOST_EMUL
         if (v.x != 0.f || v.y != 0.f || v.z != 0.f || v.w != 0.f)
             asm volatile("multimem.red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};"
                          ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+#else
+        p[0] += v.x; p[1] += v.y; p[2] += v.z; p[3] += v.w;
+#endif
     } else {
         *reinterpret_cast<float4*>(p) = v;
     }

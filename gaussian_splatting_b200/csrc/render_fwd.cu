@@ -200,7 +200,11 @@ int launch_count_work(const GsrParams& p, GeomState g, ImgState im, BinState b, 
     GSR_CUDA_TRY(cudaMemsetAsync(counts, 0, 3 * sizeof(unsigned long long), st));
     dim3 grid((p.W + TILE_X - 1) / TILE_X, (p.H + TILE_Y - 1) / TILE_Y, 1);
     dim3 block(TILE_X, TILE_Y, 1);
+#ifndef GSR_HOST_EMUL
     count_work_kernel<<<grid, block, 0, st>>>(im.ranges, b.point_list, p.W, p.H, g.rec, counts);
+#else
+    emu::launch(grid, block, [&]() { count_work_kernel(im.ranges, b.point_list, p.W, p.H, g.rec, counts); });
+#endif
     return check_stage("count work", true, st);
 }
 

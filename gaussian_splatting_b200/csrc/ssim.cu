@@ -84,7 +84,11 @@ __device__ __forceinline__ void vtaps4(const float (*sx)[SS_T], int row0, int co
 // 1/x to ~1 ulp without the slow path of IEEE division (x is never denormal here: A >= C1, B >= C2)
 __device__ __forceinline__ float rcp_newton(float x) {
     float r;
+#ifndef GSR_HOST_EMUL
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+#else
+    r = 1.0f / x;
+#endif
     return fmaf(r, fmaf(-x, r, 1.0f), r);
 }
 

@@ -21,12 +21,13 @@
 #define __shared__ static
 #define __grid_constant__
 #define __restrict__
-#define __align__(n) alignas(n)
+#define __align__(n) __attribute__((aligned(n)))
 
 struct uint2 { uint32_t x, y; };
 struct uint3 { uint32_t x, y, z; };
 struct alignas(16) uint4 { uint32_t x, y, z, w; };
 struct int2 { int x, y; };
+struct alignas(16) ulonglong2 { unsigned long long x, y; };
 struct alignas(8) float2 { float x, y; };
 struct float3 { float x, y, z; };
 struct alignas(16) float4 { float x, y, z, w; };
@@ -54,6 +55,21 @@ static inline cudaError_t cudaMemcpyAsync(void* d, const void* s, size_t n, cuda
     return cudaSuccess;
 }
 
+// events and side streams: everything is synchronous, so these only have to exist
+typedef void* cudaEvent_t;
+enum { cudaEventDisableTiming = 2, cudaStreamNonBlocking = 1 };
+enum cudaFuncAttribute { cudaFuncAttributePreferredSharedMemoryCarveout = 9, cudaFuncAttributeMaxDynamicSharedMemorySize = 8 };
+enum { cudaSharedmemCarveoutMaxShared = 100 };
+static inline cudaError_t cudaEventCreate(cudaEvent_t* e) { *e = (void*)1; return cudaSuccess; }
+static inline cudaError_t cudaEventCreateWithFlags(cudaEvent_t* e, unsigned) { *e = (void*)1; return cudaSuccess; }
+static inline cudaError_t cudaEventRecord(cudaEvent_t, cudaStream_t = nullptr) { return cudaSuccess; }
+static inline cudaError_t cudaEventSynchronize(cudaEvent_t) { return cudaSuccess; }
+static inline cudaError_t cudaEventElapsedTime(float* ms, cudaEvent_t, cudaEvent_t) { *ms = 0.f; return cudaSuccess; }
+static inline cudaError_t cudaStreamWaitEvent(cudaStream_t, cudaEvent_t, unsigned = 0) { return cudaSuccess; }
+static inline cudaError_t cudaStreamCreateWithFlags(cudaStream_t* s, unsigned) { *s = (void*)2; return cudaSuccess; }
+static inline cudaError_t cudaGetDevice(int* d) { *d = 0; return cudaSuccess; }
+template <typename F> static inline cudaError_t cudaFuncSetAttribute(F, cudaFuncAttribute, int) { return cudaSuccess; }
+
 namespace emu {
 struct Idx { unsigned x, y, z; };
 // per-fiber / per-block coordinates, updated by the scheduler on every switch
@@ -66,6 +82,7 @@ uint32_t warp_shfl(uint32_t mask, uint32_t value, int src_lane);
 uint32_t warp_ballot(uint32_t mask, int pred);
 void warp_sync(uint32_t mask);
 unsigned lane_id();
+void spin();     // a polling loop's body: give the other fibers of the block a turn
 }  // namespace emu
 
 #define threadIdx emu::g_threadIdx
@@ -81,34 +98,46 @@ static inline int __any_sync(uint32_t mask, int pred) { return emu::warp_ballot(
 static inline int __all_sync(uint32_t mask, int pred) { return emu::warp_ballot(mask, !pred) == 0; }
 static inline uint32_t __activemask() { return 0xffffffffu; }
 
-template <typename T> static inline uint32_t emu_bits(T v) { uint32_t b; static_assert(sizeof(T) == 4, "32-bit"); memcpy(&b, &v, 4); return b; }
-template <typename T> static inline T emu_from_bits(uint32_t b) { T v; memcpy(&v, &b, 4); return v; }
+// shuffle of any trivially copyable type up to 8 bytes, 32 bits at a time
+template <typename T> static inline T emu_shfl_from(uint32_t mask, T v, int src_lane) {
+    static_assert(sizeof(T) <= 8, "shuffle operand too wide");
+    uint32_t w[2] = {0, 0};
+    memcpy(w, &v, sizeof(T));
+    w[0] = emu::warp_shfl(mask, w[0], src_lane);
+    if (sizeof(T) > 4) w[1] = emu::warp_shfl(mask, w[1], src_lane);
+    T r;
+    memcpy(&r, w, sizeof(T));
+    return r;
+}
 template <typename T> static inline T __shfl_sync(uint32_t mask, T v, int src, int width = 32) {
     const int lane = (int)emu::lane_id();
-    return emu_from_bits<T>(emu::warp_shfl(mask, emu_bits(v), (lane & ~(width - 1)) | (src & (width - 1))));
+    return emu_shfl_from(mask, v, (lane & ~(width - 1)) | (src & (width - 1)));
 }
 template <typename T> static inline T __shfl_xor_sync(uint32_t mask, T v, int delta, int width = 32) {
-    const int lane = (int)emu::lane_id();
     (void)width;
-    return emu_from_bits<T>(emu::warp_shfl(mask, emu_bits(v), lane ^ delta));
+    return emu_shfl_from(mask, v, (int)emu::lane_id() ^ delta);
 }
 template <typename T> static inline T __shfl_up_sync(uint32_t mask, T v, unsigned delta, int width = 32) {
     const int lane = (int)emu::lane_id();
     const int src = lane - (int)delta;
-    return emu_from_bits<T>(emu::warp_shfl(mask, emu_bits(v), (src < (lane & ~(width - 1))) ? lane : src));
+    return emu_shfl_from(mask, v, (src < (lane & ~(width - 1))) ? lane : src);
 }
 template <typename T> static inline T __shfl_down_sync(uint32_t mask, T v, unsigned delta, int width = 32) {
     const int lane = (int)emu::lane_id();
     const int src = lane + (int)delta;
-    return emu_from_bits<T>(emu::warp_shfl(mask, emu_bits(v), (src > (lane | (width - 1))) ? lane : src));
+    return emu_shfl_from(mask, v, (src > (lane | (width - 1))) ? lane : src);
 }
-static inline uint64_t __shfl_sync(uint32_t mask, uint64_t v, int src) {
-    const uint32_t lo = __shfl_sync(mask, (uint32_t)v, src), hi = __shfl_sync(mask, (uint32_t)(v >> 32), src);
-    return ((uint64_t)hi << 32) | lo;
+// lanes of `mask` holding the same value as the caller
+static inline uint32_t __match_any_sync(uint32_t mask, uint32_t v) {
+    uint32_t m = 0;
+    for (int l = 0; l < 32; l++) {
+        const uint32_t other = emu::warp_shfl(mask, v, l);
+        if (((mask >> l) & 1u) && other == v) m |= 1u << l;
+    }
+    return m;
 }
-static inline unsigned long long __shfl_sync(uint32_t mask, unsigned long long v, int src) {
-    return (unsigned long long)__shfl_sync(mask, (uint64_t)v, src);
-}
+template <typename T> static inline uint32_t emu_bits(T v) { uint32_t b; static_assert(sizeof(T) == 4, "32-bit"); memcpy(&b, &v, 4); return b; }
+template <typename T> static inline T emu_from_bits(uint32_t b) { T v; memcpy(&v, &b, 4); return v; }
 
 // fibers of one block never run concurrently: plain read-modify-write is atomic
 template <typename T> static inline T atomicAdd(T* p, T v) { T o = *p; *p = o + v; return o; }

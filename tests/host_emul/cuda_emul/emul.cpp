@@ -87,6 +87,8 @@ template <typename F> void warp_barrier(uint32_t mask, F last) {
 }
 }  // namespace
 
+void spin() { yield(); }
+
 unsigned lane_id() { return g_blk->fibers[g_blk->cur].linear & 31u; }
 
 void warp_sync(uint32_t mask) { warp_barrier(mask, [](Warp&) {}); }

@@ -1,0 +1,297 @@
+"""The product's CUDA kernels executed on the CPU (no GPU in the authoring container) against the C oracle.
+
+tests/host_emul/cuda_emul provides a stand-in `cuda_runtime.h` and a fiber scheduler (every CUDA thread of a block is a
+fiber; __syncthreads, __shfl_*_sync, __ballot_sync, ... are scheduling points; bulk async copies complete at issue).
+ALL of gaussian_splatting_b200/csrc/*.cu is compiled as C++ against it into tests/host_emul/libgsrast_emul.so, which
+exports the same C-ABI as libgsrast.so; this test drives it the way a non-Python host would (plain pointers, numpy
+buffers): gsr_forward_stage1 -> R -> gsr_forward_stage2 -> gsr_backward, gsr_mark_visible, gsr_adam_update, gsr_ssim_*.
+Checked against oracle/ with the tolerances of the GPU parity tests: radii / num_rendered / point_list / ranges /
+n_contrib exact, images 1e-5, gradients 1e-3 relative.  What the emulation cannot show (races, asynchrony, speed) is
+the business of the -m gpu tests; what it does show is that the kernel sources compute the reference's results."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+import torch
+
+from gaussian_splatting_b200 import _lib
+from gaussian_splatting_b200._lib import GsrBackwardIO, GsrBuffers, GsrForwardOut, GsrParams
+from tests.helpers import np_inputs, np_settings, rel_err, run_oracle, small_scene
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "..", "gaussian_splatting_b200", "csrc")
+EMU = os.path.join(HERE, "host_emul", "cuda_emul")
+UNITS = ("api", "preprocess", "binning", "render_fwd", "render_bwd", "preprocess_bwd", "adam", "ssim", "exchange", "densify")
+VP = C.c_void_p
+
+
+def load_full_emul():
+    out = os.path.join(HERE, "host_emul", "libgsrast_full_emul.so")
+    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(EMU, f) for f in ("cuda_runtime.h", "emul.cpp")]
+    deps.append(os.path.join(HERE, "..", "include", "gsrast.h"))
+    if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(d) for d in deps):
+        objs = []
+        procs = []
+        for u in UNITS:
+            o = os.path.join(HERE, "host_emul", f"_emul_{u}.o")
+            objs.append(o)
+            procs.append(subprocess.Popen(["g++", "-std=c++17", "-O1", "-fPIC", "-ffp-contract=off", "-DGSR_HOST_EMUL",
+                                           "-I" + EMU, "-c", "-x", "c++", os.path.join(CSRC, u + ".cu"), "-o", o]))
+        assert all(p.wait() == 0 for p in procs)
+        subprocess.check_call(["g++", "-std=c++17", "-O1", "-shared", "-fPIC", "-I" + EMU, os.path.join(EMU, "emul.cpp")]
+                              + objs + ["-o", out])
+    lib = C.CDLL(out)
+    PP, PB, PO = C.POINTER(GsrParams), C.POINTER(GsrBuffers), C.POINTER(GsrForwardOut)
+    lib.gsr_last_error.restype = C.c_char_p
+    for n, a in (("gsr_geom_bytes", [C.c_int32]), ("gsr_img_bytes", [C.c_int32, C.c_int32]), ("gsr_bin_bytes", [C.c_int64]),
+                 ("gsr_scratch_bytes", [C.c_int32, C.c_int32, C.c_int32, C.c_int64])):
+        getattr(lib, n).restype = C.c_size_t
+        getattr(lib, n).argtypes = a
+    lib.gsr_forward_stage1.argtypes = [PP, PB, PO, VP]
+    lib.gsr_forward_stage2.argtypes = [PP, PB, PO, C.c_int64, VP]
+    lib.gsr_backward.argtypes = [PP, PB, C.c_int64, VP, C.POINTER(GsrBackwardIO), VP]
+    lib.gsr_mark_visible.argtypes = [C.c_int32, VP, VP, VP, VP, VP]
+    lib.gsr_debug_state_ptrs.argtypes = [PP, PB, C.c_int64] + [C.POINTER(VP)] * 5
+    lib.gsr_debug_sorted_keys.argtypes = [PP, PB, C.c_int64, VP, VP]
+    lib.gsr_adam_update.argtypes = [VP] * 5 + [C.c_double] * 6 + [C.c_int64, C.c_int32, VP]
+    PS = C.POINTER(_lib.GsrSsimParams)
+    lib.gsr_ssim_partials.restype = C.c_int64
+    lib.gsr_ssim_partials.argtypes = [C.c_int32] * 4
+    lib.gsr_ssim_forward.argtypes = [PS] + [VP] * 7
+    lib.gsr_ssim_backward.argtypes = [PS] + [VP] * 7
+    return lib
+
+
+@pytest.fixture(scope="module")
+def klib():
+    return load_full_emul()
+
+
+def ok(lib, rc):
+    assert rc == 0, lib.gsr_last_error().decode()
+
+
+def aligned(nbytes, align=256):
+    raw = np.zeros(int(nbytes) + align, np.uint8)
+    off = (-raw.ctypes.data) % align
+    return raw[off:off + int(nbytes)]
+
+
+def f32(a):
+    return np.ascontiguousarray(np.asarray(a, np.float32))
+
+
+class EmulRasterizer:
+    """One forward (+ backward) through the emulated library, buffers owned here as a C host would own them."""
+
+    def __init__(self, lib, gs, s, split_sh=False):
+        self.lib = lib
+        inp, st = np_inputs(gs), np_settings(s)
+        self.P = P = inp["means3D"].shape[0]
+        self.W, self.H = int(st["image_width"]), int(st["image_height"])
+        self.keep = k = {n: f32(inp[n]) for n in inp}
+        k["bg"], k["view"], k["proj"], k["campos"] = f32(st["bg"]), f32(st["viewmatrix"]), f32(st["projmatrix"]), f32(st["campos"])
+        p = self.p = GsrParams()
+        p.P, p.D, p.W, p.H = P, int(st["sh_degree"]), self.W, self.H
+        p.tanfovx, p.tanfovy, p.scale_modifier = float(st["tanfovx"]), float(st["tanfovy"]), float(st["scale_modifier"])
+        p.prefiltered, p.antialiasing, p.debug = 0, int(bool(st["antialiasing"])), 0
+        ptr = lambda a: a.ctypes.data
+        p.background, p.means3D, p.opacities = ptr(k["bg"]), ptr(k["means3D"]), ptr(k["opacities"])
+        p.viewmatrix, p.projmatrix, p.campos = ptr(k["view"]), ptr(k["proj"]), ptr(k["campos"])
+        self.split = split_sh
+        if "shs" in k:
+            p.M = k["shs"].shape[1]
+            if split_sh:
+                k["dc"], k["rest"] = f32(k["shs"][:, :1]), f32(k["shs"][:, 1:])
+                p.sh_dc, p.shs = ptr(k["dc"]), ptr(k["rest"])
+            else:
+                p.shs = ptr(k["shs"])
+        else:
+            p.colors_precomp = ptr(k["colors_precomp"])
+        if "scales" in k:
+            p.scales, p.rotations = ptr(k["scales"]), ptr(k["rotations"])
+        else:
+            p.cov3D_precomp = ptr(k["cov3D_precomp"])
+        b = self.b = GsrBuffers()
+        self.geom, self.img = aligned(lib.gsr_geom_bytes(P)), aligned(lib.gsr_img_bytes(self.W, self.H))
+        self.scratch = aligned(lib.gsr_scratch_bytes(P, self.W, self.H, 0))
+        self.pinned = np.zeros(2, np.int32)
+        b.geom, b.geom_bytes, b.img, b.img_bytes = ptr(self.geom), self.geom.nbytes, ptr(self.img), self.img.nbytes
+        b.scratch, b.scratch_bytes, b.num_rendered_host = ptr(self.scratch), self.scratch.nbytes, ptr(self.pinned)
+        self.color, self.invdepth = np.zeros((3, self.H, self.W), np.float32), np.zeros((1, self.H, self.W), np.float32)
+        self.radii = np.zeros(P, np.int32)
+        self.o = GsrForwardOut(ptr(self.color), ptr(self.invdepth), ptr(self.radii))
+
+    def forward(self):
+        lib, p, b, o = self.lib, self.p, self.b, self.o
+        ok(lib, lib.gsr_forward_stage1(C.byref(p), C.byref(b), C.byref(o), None))
+        self.R = R = int(self.pinned[0])
+        assert self.pinned[1] == 0
+        need = lib.gsr_scratch_bytes(self.P, self.W, self.H, R)
+        if need > self.scratch.nbytes:                 # regrow keeps the stage-1 prefix
+            new = aligned(need)
+            new[:self.scratch.nbytes] = self.scratch
+            self.scratch = new
+            b.scratch, b.scratch_bytes = new.ctypes.data, new.nbytes
+        self.bin = aligned(lib.gsr_bin_bytes(R))
+        b.bin, b.bin_bytes = self.bin.ctypes.data, self.bin.nbytes
+        ok(lib, lib.gsr_forward_stage2(C.byref(p), C.byref(b), C.byref(o), R, None))
+        return self
+
+    def state(self):
+        ptrs = [VP() for _ in range(5)]
+        ok(self.lib, self.lib.gsr_debug_state_ptrs(C.byref(self.p), C.byref(self.b), self.R, *[C.byref(x) for x in ptrs]))
+        T = ((self.W + 15) // 16) * ((self.H + 15) // 16)
+        N = self.W * self.H
+        arr = lambda q, n, dt: np.ctypeslib.as_array(C.cast(q, C.POINTER(C.c_uint32)), (n,)).view(dt).copy()
+        keys = np.zeros(max(self.R, 1), np.uint64)
+        ok(self.lib, self.lib.gsr_debug_sorted_keys(C.byref(self.p), C.byref(self.b), self.R, keys.ctypes.data, None))
+        return dict(point_list=arr(ptrs[0], self.R, np.uint32), ranges=arr(ptrs[1], 2 * T, np.uint32).reshape(T, 2),
+                    final_T=arr(ptrs[2], N, np.float32), n_contrib=arr(ptrs[3], N, np.uint32), keys=keys[:self.R])
+
+    def backward(self, dc, dd):
+        P, M = self.P, self.p.M
+        g = {"means3D": np.empty((P, 3), np.float32), "means2D": np.empty((P, 3), np.float32),
+             "opacities": np.empty((P, 1), np.float32)}
+        io = GsrBackwardIO()
+        self.dc, self.dd = f32(dc), (None if dd is None else f32(dd))
+        io.dL_dout_color = self.dc.ctypes.data
+        io.dL_dout_invdepth = None if dd is None else self.dd.ctypes.data
+        io.dL_dmeans3D, io.dL_dmeans2D, io.dL_dopacity = (g[n].ctypes.data for n in ("means3D", "means2D", "opacities"))
+        if self.p.shs:
+            if self.split:
+                g["dc"], g["rest"] = np.empty((P, 1, 3), np.float32), np.empty((P, M - 1, 3), np.float32)
+                io.dL_dsh_dc, io.dL_dsh = g["dc"].ctypes.data, g["rest"].ctypes.data
+            else:
+                g["shs"] = np.empty((P, M, 3), np.float32)
+                io.dL_dsh = g["shs"].ctypes.data
+        else:
+            g["colors_precomp"] = np.empty((P, 3), np.float32)
+            io.dL_dcolors = g["colors_precomp"].ctypes.data
+        if self.p.scales:
+            g["scales"], g["rotations"] = np.empty((P, 3), np.float32), np.empty((P, 4), np.float32)
+            io.dL_dscales, io.dL_drotations = g["scales"].ctypes.data, g["rotations"].ctypes.data
+        else:
+            g["cov3D_precomp"] = np.empty((P, 6), np.float32)
+            io.dL_dcov3D = g["cov3D_precomp"].ctypes.data
+        for a in g.values():
+            a.fill(np.nan)                       # every output must be fully written (gsrast.h)
+        ok(self.lib, self.lib.gsr_backward(C.byref(self.p), C.byref(self.b), self.R, self.radii.ctypes.data, C.byref(io), None))
+        if self.split:
+            g["shs"] = np.concatenate((g.pop("dc"), g.pop("rest")), 1)
+        return g
+
+
+def upstream(W, H, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    return torch.randn(3, H, W, generator=g) / 100, torch.randn(1, H, W, generator=g) / 100
+
+
+def check_against_oracle(lib, oracle, gs, s, dd_on=True, split_sh=False, state=True):
+    W, H = int(s["image_width"]), int(s["image_height"])
+    dc, dd = upstream(W, H)
+    want = run_oracle(oracle, gs, s, dc, dd if dd_on else None)
+    er = EmulRasterizer(lib, gs, s, split_sh).forward()
+    assert np.array_equal(er.radii, want["radii"])
+    fw = want["fw"]
+    assert er.R == int(fw["R"])
+    assert np.abs(er.color - want["color"]).max() <= 1e-5 and np.abs(er.invdepth - want["invdepth"]).max() <= 1e-5
+    if state:
+        st = er.state()
+        assert np.array_equal(st["point_list"], fw["point_list"][:er.R])
+        assert np.array_equal(st["ranges"], np.asarray(fw["ranges"]).reshape(-1, 2))
+        assert np.array_equal(st["n_contrib"], np.asarray(fw["n_contrib"]).reshape(-1))
+        assert np.abs(st["final_T"] - np.asarray(fw["final_T"]).reshape(-1)).max() <= 1e-5
+        assert np.array_equal(st["keys"], fw["keys"])          # tile << 32 | depth bits, sorted
+    got = er.backward(dc.numpy(), dd.numpy() if dd_on else None)
+    for k, g in got.items():
+        assert np.isfinite(g).all(), k
+        assert rel_err(g, np.asarray(want["grads"][k]).reshape(g.shape)) < 1e-3, k
+    return er
+
+
+def test_forward_backward_sh_scale_rotation(klib, oracle):
+    gs, s = small_scene(P=600, W=64, H=48, seed=1, antialiasing=True, bg=(0.1, 0.3, 0.6))
+    check_against_oracle(klib, oracle, gs, s)
+
+
+def test_split_sh_storage_and_no_depth_gradient(klib, oracle):
+    gs, s = small_scene(P=300, W=48, H=32, seed=2, sh_degree=2)
+    check_against_oracle(klib, oracle, gs, s, dd_on=False, split_sh=True, state=False)
+
+
+def test_precomputed_colors_and_covariances(klib, oracle):
+    gs, s = small_scene(P=300, W=40, H=40, seed=3, sh_degree=0, bg=(1.0, 1.0, 1.0))
+    g = torch.Generator().manual_seed(9)
+    gs = dict(gs)
+    gs["colors_precomp"] = torch.rand(300, 3, generator=g)
+    del gs["shs"]
+    # a valid covariance: the one the scales / rotations describe (computeCov3D layout xx xy xz yy yz zz)
+    q, sc = gs.pop("rotations"), gs.pop("scales")
+    w, x, y, z = q.unbind(1)
+    R = torch.stack((1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y),
+                     2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x),
+                     2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)), 1).reshape(-1, 3, 3)
+    Sg = R @ torch.diag_embed(sc * sc) @ R.transpose(1, 2)
+    gs["cov3D_precomp"] = torch.stack((Sg[:, 0, 0], Sg[:, 0, 1], Sg[:, 0, 2], Sg[:, 1, 1], Sg[:, 1, 2], Sg[:, 2, 2]), 1).contiguous()
+    check_against_oracle(klib, oracle, gs, s, state=False)
+
+
+def test_ragged_image_and_many_batches(klib, oracle):
+    # image not a multiple of the tile size; > 256 entries in a tile => several double-buffered batches per tile
+    gs, s = small_scene(P=1500, W=37, H=21, seed=4, scale_mult=10.0, behind_fraction=0.0)
+    er = check_against_oracle(klib, oracle, gs, s)
+    assert er.R / 6 > 256
+
+
+def test_mark_visible(klib, oracle):
+    gs, s = small_scene(P=500, W=32, H=32, seed=5, behind_fraction=0.4)
+    means, view, proj = f32(gs["means3D"]), f32(s["viewmatrix"]), f32(s["projmatrix"])
+    present = np.zeros(500, np.uint8)
+    ok(klib, klib.gsr_mark_visible(500, means.ctypes.data, view.ctypes.data, proj.ctypes.data, present.ctypes.data, None))
+    z = means @ view[:3, 2] + view[3, 2]                       # (W2V p).z with the column-major matrix
+    assert np.array_equal(present.astype(bool), z > 0.2) and 0 < present.sum() < 500
+
+
+def test_adam_kernel_matches_torch(klib):
+    g = torch.Generator().manual_seed(0)
+    N, M = 257, 45
+    p = torch.randn(N, M, generator=g)
+    grad, m, v = torch.randn(N, M, generator=g), torch.zeros(N, M), torch.zeros(N, M)
+    ref = torch.nn.Parameter(p.clone())
+    opt = torch.optim.Adam([ref], lr=1e-2, eps=1e-15)
+    vis = (torch.rand(N, generator=g) < 0.6).to(torch.uint8)
+    pa, ga, ma, va = (f32(t.numpy()) for t in (p, grad, m, v))
+    for step in (1, 2, 3):
+        ref.grad = grad * vis[:, None]
+        opt.step()
+        ok(klib, klib.gsr_adam_update(pa.ctypes.data, ga.ctypes.data, ma.ctypes.data, va.ctypes.data,
+                                      vis.numpy().ctypes.data, 1e-2, 0.9, 0.999, 1e-15, 1 - 0.9 ** step,
+                                      (1 - 0.999 ** step) ** 0.5, N, M, None))
+    visb = vis.bool().numpy()
+    # visible rows: torch.optim.Adam's update; invisible rows untouched (torch's Adam moves them: zero gradient
+    # still decays the moments, which is the documented difference of the sparse optimizer)
+    assert rel_err(pa[visb], ref.detach().numpy()[visb]) < 1e-6
+    assert np.array_equal(pa[~visb], p.numpy()[~visb]) and not ma[~visb].any()
+
+
+def test_ssim_kernels_match_the_oracle(klib):
+    from oracle import ssim_ref
+    rng = np.random.default_rng(0)
+    B, CH, H, W = 1, 2, 45, 70
+    a, b = rng.random((B, CH, H, W), dtype=np.float32), rng.random((B, CH, H, W), dtype=np.float32)
+    sp = _lib.GsrSsimParams(a.ctypes.data, b.ctypes.data, B, CH, H, W, 0.01 ** 2, 0.03 ** 2, 0)
+    maps = [np.zeros_like(a) for _ in range(4)]
+    mean = np.zeros(1, np.float32)
+    partials = np.zeros(int(klib.gsr_ssim_partials(B, CH, H, W)), np.float32)
+    ok(klib, klib.gsr_ssim_forward(C.byref(sp), *[m.ctypes.data for m in maps], mean.ctypes.data, partials.ctypes.data, None))
+    v_ref, g_ref = ssim_ref.fused_ssim(a, b, dtype=np.float64)
+    m_ref, *_ = ssim_ref.ssim_forward(a, b, dtype=np.float64)
+    assert abs(float(mean[0]) - v_ref) < 1e-6 and np.abs(maps[0] - m_ref).max() < 1e-5
+    dmean = np.ones(1, np.float32)
+    dimg = np.zeros_like(a)
+    ok(klib, klib.gsr_ssim_backward(C.byref(sp), None, dmean.ctypes.data, maps[1].ctypes.data, maps[2].ctypes.data,
+                                    maps[3].ctypes.data, dimg.ctypes.data, None))
+    assert rel_err(dimg, g_ref) < 1e-4
