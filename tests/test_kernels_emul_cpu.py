@@ -295,3 +295,42 @@ def test_ssim_kernels_match_the_oracle(klib):
     ok(klib, klib.gsr_ssim_backward(C.byref(sp), None, dmean.ctypes.data, maps[1].ctypes.data, maps[2].ctypes.data,
                                     maps[3].ctypes.data, dimg.ctypes.data, None))
     assert rel_err(dimg, g_ref) < 1e-4
+
+
+def test_factored_exchange_two_ranks(klib, oracle):
+    """View-parallel exchange with world = 2 on the CPU: two cameras of the same Gaussians run the sender
+    branch of preprocess_bwd.cu with multimem_reduce = 1 — under the emulation a multimem.red is an add into the one
+    local buffer, i.e. exactly the sum the NVSwitch forms in every replica — then gsr_exchange_expand rebuilds the dense
+    gradients; they must equal the sum of the two cameras' ordinary gradients (oracle)."""
+    P, W, H = 400, 48, 32
+    klib.gsr_exchange_expand.argtypes = [C.POINTER(GsrParams), C.c_int32] + [VP] * 10
+    world = 2
+    records = np.zeros((P, 12), np.float32)
+    rgb = np.zeros((world, P, 4), np.float32)
+    campos = np.zeros((world, 4), np.float32)
+    want = None
+    dc, dd = upstream(W, H, seed=3)
+    for r, yaw in enumerate((0.0, 25.0)):
+        gs, s = small_scene(P=P, W=W, H=H, seed=6, yaw_deg=yaw, antialiasing=True, behind_fraction=0.0)   # replicated Gaussians
+        o = run_oracle(oracle, gs, s, dc, dd)
+        want = o["grads"] if want is None else {k: want[k] + o["grads"][k] for k in want if k != "means2D"}
+        er = EmulRasterizer(klib, gs, s).forward()
+        io = GsrBackwardIO()
+        dcn, ddn = f32(dc.numpy()), f32(dd.numpy())
+        m2 = np.full((P, 3), np.nan, np.float32)
+        io.dL_dout_color, io.dL_dout_invdepth, io.dL_dmeans2D = dcn.ctypes.data, ddn.ctypes.data, m2.ctypes.data
+        io.multimem_reduce = 1
+        io.xchg_records, io.xchg_rgb, io.xchg_campos = records.ctypes.data, rgb[r].ctypes.data, campos[r].ctypes.data
+        ok(klib, klib.gsr_backward(C.byref(er.p), C.byref(er.b), er.R, er.radii.ctypes.data, C.byref(io), None))
+        assert rel_err(m2, o["grads"]["means2D"]) < 1e-3       # per-view statistic, never reduced
+        assert np.allclose(campos[r], np.append(f32(s["campos"]), 1.0))
+    out = {"means3D": np.full((P, 3), np.nan, np.float32), "opacities": np.full((P, 1), np.nan, np.float32),
+           "shs": np.full((P, 16, 3), np.nan, np.float32), "scales": np.full((P, 3), np.nan, np.float32),
+           "rotations": np.full((P, 4), np.nan, np.float32)}
+    ok(klib, klib.gsr_exchange_expand(C.byref(er.p), world, records.ctypes.data, rgb.ctypes.data, campos.ctypes.data,
+                                      out["means3D"].ctypes.data, out["opacities"].ctypes.data, out["shs"].ctypes.data,
+                                      out["scales"].ctypes.data, out["rotations"].ctypes.data, None, None))
+    for k, g in out.items():
+        assert rel_err(g, np.asarray(want[k]).reshape(g.shape)) < 1e-3, k
+    # self-cleaning buffers: the rows expand consumed are zero again for the next step
+    assert not records.any() and not rgb.any()
