@@ -1,8 +1,12 @@
+// (Switching: a fiber is entered once through makecontext / swapcontext; every later switch is a
+// _setjmp / _longjmp pair, which unlike swapcontext makes no signal-mask system call — build without _FORTIFY_SOURCE,
+// whose longjmp check rejects jumps between stacks.)
 // emul.cpp — cooperative fiber scheduler behind tests/host_emul/cuda_emul/cuda_runtime.h (TEST INFRASTRUCTURE).
 // One block at a time; its threads are ucontext fibers resumed round-robin.  A fiber runs until it finishes or
 // blocks in a barrier (block-wide: __syncthreads; warp-wide: every *_sync primitive).  Threads that have exited no
 // longer count for barriers (CUDA semantics).  If no fiber can make progress the emulation aborts (a barrier that
 // not all live threads reach is a bug in the kernel on the GPU too).
+#include <setjmp.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <ucontext.h>
@@ -28,8 +32,9 @@ struct Warp {
 
 struct Fiber {
     ucontext_t ctx;
+    jmp_buf jb;
     char* stack = nullptr;
-    bool done = false;
+    bool done = false, started = false;
     Idx tid;
     unsigned linear = 0;
 };
@@ -38,6 +43,7 @@ struct Block {
     std::vector<Fiber> fibers;
     std::vector<Warp> warps;
     ucontext_t sched;
+    jmp_buf sched_jb;
     unsigned cur = 0, alive = 0;
     unsigned bar_arrived = 0, bar_gen = 0;
     int bar_count = 0, bar_count_out = 0;
@@ -49,7 +55,7 @@ Block* g_blk = nullptr;
 
 void yield() {
     Block* b = g_blk;
-    swapcontext(&b->fibers[b->cur].ctx, &b->sched);
+    if (!_setjmp(b->fibers[b->cur].jb)) _longjmp(b->sched_jb, 1);
 }
 
 void trampoline() {
@@ -60,7 +66,7 @@ void trampoline() {
     b->alive--;
     b->warps[f.linear >> 5].alive &= ~(1u << (f.linear & 31));
     b->progress++;
-    swapcontext(&f.ctx, &b->sched);
+    _longjmp(b->sched_jb, 1);
 }
 
 // Warp barrier over the live lanes of `mask`; `last` runs once, by the lane that completes the barrier.
@@ -158,6 +164,7 @@ void launch(dim3 grid, dim3 block, const std::function<void()>& body) {
                 for (unsigned t = 0; t < n; t++) {
                     Fiber& f = blk.fibers[t];
                     f.done = false;
+                    f.started = false;
                     f.linear = t;
                     f.tid = {t % block.x, (t / block.x) % block.y, t / (block.x * block.y)};
                     blk.warps[t >> 5].alive |= 1u << (t & 31);
@@ -174,7 +181,11 @@ void launch(dim3 grid, dim3 block, const std::function<void()>& body) {
                         if (f.done) continue;
                         blk.cur = t;
                         g_threadIdx = f.tid;
-                        swapcontext(&blk.sched, &f.ctx);
+                        if (!_setjmp(blk.sched_jb)) {
+                            if (f.started) _longjmp(f.jb, 1);
+                            f.started = true;
+                            setcontext(&f.ctx);              // first entry: switch to the fiber's own stack
+                        }
                     }
                     if (blk.progress == before) {
                         fprintf(stderr, "cuda_emul: deadlock in block (%u,%u,%u): %u live threads wait at barriers "

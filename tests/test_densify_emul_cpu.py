@@ -57,7 +57,7 @@ def load_kernel_emul():
     deps = units + [os.path.join(emu_dir, f) for f in os.listdir(emu_dir)] + \
         [os.path.join(csrc, f) for f in ("common.cuh", "block_scan.cuh", "densify_core.cuh")]
     if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(d) for d in deps):
-        cmd = ["g++", "-std=c++17", "-O1", "-shared", "-fPIC", "-ffp-contract=off", "-DGSR_HOST_EMUL", "-I" + emu_dir]
+        cmd = ["g++", "-std=c++17", "-O1", "-shared", "-fPIC", "-ffp-contract=off", "-U_FORTIFY_SOURCE", "-D_FORTIFY_SOURCE=0", "-DGSR_HOST_EMUL", "-I" + emu_dir]
         for u in units:
             cmd += ["-x", "c++", u]
         cmd += ["-x", "c++", os.path.join(emu_dir, "emul.cpp"), os.path.join(emu_dir, "api_stub.cpp"), "-o", out]

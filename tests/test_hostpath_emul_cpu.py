@@ -1,0 +1,164 @@
+"""The product's PYTHON host layers (autograd Function, workspace handling, SparseGaussianAdam, fused_ssim, density
+control, PLY I/O) executed in the GPU-less container on top of the emulated kernel library.
+
+`_lib` is pointed at tests/host_emul/libgsrast_full_emul.so (all csrc/*.cu compiled against the CUDA emulation, see
+tests/test_kernels_emul_cpu.py) and — in this test process only — the handful of torch.cuda entry points the host code
+touches are replaced by inert stand-ins (current_stream / device / Event / pin_memory / Tensor.is_cuda), so the SAME
+Python code that runs on the B200 runs here on CPU tensors.  The product itself has no CPU path: without these
+test-only patches it refuses CPU tensors (asserted below)."""
+import contextlib
+import types
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import ssim_ref
+from tests.helpers import rel_err, run_module, run_oracle, small_scene
+from tests.test_kernels_emul_cpu import load_full_emul
+
+
+class _Stream:
+    cuda_stream = 0
+
+    def synchronize(self):
+        pass
+
+    def wait_event(self, ev):
+        pass
+
+    def wait_stream(self, s):
+        pass
+
+    def record_event(self, ev=None):
+        return ev or _Event()
+
+
+class _Event:
+    def __init__(self, *a, **k):
+        pass
+
+    def record(self, stream=None):
+        pass
+
+    def synchronize(self):
+        pass
+
+    def wait(self, stream=None):
+        pass
+
+    def elapsed_time(self, other):
+        return 0.0
+
+    def query(self):
+        return True
+
+
+@pytest.fixture()
+def emulated_cuda(monkeypatch):
+    import os
+    from gaussian_splatting_b200 import _lib, densify, plyio, rasterizer
+    load_full_emul()                                   # build if stale
+    here = os.path.dirname(os.path.abspath(__file__))
+    monkeypatch.setattr(_lib, "LIB_PATH", os.path.join(here, "host_emul", "libgsrast_full_emul.so"))
+    monkeypatch.setattr(_lib, "_lib", None)
+    monkeypatch.setattr(torch.cuda, "current_stream", lambda device=None: _Stream())
+    monkeypatch.setattr(torch.cuda, "device", lambda d: contextlib.nullcontext())
+    monkeypatch.setattr(torch.cuda, "current_device", lambda: 0)
+    monkeypatch.setattr(torch.cuda, "synchronize", lambda device=None: None)
+    monkeypatch.setattr(torch.cuda, "Event", _Event)
+    monkeypatch.setattr(torch.Tensor, "pin_memory", lambda self, *a, **k: self)
+    monkeypatch.setattr(torch.Tensor, "is_cuda", property(lambda self: True))
+    monkeypatch.setattr(rasterizer, "_workspaces", {})
+    for mod in (densify, plyio):
+        monkeypatch.setattr(mod, "_device_ctx", lambda d: contextlib.nullcontext())
+    yield
+    _lib._lib = None
+
+
+def test_the_product_refuses_cpu_tensors_without_the_patches():
+    import diff_gaussian_rasterization as dgr
+    from tests.helpers import settings_for
+    gs, s = small_scene(P=10, W=16, H=16)
+    rast = dgr.GaussianRasterizer(settings_for(dgr, s, "cpu"))
+    with pytest.raises(RuntimeError, match="CUDA"):
+        rast(means3D=gs["means3D"], means2D=torch.zeros(10, 3), opacities=gs["opacities"], shs=gs["shs"],
+             scales=gs["scales"], rotations=gs["rotations"])
+
+
+@pytest.mark.parametrize("aa,bg", ((True, (0.1, 0.3, 0.6)), (False, (0.0, 0.0, 0.0))))
+def test_autograd_path_matches_oracle(emulated_cuda, oracle, aa, bg):
+    import diff_gaussian_rasterization as dgr
+    W, H = 64, 48
+    gs, s = small_scene(P=500, W=W, H=H, seed=11, antialiasing=aa, bg=bg)
+    g = torch.Generator().manual_seed(0)
+    dc, dd = torch.randn(3, H, W, generator=g) / 100, torch.randn(1, H, W, generator=g) / 100
+    got = run_module(dgr, gs, s, dc, dd, device="cpu")
+    want = run_oracle(oracle, gs, s, dc, dd)
+    assert np.array_equal(got["radii"], want["radii"])
+    assert np.abs(got["color"] - want["color"]).max() <= 1e-5 and np.abs(got["invdepth"] - want["invdepth"]).max() <= 1e-5
+    for k in ("means3D", "means2D", "opacities", "shs", "scales", "rotations"):
+        assert rel_err(got["grads"][k], want["grads"][k].reshape(got["grads"][k].shape)) < 1e-3, k
+    # a second call reuses the workspace arena; P == 0 returns zero images without a launch
+    again = run_module(dgr, gs, s, dc, dd, device="cpu")
+    assert np.array_equal(again["color"], got["color"])
+    empty = {k: v[:0] for k, v in gs.items()}
+    z = run_module(dgr, empty, s, device="cpu")
+    assert not z["color"].any() and z["radii"].shape == (0,)
+
+
+def test_dc_keyword_equals_concatenated_call(emulated_cuda):
+    import diff_gaussian_rasterization as dgr
+    from tests.helpers import settings_for
+    W, H = 48, 32
+    gs, s = small_scene(P=301, W=W, H=H, seed=12, sh_degree=2)          # ragged: 301 % 4 != 0
+    rast = dgr.GaussianRasterizer(settings_for(dgr, s, "cpu"))
+    outs = []
+    for split in (False, True):
+        leaves = {k: v.clone().requires_grad_(True) for k, v in gs.items()}
+        dcl = gs["shs"][:, :1].clone().requires_grad_(True)
+        rest = gs["shs"][:, 1:].clone().requires_grad_(True)
+        m2 = torch.zeros(301, 3, requires_grad=True)
+        kw = dict(dc=dcl, shs=rest) if split else dict(shs=leaves["shs"])
+        color, radii, invd = rast(means3D=leaves["means3D"], means2D=m2, opacities=leaves["opacities"],
+                                  scales=leaves["scales"], rotations=leaves["rotations"], **kw)
+        (color.sum() + invd.sum()).backward()
+        gsh = torch.cat((dcl.grad, rest.grad), 1) if split else leaves["shs"].grad
+        outs.append((color.detach(), gsh, leaves["means3D"].grad, leaves["scales"].grad))
+    assert torch.equal(outs[0][0], outs[1][0])
+    for a, b in zip(outs[0][1:], outs[1][1:]):
+        assert rel_err(a.numpy(), b.numpy()) < 1e-5
+
+
+def test_sparse_adam_and_fused_ssim(emulated_cuda):
+    import diff_gaussian_rasterization as dgr
+    import fused_ssim as fs
+    g = torch.Generator().manual_seed(3)
+    pa = torch.nn.Parameter(torch.randn(130, 45, generator=g))
+    pb = torch.nn.Parameter(pa.detach().clone())
+    ours = dgr.SparseGaussianAdam([{"params": [pa], "lr": 1e-2, "name": "f_rest"}], lr=0.0, eps=1e-15)
+    ref = torch.optim.Adam([{"params": [pb], "lr": 1e-2}], lr=0.0, eps=1e-15)
+    for _ in range(3):
+        grad = torch.randn(130, 45, generator=g)
+        pa.grad, pb.grad = grad.clone(), grad.clone()
+        ours.step(torch.ones(130, dtype=torch.bool), 130)
+        ref.step()
+    assert rel_err(pa.detach().numpy(), pb.detach().numpy()) < 1e-6
+    img1 = torch.rand(1, 3, 40, 52, generator=g).requires_grad_(True)
+    img2 = torch.rand(1, 3, 40, 52, generator=g)
+    v = fs.fused_ssim(img1, img2)
+    v.backward()
+    v_ref, g_ref = ssim_ref.fused_ssim(img1.detach().numpy(), img2.numpy(), dtype=np.float64)
+    assert abs(float(v.detach()) - v_ref) < 1e-5 and rel_err(img1.grad.numpy(), g_ref) < 1e-3
+
+
+def test_training_slice_of_the_gpu_suite(emulated_cuda, tmp_path, monkeypatch):
+    """tests/test_zz_densify_gpu.py::test_training_slice_render_stats_step_densify_save_load — the callers either side
+    of the rasterizer in one piece — executed here on the emulation."""
+    from gaussian_splatting_b200 import densify, plyio
+    from tests import test_zz_densify_gpu as G
+    monkeypatch.setattr(G, "DEV", "cpu")
+    monkeypatch.setattr(densify, "_pinned_counts", lambda: torch.zeros(4, dtype=torch.int32))
+    monkeypatch.setattr(plyio, "_to_host", lambda rows: rows)
+    monkeypatch.setattr(plyio, "_to_device", lambda host, device: host)
+    G.test_training_slice_render_stats_step_densify_save_load(tmp_path)

@@ -37,10 +37,11 @@ def load_full_emul():
         for u in UNITS:
             o = os.path.join(HERE, "host_emul", f"_emul_{u}.o")
             objs.append(o)
-            procs.append(subprocess.Popen(["g++", "-std=c++17", "-O1", "-fPIC", "-ffp-contract=off", "-DGSR_HOST_EMUL",
+            procs.append(subprocess.Popen(["g++", "-std=c++17", "-O1", "-fPIC", "-ffp-contract=off", "-U_FORTIFY_SOURCE", "-D_FORTIFY_SOURCE=0", "-DGSR_HOST_EMUL",
                                            "-I" + EMU, "-c", "-x", "c++", os.path.join(CSRC, u + ".cu"), "-o", o]))
         assert all(p.wait() == 0 for p in procs)
-        subprocess.check_call(["g++", "-std=c++17", "-O1", "-shared", "-fPIC", "-I" + EMU, os.path.join(EMU, "emul.cpp")]
+        subprocess.check_call(["g++", "-std=c++17", "-O1", "-shared", "-fPIC", "-U_FORTIFY_SOURCE", "-D_FORTIFY_SOURCE=0", "-I" + EMU,
+                               os.path.join(EMU, "emul.cpp")]
                               + objs + ["-o", out])
     lib = C.CDLL(out)
     PP, PB, PO = C.POINTER(GsrParams), C.POINTER(GsrBuffers), C.POINTER(GsrForwardOut)
