@@ -335,3 +335,46 @@ def test_factored_exchange_two_ranks(klib, oracle):
         assert rel_err(g, np.asarray(want[k]).reshape(g.shape)) < 1e-3, k
     # self-cleaning buffers: the rows expand consumed are zero again for the next step
     assert not records.any() and not rgb.any()
+
+
+@pytest.mark.parametrize("bands", (0, 3))
+def test_full_multicast_reduction_with_band_pipelining(klib, oracle, bands):
+    """multimem_reduce = 1 without the factored exchange (`GSR_REDUCE_FACTORED=0`): every gradient store is
+    an add into the (pre-zeroed) replica; with `reserved1 = bands` the blend backward runs tile-row band by band and
+    each band's Gaussians go to the per-Gaussian kernel through index lists.  One rank here, so the result must be the
+    ordinary gradient."""
+    P, W, H = 500, 48, 64
+    gs, s = small_scene(P=P, W=W, H=H, seed=8, antialiasing=True)
+    dc, dd = upstream(W, H, seed=5)
+    want = run_oracle(oracle, gs, s, dc, dd)["grads"]
+    er = EmulRasterizer(klib, gs, s).forward()
+    g = {"means3D": np.zeros((P, 3), np.float32), "opacities": np.zeros((P, 1), np.float32),
+         "shs": np.zeros((P, 16, 3), np.float32), "scales": np.zeros((P, 3), np.float32),
+         "rotations": np.zeros((P, 4), np.float32)}
+    m2 = np.full((P, 3), np.nan, np.float32)
+    io = GsrBackwardIO()
+    dcn, ddn = f32(dc.numpy()), f32(dd.numpy())
+    io.dL_dout_color, io.dL_dout_invdepth, io.dL_dmeans2D = dcn.ctypes.data, ddn.ctypes.data, m2.ctypes.data
+    io.dL_dmeans3D, io.dL_dopacity, io.dL_dsh = g["means3D"].ctypes.data, g["opacities"].ctypes.data, g["shs"].ctypes.data
+    io.dL_dscales, io.dL_drotations = g["scales"].ctypes.data, g["rotations"].ctypes.data
+    io.multimem_reduce, io.reserved1 = 1, bands
+    ok(klib, klib.gsr_backward(C.byref(er.p), C.byref(er.b), er.R, er.radii.ctypes.data, C.byref(io), None))
+    assert rel_err(m2, want["means2D"]) < 1e-3
+    for k, v in g.items():
+        assert rel_err(v, np.asarray(want[k]).reshape(v.shape)) < 1e-3, k
+
+
+def test_debug_mode_and_error_reporting(klib):
+    gs, s = small_scene(P=100, W=32, H=32, seed=9)
+    er = EmulRasterizer(klib, gs, s)
+    er.p.debug = 1                                   # synchronise + check after every stage
+    er.forward()
+    assert er.R > 0
+    bad = EmulRasterizer(klib, gs, s)
+    bad.p.shs = None                                 # neither SHs nor precomputed colours
+    rc = klib.gsr_forward_stage1(C.byref(bad.p), C.byref(bad.b), C.byref(bad.o), None)
+    assert rc == _lib.GSR_ERR_INVALID_ARG
+    assert klib.gsr_last_error().decode() == "Please provide exactly one of either SHs or precomputed colors!"
+    small = EmulRasterizer(klib, gs, s)
+    small.b.geom_bytes = 64
+    assert klib.gsr_forward_stage1(C.byref(small.p), C.byref(small.b), C.byref(small.o), None) == _lib.GSR_ERR_CAPACITY
