@@ -3,9 +3,12 @@
 Restates GaussianModel.save_ply / load_ply (scene/gaussian_model.py:285-321, 329-380) value by value with
 `struct` and Python loops (small cases only), independently of the product's numpy/CUDA row path.
 
-parity unpinned by reference fixtures: the reference writes through the third-party `plyfile` package
-(environment.yml:8, unpinned), which is absent from /root/reference and from this image, and the tree holds no .ply
-file.  The format restated here is PLY 1.0 as plyfile emits it for a structured array of '<f4' fields:
+Pin: the reference writes through the third-party `plyfile` package (environment.yml:8, unpinned), which is absent from
+/root/reference and from this image, and the tree holds no .ply file, so there is no reference FIXTURE.  The row layout
+(attribute order, the f_rest transposition) is pinned by the reference's own code instead: tests/test_plyio_cpu.py runs
+its unmodified GaussianModel.save_ply / load_ply on gaussian_splatting_b200.plyfile_compat and requires its file to
+equal save_ply_bytes() byte for byte.  What stays unpinned is only plyfile's header spelling, restated here from its
+published behaviour — PLY 1.0 for a structured array of '<f4' fields:
     ply\\nformat binary_little_endian 1.0\\nelement vertex <N>\\nproperty float <name>\\n...end_header\\n
 followed by N rows of little-endian float32 in property order."""
 import struct
