@@ -75,7 +75,8 @@ def ok(lib, rc):
 
 
 def aligned(nbytes, align=256):
-    raw = np.zeros(int(nbytes) + align, np.uint8)
+    # state and scratch arrive uninitialised on the device (torch.empty): fill with garbage, not zeros
+    raw = np.full(int(nbytes) + align, 0xA5, np.uint8)
     off = (-raw.ctypes.data) % align
     return raw[off:off + int(nbytes)]
 
