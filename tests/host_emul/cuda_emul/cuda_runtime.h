@@ -82,6 +82,7 @@ uint32_t warp_shfl(uint32_t mask, uint32_t value, int src_lane);
 uint32_t warp_ballot(uint32_t mask, int pred);
 void warp_sync(uint32_t mask);
 unsigned lane_id();
+uint32_t warp_alive();   // lanes of the caller's warp that have not exited
 void spin();     // a polling loop's body: give the other fibers of the block a turn
 }  // namespace emu
 
@@ -130,9 +131,10 @@ template <typename T> static inline T __shfl_down_sync(uint32_t mask, T v, unsig
 // lanes of `mask` holding the same value as the caller
 static inline uint32_t __match_any_sync(uint32_t mask, uint32_t v) {
     uint32_t m = 0;
+    const uint32_t live = mask & emu::warp_alive();
     for (int l = 0; l < 32; l++) {
         const uint32_t other = emu::warp_shfl(mask, v, l);
-        if (((mask >> l) & 1u) && other == v) m |= 1u << l;
+        if (((live >> l) & 1u) && other == v) m |= 1u << l;
     }
     return m;
 }

@@ -53,6 +53,23 @@ struct Block {
 
 Block* g_blk = nullptr;
 
+// GSR_EMUL_SCHED = "reverse" | "random[:seed]": order in which the runnable fibers of a block are resumed in each
+// scheduling pass (default: thread order).  A result that changes with the order means the kernel lacks a barrier
+// between a write and another thread's read — a race on the GPU.
+int g_sched_mode = -1;
+uint64_t g_rng = 0x9E3779B97F4A7C15ull;
+void sched_init() {
+    if (g_sched_mode >= 0) return;
+    const char* e = getenv("GSR_EMUL_SCHED");
+    g_sched_mode = 0;
+    if (e && !strncmp(e, "reverse", 7)) g_sched_mode = 1;
+    if (e && !strncmp(e, "random", 6)) {
+        g_sched_mode = 2;
+        if (e[6] == ':') g_rng ^= strtoull(e + 7, nullptr, 10) * 0xD1342543DE82EF95ull;
+    }
+}
+uint64_t rng() { g_rng ^= g_rng << 13; g_rng ^= g_rng >> 7; g_rng ^= g_rng << 17; return g_rng; }
+
 void yield() {
     Block* b = g_blk;
     if (!_setjmp(b->fibers[b->cur].jb)) _longjmp(b->sched_jb, 1);
@@ -94,6 +111,8 @@ template <typename F> void warp_barrier(uint32_t mask, F last) {
 }  // namespace
 
 void spin() { yield(); }
+
+uint32_t warp_alive() { return g_blk->warps[g_blk->fibers[g_blk->cur].linear >> 5].alive; }
 
 unsigned lane_id() { return g_blk->fibers[g_blk->cur].linear & 31u; }
 
@@ -145,6 +164,9 @@ int syncthreads_count(int pred) {
 
 void launch(dim3 grid, dim3 block, const std::function<void()>& body) {
     const unsigned n = block.x * block.y * block.z;
+    sched_init();
+    std::vector<unsigned> order(n);
+    for (unsigned t = 0; t < n; t++) order[t] = g_sched_mode == 1 ? n - 1 - t : t;
     Block blk;
     blk.body = &body;
     blk.fibers.resize(n);
@@ -176,7 +198,10 @@ void launch(dim3 grid, dim3 block, const std::function<void()>& body) {
                 }
                 while (blk.alive) {
                     const unsigned long long before = blk.progress;
-                    for (unsigned t = 0; t < n; t++) {
+                    if (g_sched_mode == 2)
+                        for (unsigned i = n - 1; i > 0; i--) std::swap(order[i], order[rng() % (i + 1)]);
+                    for (unsigned k = 0; k < n; k++) {
+                        const unsigned t = order[k];
                         Fiber& f = blk.fibers[t];
                         if (f.done) continue;
                         blk.cur = t;
