@@ -21,7 +21,20 @@ while time.time() - t0 < float(sys.argv[2]) if len(sys.argv) > 2 else 120:
     cfg = dict(P=P, W=W, H=H, deg=deg, aa=aa, split=split, sm=sm, bf=bf, seed=seed, dd_on=dd_on, yaw=yaw)
     try:
         gs, s = small_scene(P=P, W=W, H=H, seed=seed, sh_degree=deg, scale_mult=sm, antialiasing=aa, bg=bg, behind_fraction=bf, yaw_deg=yaw)
-        if rng.integers(0, 4) == 0 and deg > 0:
+        if rng.integers(0, 5) == 0:                          # precomputed colours instead of SH
+            gs = dict(gs); del gs["shs"]; split = False
+            gs["colors_precomp"] = torch.rand(P, 3, generator=torch.Generator().manual_seed(seed))
+            cfg["colors_precomp"] = True
+        if rng.integers(0, 5) == 0:                          # precomputed 3D covariance instead of scale / rotation
+            gs = dict(gs); q, sc = gs.pop("rotations"), gs.pop("scales")
+            w, x, y, z = q.unbind(1)
+            R = torch.stack((1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y),
+                             2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x),
+                             2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)), 1).reshape(-1, 3, 3)
+            Sg = R @ torch.diag_embed(sc * sc) @ R.transpose(1, 2)
+            gs["cov3D_precomp"] = torch.stack((Sg[:, 0, 0], Sg[:, 0, 1], Sg[:, 0, 2], Sg[:, 1, 1], Sg[:, 1, 2], Sg[:, 2, 2]), 1).contiguous()
+            cfg["cov3D_precomp"] = True
+        if "shs" in gs and rng.integers(0, 4) == 0 and deg > 0:
             s["sh_degree"] = int(rng.integers(0, deg))       # active degree below the stored one
             cfg["active"] = s["sh_degree"]
         T.check_against_oracle(lib, cpu_ref, gs, s, dd_on=dd_on, split_sh=split, state=True)
