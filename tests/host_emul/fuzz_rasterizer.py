@@ -2,7 +2,8 @@
 emulation (tests/test_kernels_emul_cpu.py) against the C oracle — forward state bit-exact, images 1e-5, gradients 1e-3.
     python tests/host_emul/fuzz_rasterizer.py <seed> <seconds>
 Round-1 run: 1162 configurations (P 1..400, images 1..80 x 1..70, SH degree 0-3 incl. active < stored, split SH,
-antialiasing, backgrounds, scale multipliers 0.5..20, 0-50 % culled, three camera yaws, with / without depth gradient): 0 mismatches."""
+antialiasing, backgrounds, scale multipliers 0.5..20, 0-50 % culled, three camera yaws, with / without depth gradient): 0 mismatches;
+with precomputed colours / covariances added and GSR_EMUL_SCHED=random:77: 4670 configurations, 0 mismatches."""
 import sys, time; sys.path.insert(0, "/root/repo")
 import numpy as np, torch
 import tests.test_kernels_emul_cpu as T
