@@ -379,3 +379,11 @@ def test_debug_mode_and_error_reporting(klib):
     small = EmulRasterizer(klib, gs, s)
     small.b.geom_bytes = 64
     assert klib.gsr_forward_stage1(C.byref(small.p), C.byref(small.b), C.byref(small.o), None) == _lib.GSR_ERR_CAPACITY
+
+
+def test_more_than_65536_tiles_three_pass_tile_sort(klib, oracle):
+    """257 x 257 tiles: tile ids need 17 bits, so the tile sort takes three 8-bit passes (binning.cu) — the path the GPU
+    suite covers with test_three_pass_tile_sort.  Small Gaussians keep the emulation at about a minute."""
+    gs, s = small_scene(P=300, W=4112, H=4112, seed=5, scale_mult=0.1, antialiasing=True)
+    er = check_against_oracle(klib, oracle, gs, s)
+    assert ((er.W + 15) // 16) * ((er.H + 15) // 16) > 65536 and er.R > 10000
