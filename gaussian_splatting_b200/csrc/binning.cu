@@ -154,7 +154,10 @@ constexpr int OS_ITEMS = 8;
 constexpr int OS_TILE = OS_THREADS * OS_ITEMS;          // 4096 == SORT_CHUNK
 static_assert(OS_TILE == SORT_CHUNK, "scratch sizing assumes 4096-item tiles");
 constexpr uint32_t OS_FLAG_AGG = 1u << 30, OS_FLAG_PREFIX = 1u << 31, OS_COUNT_MASK = (1u << 30) - 1u;
-constexpr uint32_t OS_MAX_N = 1u << 30;                 // counts must fit in 30 bits
+#ifndef GSR_OS_MAX_N
+#define GSR_OS_MAX_N (1u << 30)                          // look-back counts must fit in 30 bits
+#endif
+constexpr uint32_t OS_MAX_N = GSR_OS_MAX_N;             // (tests lower it to reach the 3-kernel pass at small sizes)
 
 // Histograms of `passes` consecutive 8-bit digits starting at bit `shift`, one read of the input.
 template <int PASSES>

@@ -27,18 +27,19 @@ UNITS = ("api", "preprocess", "binning", "render_fwd", "render_bwd", "preprocess
 VP = C.c_void_p
 
 
-def load_full_emul():
-    out = os.path.join(HERE, "host_emul", "libgsrast_full_emul.so")
+def load_full_emul(defines=(), tag="full"):
+    """defines / tag: a variant of the emulated library (e.g. a lowered threshold) next to the default one."""
+    out = os.path.join(HERE, "host_emul", f"libgsrast_{tag}_emul.so")
     deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(EMU, f) for f in ("cuda_runtime.h", "emul.cpp")]
     deps.append(os.path.join(HERE, "..", "include", "gsrast.h"))
     if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(d) for d in deps):
         objs = []
         procs = []
         for u in UNITS:
-            o = os.path.join(HERE, "host_emul", f"_emul_{u}.o")
+            o = os.path.join(HERE, "host_emul", f"_emul_{tag}_{u}.o")
             objs.append(o)
             procs.append(subprocess.Popen(["g++", "-std=c++17", "-O1", "-fPIC", "-ffp-contract=off", "-U_FORTIFY_SOURCE", "-D_FORTIFY_SOURCE=0", "-DGSR_HOST_EMUL",
-                                           "-I" + EMU, "-c", "-x", "c++", os.path.join(CSRC, u + ".cu"), "-o", o]))
+                                           *[f"-D{d}" for d in defines], "-I" + EMU, "-c", "-x", "c++", os.path.join(CSRC, u + ".cu"), "-o", o]))
         assert all(p.wait() == 0 for p in procs)
         subprocess.check_call(["g++", "-std=c++17", "-O1", "-shared", "-fPIC", "-U_FORTIFY_SOURCE", "-D_FORTIFY_SOURCE=0", "-I" + EMU,
                                os.path.join(EMU, "emul.cpp")]
@@ -387,3 +388,13 @@ def test_more_than_65536_tiles_three_pass_tile_sort(klib, oracle):
     gs, s = small_scene(P=300, W=4112, H=4112, seed=5, scale_mult=0.1, antialiasing=True)
     er = check_against_oracle(klib, oracle, gs, s)
     assert ((er.W + 15) // 16) * ((er.H + 15) // 16) > 65536 and er.R > 10000
+
+
+def test_radix_fallback_pass_for_counts_beyond_30_bits(oracle):
+    """Above 2^30 items the onesweep look-back counters (30 bits) do not suffice and binning.cu falls back to a
+    histogram / row-scan / scatter pass per digit with full 32-bit counters — unreachable at test sizes, so this variant
+    of the emulated library lowers the threshold (-DGSR_OS_MAX_N=64) and both sorts take the fallback."""
+    lib = load_full_emul(defines=("GSR_OS_MAX_N=64",), tag="fallback")
+    gs, s = small_scene(P=700, W=80, H=48, seed=13, scale_mult=4.0, antialiasing=True)
+    er = check_against_oracle(lib, oracle, gs, s)
+    assert er.P > 64 and er.R > 64
