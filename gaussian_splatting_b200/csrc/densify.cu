@@ -14,6 +14,9 @@
 
 namespace gsr {
 
+#ifndef GSR_INDEX32_LIMIT
+#define GSR_INDEX32_LIMIT (1LL << 32)     // element counts below this use 32-bit index math (tests lower it)
+#endif
 constexpr int DP_THREADS = 256;
 constexpr int DP_ITEMS = 4;
 constexpr int DP_CHUNK = DP_THREADS * DP_ITEMS;    // Gaussians per block of the plan kernels
@@ -260,7 +263,7 @@ extern "C" int gsr_densify_apply(const GsrDensifyApplyArgs* a, const uint32_t* p
     const uint32_t* dstC = plan + 2 * (size_t)P;
     const long long widest = (long long)P * max_width;
     const unsigned gx = (unsigned)std::min<long long>((widest + 255) / 256, 148LL * 8);
-    if (widest + 256LL * gx < (1LL << 32))      // element index + one grid stride fits in 32 bits
+    if (widest + 256LL * gx < GSR_INDEX32_LIMIT)  // element index + one grid stride fits in 32 bits
         GSR_LAUNCH(densify_move_kernel<uint32_t>, dim3(gx, (unsigned)a->n_tensors), 256, 0, st, *a, dstA, dstB, dstC);
     else
         GSR_LAUNCH(densify_move_kernel<long long>, dim3(gx, (unsigned)a->n_tensors), 256, 0, st, *a, dstA, dstB, dstC);
@@ -307,7 +310,7 @@ static int ply_rows(bool pack, int32_t P, int32_t K, float* xyz, float* f_dc, fl
     const unsigned gx = (unsigned)std::min<long long>((total + 255) / 256, 148LL * 16);
 #define PLY_LAUNCH(PACK, T) GSR_LAUNCH((ply_rows_kernel<PACK, T>), gx, 256, 0, st, (T)total, (int)K, xyz, f_dc, f_rest, \
                                        opacity, scaling, rotation, rows)
-    const bool small = total + 256LL * gx < (1LL << 32);
+    const bool small = total + 256LL * gx < GSR_INDEX32_LIMIT;
     if (pack) { if (small) PLY_LAUNCH(true, uint32_t); else PLY_LAUNCH(true, long long); }
     else      { if (small) PLY_LAUNCH(false, uint32_t); else PLY_LAUNCH(false, long long); }
 #undef PLY_LAUNCH

@@ -47,17 +47,18 @@ def load_emul():
     return lib
 
 
-def load_kernel_emul():
-    """Builds (if stale) tests/host_emul/libgsrast_emul.so: the product's .cu sources compiled as C++ (-DGSR_HOST_EMUL)
+def load_kernel_emul(defines=(), tag=""):
+    """Builds (if stale) tests/host_emul/libgsrast_emul.so (or a variant with extra defines): the product's .cu sources compiled as C++ (-DGSR_HOST_EMUL)
     against the CUDA stand-in of tests/host_emul/cuda_emul; exports the same C-ABI as libgsrast.so for those files."""
     emu_dir = os.path.join(HERE, "host_emul", "cuda_emul")
     csrc = os.path.join(HERE, "..", "gaussian_splatting_b200", "csrc")
-    out = os.path.join(HERE, "host_emul", "libgsrast_emul.so")
+    out = os.path.join(HERE, "host_emul", f"libgsrast{tag}_emul.so")
     units = [os.path.join(csrc, "densify.cu")]
     deps = units + [os.path.join(emu_dir, f) for f in os.listdir(emu_dir)] + \
         [os.path.join(csrc, f) for f in ("common.cuh", "block_scan.cuh", "densify_core.cuh")]
     if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(d) for d in deps):
         cmd = ["g++", "-std=c++17", "-O1", "-shared", "-fPIC", "-ffp-contract=off", "-U_FORTIFY_SOURCE", "-D_FORTIFY_SOURCE=0", "-DGSR_HOST_EMUL", "-I" + emu_dir]
+        cmd += [f"-D{d}" for d in defines]
         for u in units:
             cmd += ["-x", "c++", u]
         cmd += ["-x", "c++", os.path.join(emu_dir, "emul.cpp"), os.path.join(emu_dir, "api_stub.cpp"), "-o", out]
@@ -110,9 +111,15 @@ class FakeLib:
         return b"emulation"
 
 
-@pytest.fixture(params=("per-element", "kernels"))
-def on_cpu(request, emul, kernel_emul, monkeypatch):
-    fake = FakeLib(emul) if request.param == "per-element" else kernel_emul
+@pytest.fixture(scope="module")
+def kernel_emul_wide():
+    # the 64-bit index instantiations of the move / PLY kernels (taken above 2^32 elements) forced at test sizes
+    return load_kernel_emul(defines=("GSR_INDEX32_LIMIT=0",), tag="_wide")
+
+
+@pytest.fixture(params=("per-element", "kernels", "kernels-64bit-index"))
+def on_cpu(request, emul, kernel_emul, kernel_emul_wide, monkeypatch):
+    fake = {"per-element": FakeLib(emul), "kernels": kernel_emul, "kernels-64bit-index": kernel_emul_wide}[request.param]
     monkeypatch.setattr(_lib, "load", lambda: fake)
     for mod in (densify,):
         monkeypatch.setattr(mod, "_require_cuda", lambda t, what: None)

@@ -398,3 +398,58 @@ def test_radix_fallback_pass_for_counts_beyond_30_bits(oracle):
     gs, s = small_scene(P=700, W=80, H=48, seed=13, scale_mult=4.0, antialiasing=True)
     er = check_against_oracle(lib, oracle, gs, s)
     assert er.P > 64 and er.R > 64
+
+
+def test_adam_scalar_path_and_unmasked(klib):
+    # element count not a multiple of 4 -> the scalar kernel instead of the 16-byte one; visible == NULL -> everywhere
+    g = torch.Generator().manual_seed(1)
+    N, M = 7, 3
+    p = torch.randn(N, M, generator=g)
+    grad = torch.randn(N, M, generator=g)
+    ref = torch.nn.Parameter(p.clone())
+    opt = torch.optim.Adam([ref], lr=3e-3, eps=1e-15)
+    pa, ga, ma, va = f32(p.numpy()), f32(grad.numpy()), np.zeros((N, M), np.float32), np.zeros((N, M), np.float32)
+    for step in (1, 2):
+        ref.grad = grad.clone()
+        opt.step()
+        ok(klib, klib.gsr_adam_update(pa.ctypes.data, ga.ctypes.data, ma.ctypes.data, va.ctypes.data, None, 3e-3, 0.9, 0.999,
+                                      1e-15, 1 - 0.9 ** step, (1 - 0.999 ** step) ** 0.5, N, M, None))
+    assert rel_err(pa, ref.detach().numpy()) < 1e-6
+    assert rel_err(ma, opt.state[ref]["exp_avg"].numpy()) < 1e-6
+
+
+@pytest.mark.parametrize("shape", ((2, 1, 23, 40), (1, 3, 12, 11)))
+def test_ssim_valid_crop_and_map_gradient(klib, shape):
+    """padding="valid" (crop = 5) through the fused-mean path, and the FusedSSIMMap path (map gradient in)."""
+    from oracle import ssim_ref
+    rng = np.random.default_rng(2)
+    B, CH, H, W = shape
+    a, b = rng.random(shape, dtype=np.float32), rng.random(shape, dtype=np.float32)
+    sp = _lib.GsrSsimParams(a.ctypes.data, b.ctypes.data, B, CH, H, W, 0.01 ** 2, 0.03 ** 2, 5)
+    maps = [np.zeros_like(a) for _ in range(4)]
+    mean = np.zeros(1, np.float32)
+    partials = np.zeros(int(klib.gsr_ssim_partials(B, CH, H, W)), np.float32)
+    ok(klib, klib.gsr_ssim_forward(C.byref(sp), *[m.ctypes.data for m in maps], mean.ctypes.data, partials.ctypes.data, None))
+    v_ref, g_ref = ssim_ref.fused_ssim(a, b, "valid", dtype=np.float64)
+    assert abs(float(mean[0]) - v_ref) < 2e-6
+    dmean = np.ones(1, np.float32)
+    dimg = np.full_like(a, np.nan)
+    ok(klib, klib.gsr_ssim_backward(C.byref(sp), None, dmean.ctypes.data, maps[1].ctypes.data, maps[2].ctypes.data,
+                                    maps[3].ctypes.data, dimg.ctypes.data, None))
+    assert rel_err(dimg, g_ref) < 1e-4
+    # map gradient in (crop 0): a random dL_dmap must give sum(dL_dmap * dmap/dimg1), linear in dL_dmap
+    sp0 = _lib.GsrSsimParams(a.ctypes.data, b.ctypes.data, B, CH, H, W, 0.01 ** 2, 0.03 ** 2, 0)
+    ok(klib, klib.gsr_ssim_forward(C.byref(sp0), *[m.ctypes.data for m in maps], None, None, None))
+    dmap = rng.random(shape, dtype=np.float32)
+    d1, d2 = np.zeros_like(a), np.zeros_like(a)
+    ok(klib, klib.gsr_ssim_backward(C.byref(sp0), dmap.ctypes.data, None, maps[1].ctypes.data, maps[2].ctypes.data,
+                                    maps[3].ctypes.data, d1.ctypes.data, None))
+    dmap2 = f32(2 * dmap)
+    ok(klib, klib.gsr_ssim_backward(C.byref(sp0), dmap2.ctypes.data, None, maps[1].ctypes.data, maps[2].ctypes.data,
+                                    maps[3].ctypes.data, d2.ctypes.data, None))
+    assert rel_err(d2, 2 * d1) < 1e-6
+    ones = np.full(shape, 1.0 / a.size, np.float32)
+    ok(klib, klib.gsr_ssim_backward(C.byref(sp0), ones.ctypes.data, None, maps[1].ctypes.data, maps[2].ctypes.data,
+                                    maps[3].ctypes.data, d1.ctypes.data, None))
+    _, g_same = ssim_ref.fused_ssim(a, b, "same", dtype=np.float64)
+    assert rel_err(d1, g_same) < 1e-4

@@ -12,12 +12,12 @@ from torch import nn
 
 from gaussian_splatting_b200 import _lib, plyio
 from oracle import ply_ref
-from tests.test_densify_emul_cpu import FakeLib, emul, kernel_emul  # noqa: F401  (fixtures)
+from tests.test_densify_emul_cpu import FakeLib, emul, kernel_emul, kernel_emul_wide  # noqa: F401  (fixtures)
 
 
-@pytest.fixture(params=("per-element", "kernels"))
-def on_cpu(request, emul, kernel_emul, monkeypatch):  # noqa: F811
-    fake = FakeLib(emul) if request.param == "per-element" else kernel_emul
+@pytest.fixture(params=("per-element", "kernels", "kernels-64bit-index"))
+def on_cpu(request, emul, kernel_emul, kernel_emul_wide, monkeypatch):  # noqa: F811
+    fake = {"per-element": FakeLib(emul), "kernels": kernel_emul, "kernels-64bit-index": kernel_emul_wide}[request.param]
     monkeypatch.setattr(_lib, "load", lambda: fake)
     monkeypatch.setattr(plyio, "_require_cuda", lambda t, what: None)
     monkeypatch.setattr(plyio, "_device_ctx", lambda d: contextlib.nullcontext())
