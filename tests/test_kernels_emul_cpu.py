@@ -453,3 +453,36 @@ def test_ssim_valid_crop_and_map_gradient(klib, shape):
                                     maps[3].ctypes.data, d1.ctypes.data, None))
     _, g_same = ssim_ref.fused_ssim(a, b, "same", dtype=np.float64)
     assert rel_err(d1, g_same) < 1e-4
+
+
+def test_one_call_forward_capacity_protocol_and_work_counters(klib, oracle):
+    """gsr_forward (stage 1, wait, stage 2 in one call): with a bin buffer that is too small it reports
+    GSR_ERR_CAPACITY and still returns num_rendered, the caller regrows and finishes with gsr_forward_stage2;
+    gsr_debug_count_work (the bench's work descriptors Wf / Bp / Wb) against the oracle's own counters."""
+    klib.gsr_forward.argtypes = [C.POINTER(GsrParams), C.POINTER(GsrBuffers), C.POINTER(GsrForwardOut),
+                                 C.POINTER(C.c_int64), VP]
+    klib.gsr_debug_count_work.argtypes = [C.POINTER(GsrParams), C.POINTER(GsrBuffers), C.c_int64, VP, VP]
+    gs, s = small_scene(P=400, W=48, H=48, seed=14, antialiasing=True)
+    want = run_oracle(oracle, gs, s)
+    er = EmulRasterizer(klib, gs, s)
+    er.scratch = aligned(klib.gsr_scratch_bytes(er.P, er.W, er.H, 1 << 16))       # generous: only bin is short
+    er.b.scratch, er.b.scratch_bytes = er.scratch.ctypes.data, er.scratch.nbytes
+    tiny = aligned(256)
+    er.b.bin, er.b.bin_bytes = tiny.ctypes.data, tiny.nbytes
+    R = C.c_int64(-1)
+    rc = klib.gsr_forward(C.byref(er.p), C.byref(er.b), C.byref(er.o), C.byref(R), None)
+    assert rc == _lib.GSR_ERR_CAPACITY and R.value == int(want["fw"]["R"]) > 64
+    er.R = R.value
+    er.bin = aligned(klib.gsr_bin_bytes(er.R))
+    er.b.bin, er.b.bin_bytes = er.bin.ctypes.data, er.bin.nbytes
+    ok(klib, klib.gsr_forward_stage2(C.byref(er.p), C.byref(er.b), C.byref(er.o), er.R, None))
+    assert np.abs(er.color - want["color"]).max() <= 1e-5
+    # the same call with enough room succeeds in one go
+    R2 = C.c_int64(-1)
+    ok(klib, klib.gsr_forward(C.byref(er.p), C.byref(er.b), C.byref(er.o), C.byref(R2), None))
+    assert R2.value == er.R and np.abs(er.color - want["color"]).max() <= 1e-5
+    counts = np.zeros(3, np.uint64)
+    ok(klib, klib.gsr_debug_count_work(C.byref(er.p), C.byref(er.b), er.R, counts.ctypes.data, None))
+    stats = want["fw"]["stats"]
+    assert int(counts[0]) == int(stats[0]) and int(counts[1]) == int(stats[1])
+    assert int(counts[2]) == int(np.asarray(want["fw"]["n_contrib"], np.int64).sum())
