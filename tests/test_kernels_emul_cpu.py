@@ -300,7 +300,8 @@ def test_ssim_kernels_match_the_oracle(klib):
     assert rel_err(dimg, g_ref) < 1e-4
 
 
-def test_factored_exchange_two_ranks(klib, oracle):
+@pytest.mark.parametrize("split", (False, True))
+def test_factored_exchange_two_ranks(klib, oracle, split):
     """View-parallel exchange with world = 2 on the CPU: two cameras of the same Gaussians run the sender
     branch of preprocess_bwd.cu with multimem_reduce = 1 — under the emulation a multimem.red is an add into the one
     local buffer, i.e. exactly the sum the NVSwitch forms in every replica — then gsr_exchange_expand rebuilds the dense
@@ -317,7 +318,7 @@ def test_factored_exchange_two_ranks(klib, oracle):
         gs, s = small_scene(P=P, W=W, H=H, seed=6, yaw_deg=yaw, antialiasing=True, behind_fraction=0.0)   # replicated Gaussians
         o = run_oracle(oracle, gs, s, dc, dd)
         want = o["grads"] if want is None else {k: want[k] + o["grads"][k] for k in want if k != "means2D"}
-        er = EmulRasterizer(klib, gs, s).forward()
+        er = EmulRasterizer(klib, gs, s, split_sh=split).forward()
         io = GsrBackwardIO()
         dcn, ddn = f32(dc.numpy()), f32(dd.numpy())
         m2 = np.full((P, 3), np.nan, np.float32)
@@ -330,9 +331,15 @@ def test_factored_exchange_two_ranks(klib, oracle):
     out = {"means3D": np.full((P, 3), np.nan, np.float32), "opacities": np.full((P, 1), np.nan, np.float32),
            "shs": np.full((P, 16, 3), np.nan, np.float32), "scales": np.full((P, 3), np.nan, np.float32),
            "rotations": np.full((P, 4), np.nan, np.float32)}
+    sh_dc = np.full((P, 1, 3), np.nan, np.float32)
+    sh_rest = np.full((P, 15, 3), np.nan, np.float32)
     ok(klib, klib.gsr_exchange_expand(C.byref(er.p), world, records.ctypes.data, rgb.ctypes.data, campos.ctypes.data,
-                                      out["means3D"].ctypes.data, out["opacities"].ctypes.data, out["shs"].ctypes.data,
-                                      out["scales"].ctypes.data, out["rotations"].ctypes.data, None, None))
+                                      out["means3D"].ctypes.data, out["opacities"].ctypes.data,
+                                      sh_rest.ctypes.data if split else out["shs"].ctypes.data,
+                                      out["scales"].ctypes.data, out["rotations"].ctypes.data,
+                                      sh_dc.ctypes.data if split else None, None))
+    if split:                                    # split SH storage: coefficient 0 and the rest leave separately
+        out["shs"] = np.concatenate((sh_dc, sh_rest), 1)
     for k, g in out.items():
         assert rel_err(g, np.asarray(want[k]).reshape(g.shape)) < 1e-3, k
     # self-cleaning buffers: the rows expand consumed are zero again for the next step
