@@ -493,3 +493,85 @@ def test_one_call_forward_capacity_protocol_and_work_counters(klib, oracle):
     stats = want["fw"]["stats"]
     assert int(counts[0]) == int(stats[0]) and int(counts[1]) == int(stats[1])
     assert int(counts[2]) == int(np.asarray(want["fw"]["n_contrib"], np.int64).sum())
+
+
+@pytest.mark.parametrize("deg,P,split", ((0, 97, False), (1, 64, False), (2, 130, False), (3, 301, True), (1, 35, True)))
+def test_sh_layouts_of_the_per_gaussian_backward(klib, oracle, deg, P, split):
+    """M = 1, 4, 9, 16 coefficients: rows that are / are not whole float4s take the vector / scalar staging of
+    preprocess_bwd.cu; ragged last warps of the split layout are copied by the lanes instead of bulk copies."""
+    gs, s = small_scene(P=P, W=40, H=24, seed=20 + deg, sh_degree=deg, antialiasing=bool(deg & 1))
+    check_against_oracle(klib, oracle, gs, s, split_sh=split, state=False)
+
+
+@pytest.mark.parametrize("masked", (True, False))
+def test_adam_vector_kernel(klib, masked):
+    # element count a multiple of 4 and 16-byte aligned tensors: the float4 kernel every real model tensor takes
+    g = torch.Generator().manual_seed(5)
+    N, M = 256, 45
+    p, grad = torch.randn(N, M, generator=g), torch.randn(N, M, generator=g)
+    vis = (torch.rand(N, generator=g) < 0.5).to(torch.uint8) if masked else torch.ones(N, dtype=torch.uint8)
+    ref = torch.nn.Parameter(p.clone())
+    opt = torch.optim.Adam([ref], lr=1e-2, eps=1e-15)
+    bufs = [aligned(N * M * 4, 16).view(np.float32).reshape(N, M) for _ in range(4)]
+    pa, ga, ma, va = bufs
+    pa[:], ga[:], ma[:], va[:] = p.numpy(), grad.numpy(), 0, 0
+    for step in (1, 2, 3):
+        ref.grad = grad * vis[:, None]
+        opt.step()
+        ok(klib, klib.gsr_adam_update(pa.ctypes.data, ga.ctypes.data, ma.ctypes.data, va.ctypes.data,
+                                      vis.numpy().ctypes.data if masked else None, 1e-2, 0.9, 0.999, 1e-15,
+                                      1 - 0.9 ** step, (1 - 0.999 ** step) ** 0.5, N, M, None))
+    v = vis.bool().numpy()
+    assert rel_err(pa[v], ref.detach().numpy()[v]) < 1e-6
+    assert np.array_equal(pa[~v], p.numpy()[~v]) and not ma[~v].any() and not va[~v].any()
+    assert klib.gsr_adam_update(None, None, None, None, None, 1e-2, 0.9, 0.999, 1e-15, 0.1, 0.1, 4, 3, None) == _lib.GSR_ERR_INVALID_ARG
+
+
+def test_profiling_hooks_and_argument_errors(klib):
+    klib.gsr_profile_collect.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_int64)]
+    klib.gsr_stage_name.restype = C.c_char_p
+    klib.gsr_launch_count.restype = C.c_uint64
+    gs, s = small_scene(P=120, W=32, H=32, seed=15)
+    klib.gsr_profile_enable(1)
+    l0 = klib.gsr_launch_count()
+    er = EmulRasterizer(klib, gs, s).forward()
+    er.backward(np.ones((3, 32, 32), np.float32), None)
+    ms, n = (C.c_double * _lib.STAGE_COUNT)(), (C.c_int64 * _lib.STAGE_COUNT)()
+    ok(klib, klib.gsr_profile_collect(ms, n))
+    klib.gsr_profile_enable(0)
+    names = [klib.gsr_stage_name(i).decode() for i in range(_lib.STAGE_COUNT)]
+    assert all(c == 1 for c in n) and "render_bwd" in names and klib.gsr_stage_name(99) == b"?"
+    assert klib.gsr_launch_count() - l0 >= 15
+    # argument errors come back as codes with the reference's messages, never as aborts
+    e = EmulRasterizer(klib, gs, s)
+    e.p.scales = None
+    assert klib.gsr_forward_stage1(C.byref(e.p), C.byref(e.b), C.byref(e.o), None) == _lib.GSR_ERR_INVALID_ARG
+    assert b"scale/rotation pair or precomputed 3D covariance" in klib.gsr_last_error()
+    e = EmulRasterizer(klib, gs, s)
+    e.p.M = 3                                            # fewer coefficients than the active degree needs
+    assert klib.gsr_forward_stage1(C.byref(e.p), C.byref(e.b), C.byref(e.o), None) == _lib.GSR_ERR_INVALID_ARG
+    e = EmulRasterizer(klib, gs, s)
+    e.b.img_bytes = 16
+    assert klib.gsr_forward_stage1(C.byref(e.p), C.byref(e.b), C.byref(e.o), None) == _lib.GSR_ERR_CAPACITY
+    e = EmulRasterizer(klib, gs, s)
+    e.o.out_color = None
+    rc1 = klib.gsr_forward_stage1(C.byref(e.p), C.byref(e.b), C.byref(e.o), None)
+    assert rc1 == _lib.GSR_ERR_INVALID_ARG or klib.gsr_forward_stage2(C.byref(e.p), C.byref(e.b), C.byref(e.o), 0, None) != 0
+
+
+def test_ssim_inference_mode_and_argument_errors(klib):
+    from oracle import ssim_ref
+    rng = np.random.default_rng(4)
+    a, b = rng.random((1, 1, 20, 33), dtype=np.float32), rng.random((1, 1, 20, 33), dtype=np.float32)
+    sp = _lib.GsrSsimParams(a.ctypes.data, b.ctypes.data, 1, 1, 20, 33, 0.01 ** 2, 0.03 ** 2, 0)
+    smap = np.zeros_like(a)
+    ok(klib, klib.gsr_ssim_forward(C.byref(sp), smap.ctypes.data, None, None, None, None, None, None))   # train=False
+    m_ref, *_ = ssim_ref.ssim_forward(a, b, dtype=np.float64)
+    assert np.abs(smap - m_ref).max() < 1e-5
+    one = np.zeros_like(a)
+    assert klib.gsr_ssim_forward(C.byref(sp), smap.ctypes.data, one.ctypes.data, None, None, None, None, None) == _lib.GSR_ERR_INVALID_ARG
+    mean = np.zeros(1, np.float32)
+    assert klib.gsr_ssim_forward(C.byref(sp), None, None, None, None, mean.ctypes.data, None, None) == _lib.GSR_ERR_INVALID_ARG
+    assert klib.gsr_ssim_backward(C.byref(sp), smap.ctypes.data, None, None, None, None, one.ctypes.data, None) == _lib.GSR_ERR_INVALID_ARG
+    bad = _lib.GsrSsimParams(None, b.ctypes.data, 1, 1, 20, 33, 1e-4, 9e-4, 0)
+    assert klib.gsr_ssim_forward(C.byref(bad), smap.ctypes.data, None, None, None, None, None, None) == _lib.GSR_ERR_INVALID_ARG
