@@ -300,8 +300,8 @@ def test_ssim_kernels_match_the_oracle(klib):
     assert rel_err(dimg, g_ref) < 1e-4
 
 
-@pytest.mark.parametrize("split", (False, True))
-def test_factored_exchange_two_ranks(klib, oracle, split):
+@pytest.mark.parametrize("deg,split", ((3, False), (3, True), (2, False), (1, True), (0, False)))
+def test_factored_exchange_two_ranks(klib, oracle, deg, split):
     """View-parallel exchange with world = 2 on the CPU: two cameras of the same Gaussians run the sender
     branch of preprocess_bwd.cu with multimem_reduce = 1 — under the emulation a multimem.red is an add into the one
     local buffer, i.e. exactly the sum the NVSwitch forms in every replica — then gsr_exchange_expand rebuilds the dense
@@ -315,7 +315,7 @@ def test_factored_exchange_two_ranks(klib, oracle, split):
     want = None
     dc, dd = upstream(W, H, seed=3)
     for r, yaw in enumerate((0.0, 25.0)):
-        gs, s = small_scene(P=P, W=W, H=H, seed=6, yaw_deg=yaw, antialiasing=True, behind_fraction=0.0)   # replicated Gaussians
+        gs, s = small_scene(P=P, W=W, H=H, seed=6, yaw_deg=yaw, antialiasing=True, behind_fraction=0.0, sh_degree=deg)   # replicated Gaussians
         o = run_oracle(oracle, gs, s, dc, dd)
         want = o["grads"] if want is None else {k: want[k] + o["grads"][k] for k in want if k != "means2D"}
         er = EmulRasterizer(klib, gs, s, split_sh=split).forward()
@@ -329,10 +329,10 @@ def test_factored_exchange_two_ranks(klib, oracle, split):
         assert rel_err(m2, o["grads"]["means2D"]) < 1e-3       # per-view statistic, never reduced
         assert np.allclose(campos[r], np.append(f32(s["campos"]), 1.0))
     out = {"means3D": np.full((P, 3), np.nan, np.float32), "opacities": np.full((P, 1), np.nan, np.float32),
-           "shs": np.full((P, 16, 3), np.nan, np.float32), "scales": np.full((P, 3), np.nan, np.float32),
+           "shs": np.full((P, (deg + 1) ** 2, 3), np.nan, np.float32), "scales": np.full((P, 3), np.nan, np.float32),
            "rotations": np.full((P, 4), np.nan, np.float32)}
     sh_dc = np.full((P, 1, 3), np.nan, np.float32)
-    sh_rest = np.full((P, 15, 3), np.nan, np.float32)
+    sh_rest = np.full((P, (deg + 1) ** 2 - 1, 3), np.nan, np.float32)
     ok(klib, klib.gsr_exchange_expand(C.byref(er.p), world, records.ctypes.data, rgb.ctypes.data, campos.ctypes.data,
                                       out["means3D"].ctypes.data, out["opacities"].ctypes.data,
                                       sh_rest.ctypes.data if split else out["shs"].ctypes.data,
