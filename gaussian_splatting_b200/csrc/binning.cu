@@ -565,7 +565,7 @@ __global__ void rebuild_keys_kernel(const uint2* __restrict__ ranges, uint32_t T
     if (tile >= T) return;
     uint2 rg = ranges[tile];
     for (uint32_t i = rg.x + threadIdx.x; i < rg.y; i += blockDim.x)
-        keys[i] = ((uint64_t)tile << 32) | __float_as_uint(rec[point_list[i]].q2.z);
+        keys[i] = ((uint64_t)tile << 32) | __float_as_uint(rec[point_list[i]].q3.z);
 }
 
 // ---------------------------------------------------------------- launchers

@@ -22,8 +22,9 @@ constexpr int TILE_PIX = TILE_X * TILE_Y;
 // One Gaussian after projection.  16 floats, 64 B, 64 B aligned.
 //   q0 = {x, y, conic.x, conic.y}            pixel centre + conic a,b
 //   q1 = {conic.z, opacity*aa, r, g}
-//   q2 = {b, 1/depth, depth, radius(int bits)}
-//   q3 = {clamped bits (int), tiles_touched (int), unused, unused}
+//   q2 = {b, 1/depth, cull half-extent x, cull half-extent y}     (render_common.cuh: cull_extent)
+//   q3 = {clamped bits (int), tiles_touched (int), depth, radius (int bits)}
+// The first 48 B are what the blend kernels stage per tile entry.
 struct __align__(16) GsRecord {
     float4 q0, q1, q2, q3;
 };
@@ -31,7 +32,9 @@ static_assert(sizeof(GsRecord) == GSR_RECORD_FLOATS * 4, "record size");
 
 // Gradient accumulator per Gaussian written by render backward (atomics) and
 // consumed by preprocess backward.  12 floats, 48 B:
-//   {dcolor r,g,b, dinvdepth | dmean2D x,y, dconic a,b | dconic c, dopacity, pad, pad}
+//   {dcolor r,g,b, dinvdepth | S h, S h dx, S h dy, S h dx^2 | S h dx dy, S h dy^2, pad, pad}
+// h = G * dL_dalpha, d = centre - pixel, sums over the blended pixels; preprocess_bwd turns the six moments into
+// dL_dopacity, dL_dmean2D and dL_dconic with the Gaussian's own conic / opacity.
 constexpr int ACC_FLOATS = 12;
 
 __host__ __device__ inline uint32_t div_up(uint32_t a, uint32_t b) { return (a + b - 1) / b; }

@@ -7,6 +7,7 @@
 // padded shared-memory transpose; only visible Gaussians' rows are fetched.
 #include "common.cuh"
 #include "gs_math.cuh"
+#include "render_common.cuh"
 
 namespace gsr {
 
@@ -214,8 +215,9 @@ preprocess_fwd_kernel(GsrParams p, float focal_x, float focal_y, int gx, int gy,
         GsRecord r;
         r.q0 = make_float4(pix.x, pix.y, conic.x, conic.y);
         r.q1 = make_float4(conic.z, opacity_aa, rgb[0], rgb[1]);
-        r.q2 = make_float4(rgb[2], 1.f / depth, depth, __int_as_float((int)my_radius));
-        r.q3 = make_float4(__int_as_float(clamped_bits), __int_as_float(tiles), 0.f, 0.f);
+        const float2 ext = cull_extent(conic.x, conic.y, conic.z, opacity_aa);     // render_common.cuh
+        r.q2 = make_float4(rgb[2], 1.f / depth, ext.x, ext.y);
+        r.q3 = make_float4(__int_as_float(clamped_bits), __int_as_float(tiles), depth, __int_as_float((int)my_radius));
         rec[idx] = r;
     }
 }

@@ -2,7 +2,8 @@
 //
 // One kernel replaces computeCov2DCUDA + preprocessCUDA backward + the ten torch::zeros
 // fills (DGR/cuda_rasterizer/backward.cu:153-290, 296-365, 372-429; rasterize_points.cu:
-// 186-204): it consumes the 12-float accumulator written by render_bwd.cu and writes every
+// 186-204): it consumes the 12-float accumulator written by render_bwd.cu (colour / inverse-depth
+// gradients and six moments, converted here to dL_dmean2D, dL_dconic, dL_dopacity) and writes every
 // output gradient exactly once (zeros for culled Gaussians), so no zero-init pass is needed.
 //
 // The tail of computeCov2DCUDA that this fork elided (backward.cu:285-290: dL_dcov3D and the
@@ -343,9 +344,9 @@ preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord*
         const float4 a0 = a4[0], a1 = a4[1], a2 = a4[2];
         dL_dcolor[0] = a0.x; dL_dcolor[1] = a0.y; dL_dcolor[2] = a0.z;
         const float dL_dinvdepth = a0.w;
-        dL_dmean2D = make_float2(a1.x, a1.y);
-        const float3 dL_dconic = {a1.z, a1.w, a2.x};
-        const float dL_dopacity_v = a2.y;
+        // moments of h = G * dL_dalpha about the centre (render_bwd.cu): S h, S h dx, S h dy, S h dx^2, S h dx dy, S h dy^2
+        const float m0 = a1.x, mx = a1.y, my = a1.z, mxx = a1.w, mxy = a2.x, myy = a2.y;
+        const float dL_dopacity_v = m0;                                   // backward.cu:587-609
         clamped_bits = __float_as_int(rec[idx].q3.x);
 
         mean = make_float3(p.means3D[3 * idx], p.means3D[3 * idx + 1], p.means3D[3 * idx + 2]);
@@ -367,17 +368,21 @@ preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord*
         const float y_grad_mul = (ctx.tytz < -ctx.limy || ctx.tytz > ctx.limy) ? 0.f : 1.f;
 
         float c_xx = cov.x, c_xy = cov.y, c_yy = cov.z;
+        float3 dL_dconic;
         constexpr float h_var = 0.3f;
         float d_inside_root = 0.f;
         dL_dopacity = dL_dopacity_v;
+        const float opacity = p.opacities[idx];
+        float o_blend = opacity;                     // what the blend multiplied G with (forward.cu:344)
         if (p.antialiasing) {
             const float det_cov = c_xx * c_yy - c_xy * c_xy;
             c_xx += h_var;
             c_yy += h_var;
             const float det_cov_plus_h_cov = c_xx * c_yy - c_xy * c_xy;
             const float h_convolution_scaling = sqrtf(fmaxf(0.000025f, det_cov / det_cov_plus_h_cov));
-            const float d_h_convolution_scaling = dL_dopacity_v * p.opacities[idx];
+            const float d_h_convolution_scaling = dL_dopacity_v * opacity;
             dL_dopacity = dL_dopacity_v * h_convolution_scaling;
+            o_blend = opacity * h_convolution_scaling;
             d_inside_root = (det_cov / det_cov_plus_h_cov) <= 0.000025f
                                 ? 0.f
                                 : d_h_convolution_scaling / (2 * h_convolution_scaling);
@@ -394,6 +399,19 @@ preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord*
             dL_dc_xy = -2.f * w * z * (w + x + y) * denom_f;
         }
         const float denom = c_xx * c_yy - c_xy * c_xy;
+        // The blend's per-Gaussian constants: conic = inverse of the filtered covariance (forward.cu:291-293),
+        // blend opacity o = opacity * AA scaling, viewport scale 0.5 W / 0.5 H.  With dL_dG = o * dL_dalpha:
+        //   dL_dmean2D = -0.5 (W, H) * o * conic * (S h dx, S h dy),  dL_dconic = -0.5 o (S h dx^2, S h dx dy, S h dy^2)
+        // (backward.cu:569-586 summed over the pixels).
+        {
+            const float det_inv = 1.f / denom;
+            const float ca = c_yy * det_inv, cb = -c_xy * det_inv, cc = c_xx * det_inv;
+            const float o = o_blend;
+            const float ddelx_dx = 0.5 * p.W, ddely_dy = 0.5 * p.H;
+            dL_dmean2D.x = -ddelx_dx * o * (ca * mx + cb * my);
+            dL_dmean2D.y = -ddely_dy * o * (cc * my + cb * mx);
+            dL_dconic = make_float3(-0.5f * o * mxx, -0.5f * o * mxy, -0.5f * o * myy);
+        }
         const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
         if (denom2inv != 0) {
             dL_dc_xx += denom2inv * (-c_yy * c_yy * dL_dconic.x + 2 * c_xy * c_yy * dL_dconic.y + (denom - c_xx * c_yy) * dL_dconic.z);
@@ -593,7 +611,7 @@ struct BandLimits { int n; int hi[MAX_BANDS]; };
 
 __device__ __forceinline__ int band_of(const GsRecord* r, int gy, const BandLimits& lim) {
     const float py = r->q0.y;
-    const int rad = __float_as_int(r->q2.w);
+    const int rad = __float_as_int(r->q3.w);
     const int last_row = min(gy, max(0, (int)((py + rad + TILE_Y - 1) / TILE_Y))) - 1;   // get_rect, gs_math.cuh
     int k = 0;
     while (k < lim.n - 1 && last_row >= lim.hi[k]) k++;

@@ -31,8 +31,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   float* __restrict__ out_color, float* __restrict__ out_invdepth) {
     __shared__ __align__(128) float4 s_rec[RF_STAGES][RF_BATCH * 3];
     __shared__ __align__(8) uint64_t s_bar[RF_STAGES];
-    __shared__ uint8_t s_mask[RF_STAGES][RF_BATCH];
-    __shared__ __align__(4) uint8_t s_list[TILE_PIX / 32][RF_BATCH];
+    __shared__ __align__(16) uint32_t s_bits[RF_STAGES][CULL_WARPS][CULL_WARPS];   // [stage][source warp][target warp]
     __shared__ uint32_t s_max;
 
     const uint32_t rank = threadIdx.x;
@@ -75,6 +74,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     uint32_t last_contributor = 0;
     float C[3] = {0.f, 0.f, 0.f};
     float expected_invdepth = 0.0f;
+    bool warp_done = false;                    // all 32 pixels of this warp are saturated
 
     if (rounds > 0) issue(0);
     for (int k = 0; k < rounds; k++) {
@@ -82,55 +82,54 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         const int cnt = min(RF_BATCH, n - k * RF_BATCH);
         const float4* sr = s_rec[stage];
         mbar_wait(smem_u32(&s_bar[stage]), (uint32_t)((k >> 1) & 1));   // batch k has landed
-        if ((int)rank < cnt) s_mask[stage][rank] = (uint8_t)cull_mask(sr[rank * 3], sr[rank * 3 + 1], tx0, ty0);
+        {
+            uint32_t m = 0;
+            if ((int)rank < cnt) {
+                const float4 e0 = sr[rank * 3], e2 = sr[rank * 3 + 2];
+                m = cull_mask(e0.x, e0.y, e2.z, e2.w, tx0, ty0);
+            }
+            publish_cull_bits(reinterpret_cast<uint4*>(s_bits[stage]), m, lane, warp);
+        }
         // all threads are past batch k-1 here, so its stage may be refilled; nothing is
         // in flight when the CTA leaves through the break
         const int num_done = __syncthreads_count(done);
         if (num_done == TILE_PIX) break;
         if (k + 1 < rounds) issue(k + 1);
 
-        // this warp's entries, in list order
-        int cntw = 0;
-        for (int i = 0; i * 32 < cnt; i++) {
-            const int slot = i * 32 + (int)lane;
-            const bool hit = slot < cnt && ((s_mask[stage][slot] >> warp) & 1u);
-            const uint32_t b = __ballot_sync(0xffffffffu, hit);
-            if (hit) s_list[warp][cntw + __popc(b & ((1u << lane) - 1u))] = (uint8_t)slot;
-            cntw += __popc(b);
-        }
-        __syncwarp();
-
-        const uint8_t* sl = s_list[warp];
         const uint32_t base = (uint32_t)k * RF_BATCH;
-        // Warp-uniform loop, branch-free body: the reference's rejections (power > 0, alpha < 1/255, pixel
-        // already saturated; forward.cu:468-487) zero the blend weight instead of skipping, which leaves C, T
-        // and last_contributor bit-identical (fma(T, 0, C) == C).
-        for (int jj = 0; jj < cntw; jj++) {
-            const int j = sl[jj];
-            const float4 q0 = sr[j * 3 + 0];      // x, y, conic.x, conic.y
-            const float4 q1 = sr[j * 3 + 1];      // conic.z, opacity, r, g
-            const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
-            const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
-            const float alpha = fminf(0.99f, q1.y * expf(power));
-            bool ok = !done && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-            const float test_T = T * (1 - alpha);
-            const bool stop = ok && test_T < 0.0001f;
-            done = done || stop;
-            ok = ok && !stop;
-            if (!__any_sync(0xffffffffu, ok)) {
-                if (__all_sync(0xffffffffu, done)) break;
-                continue;
+        // Warp-uniform loop over this warp's entries (set bits, in list order), branch-free body: the reference's
+        // rejections (power > 0, alpha < 1/255, pixel already saturated; forward.cu:468-487) zero the blend weight
+        // instead of skipping, which leaves C, T and last_contributor bit-identical (fma(T, 0, C) == C).
+        for (int w8 = 0; w8 * 32 < cnt && !warp_done; w8++) {
+            // redux.sync: the word lands in a uniform register, so the bit walk below is uniform control flow
+            uint32_t bits = __reduce_or_sync(0xffffffffu, s_bits[stage][w8][warp]);
+            while (bits != 0) {
+                const int j = w8 * 32 + __ffs((int)bits) - 1;
+                bits &= bits - 1;
+                const float4 q0 = sr[j * 3 + 0];      // x, y, conic.x, conic.y
+                const float4 q1 = sr[j * 3 + 1];      // conic.z, opacity, r, g
+                const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
+                const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
+                const float alpha = fminf(0.99f, q1.y * expf(power));
+                bool ok = !done && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+                const float test_T = T * (1 - alpha);
+                const bool stop = ok && test_T < 0.0001f;
+                done = done || stop;
+                ok = ok && !stop;
+                if (!__any_sync(0xffffffffu, ok)) {
+                    if (__all_sync(0xffffffffu, done)) { warp_done = true; break; }
+                    continue;
+                }
+                const float2 q2 = *reinterpret_cast<const float2*>(&sr[j * 3 + 2]);      // b, 1/depth
+                const float a = ok ? alpha : 0.f;
+                C[0] += q1.z * a * T;
+                C[1] += q1.w * a * T;
+                C[2] += q2.x * a * T;
+                expected_invdepth += q2.y * a * T;
+                T = ok ? test_T : T;
+                last_contributor = ok ? base + j + 1 : last_contributor;
             }
-            const float4 q2 = sr[j * 3 + 2];      // b, 1/depth, depth, radius
-            const float a = ok ? alpha : 0.f;
-            C[0] += q1.z * a * T;
-            C[1] += q1.w * a * T;
-            C[2] += q2.x * a * T;
-            expected_invdepth += q2.y * a * T;
-            T = ok ? test_T : T;
-            last_contributor = ok ? base + j + 1 : last_contributor;
         }
-        __syncwarp();                              // s_list is rebuilt next round
     }
 
     if (inside) {

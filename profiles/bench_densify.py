@@ -35,7 +35,7 @@ FLOATS = 59
 def hbm_peak():
     try:
         d = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        for k in ("hbm_copy_gbps_burst", "hbm_gbps", "hbm_copy_gbps"):
+        for k in ("hbm_gbs", "hbm_copy_gbps_burst", "hbm_gbps", "hbm_copy_gbps"):
             if k in d:
                 return float(d[k]), f"MEASURED_PEAKS.json:{k}"
     except Exception:  # noqa: BLE001

@@ -118,6 +118,15 @@ template <typename T> static inline T __shfl_xor_sync(uint32_t mask, T v, int de
     (void)width;
     return emu_shfl_from(mask, v, (int)emu::lane_id() ^ delta);
 }
+// redux.sync: warp-wide integer reductions (all lanes named in the mask take part; exited lanes contribute nothing)
+static inline uint32_t __reduce_or_sync(uint32_t mask, uint32_t v) {
+    for (int o = 16; o > 0; o >>= 1) v |= emu_shfl_from(mask, v, (int)emu::lane_id() ^ o);
+    return v;
+}
+static inline uint32_t __reduce_max_sync(uint32_t mask, uint32_t v) {
+    for (int o = 16; o > 0; o >>= 1) { const uint32_t w = emu_shfl_from(mask, v, (int)emu::lane_id() ^ o); v = w > v ? w : v; }
+    return v;
+}
 template <typename T> static inline T __shfl_up_sync(uint32_t mask, T v, unsigned delta, int width = 32) {
     const int lane = (int)emu::lane_id();
     const int src = lane - (int)delta;
