@@ -3,6 +3,7 @@
 #include <stdarg.h>
 #include <stdio.h>
 #include <string.h>
+#include <mutex>
 #include <vector>
 #include "common.cuh"
 
@@ -37,6 +38,7 @@ static std::vector<ProfSpan> g_spans;       // recorded, not yet collected
 static std::vector<cudaEvent_t> g_free;     // event pool
 static cudaEvent_t g_open[GSR_STAGE_COUNT];
 
+static std::mutex g_prof_mutex;           // the measurement hooks may be reached from several host threads
 static cudaEvent_t take_event() {
     cudaEvent_t e = nullptr;
     if (!g_free.empty()) { e = g_free.back(); g_free.pop_back(); }
@@ -45,11 +47,14 @@ static cudaEvent_t take_event() {
 }
 void profile_begin(int stage, cudaStream_t st) {
     if (!g_profile) return;
+    std::lock_guard<std::mutex> lock(g_prof_mutex);
     g_open[stage] = take_event();
     cudaEventRecord(g_open[stage], st);
 }
 void profile_end(int stage, cudaStream_t st) {
-    if (!g_profile || !g_open[stage]) return;
+    if (!g_profile) return;
+    std::lock_guard<std::mutex> lock(g_prof_mutex);
+    if (!g_open[stage]) return;
     cudaEvent_t b = take_event();
     cudaEventRecord(b, st);
     g_spans.push_back({stage, g_open[stage], b});
@@ -74,6 +79,10 @@ static int validate(const GsrParams* p, const GsrBuffers* buf) {
     const bool have_sr = p->scales != nullptr && p->rotations != nullptr;
     if (have_sr == (p->cov3D_precomp != nullptr) || ((p->scales != nullptr) != (p->rotations != nullptr))) {
         set_error("Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!");
+        return GSR_ERR_INVALID_ARG;
+    }
+    if (p->rotations && (reinterpret_cast<uintptr_t>(p->rotations) & 15) != 0) {
+        set_error("rotations must be 16-byte aligned (read as float4)");
         return GSR_ERR_INVALID_ARG;
     }
     if (p->sh_dc && (!p->shs || p->M < 2)) {
@@ -120,6 +129,10 @@ struct SideStream {
     cudaEvent_t joined = nullptr;
 };
 static SideStream g_side[64];
+// The banded backward re-records the per-device events above on every call: two host threads (or two caller
+// streams) driving the same device are serialised through this section, so that one call's waits can never
+// pick up the other's records.
+static std::mutex g_side_mutex;
 static SideStream* side_stream() {
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
@@ -160,6 +173,7 @@ size_t gsr_scratch_bytes(int32_t P, int32_t W, int32_t H, int64_t R) {
 }
 
 int gsr_profile_enable(int on) {
+    std::lock_guard<std::mutex> lock(g_prof_mutex);
     g_profile = on != 0;
     if (!g_profile) {
         for (auto& sp : g_spans) { g_free.push_back(sp.a); g_free.push_back(sp.b); }
@@ -169,6 +183,7 @@ int gsr_profile_enable(int on) {
 }
 
 int gsr_profile_collect(double* ms_sum, int64_t* calls) {
+    std::lock_guard<std::mutex> lock(g_prof_mutex);
     for (auto& sp : g_spans) {
         GSR_CUDA_TRY(cudaEventSynchronize(sp.b));
         float ms = 0.f;
@@ -285,6 +300,7 @@ int gsr_backward(const GsrParams* p, const GsrBuffers* buf, int64_t R, const int
     // bottom) and hand every finished band's Gaussians (those whose last tile row lies in it) to the
     // per-Gaussian kernel on a side stream, so that the gradient traffic of band k crosses NVLink
     // while band k+1 is blended.
+    std::lock_guard<std::mutex> side_lock(g_side_mutex);
     int band_hi[MAX_BANDS];
     for (int k = 0; k < bands; k++) band_hi[k] = (int)((long long)gy * (k + 1) / bands);
     GSR_CUDA_TRY(cudaEventRecord(side->joined, st));                       // order the side stream after the caller's work

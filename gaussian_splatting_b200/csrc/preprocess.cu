@@ -171,7 +171,7 @@ preprocess_fwd_kernel(GsrParams p, float focal_x, float focal_y, int gx, int gy,
                         for (int k = lane; k < Lr; k += 32) ws[SPLIT_OFF + g * rrow + k] = __ldg(rest + (size_t)g * rrow + k);
                     }
                 }
-            } else if ((L & 3) == 0 && (row & 3) == 0) {
+            } else if ((L & 3) == 0 && (row & 3) == 0 && (reinterpret_cast<uintptr_t>(p.shs) & 15) == 0) {
                 const int L4 = L >> 2;
                 for (int i = lane; i < 32 * L4; i += 32) {
                     int g = i / L4, k = i - g * L4;

@@ -62,6 +62,20 @@ __device__ __forceinline__ void out4(float* p, float4 v) {
     }
 }
 
+// Plain 16 B store; MM = true: `p` is a multicast address, which only multimem.* instructions may access
+// (PTX ISA: ld/st on a multimem address is undefined) -- multimem.st writes the value to every replica.
+template <bool MM>
+__device__ __forceinline__ void store4(float* p, float4 v) {
+#ifndef GSR_HOST_EMUL
+    if (MM) {
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                     ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+        return;
+    }
+#endif
+    *reinterpret_cast<float4*>(p) = v;
+}
+
 // auxiliary.h:128-139
 __device__ __forceinline__ float3 dnormvdv(float3 v, float3 dv) {
     float sum2 = v.x * v.x + v.y * v.y + v.z * v.z;
@@ -474,7 +488,29 @@ preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord*
     // dc block + rest block (split storage), or padded 49-float rows (scalar path).
     const bool has_sh = p.shs != nullptr;
     const bool fact = io.xchg_records != nullptr;
-    if (has_sh && (fact || io.dL_dsh != nullptr)) {
+    const bool want_sh = fact || io.dL_dsh != nullptr;
+    if (has_sh && !want_sh) {
+        // dL_dsh not wanted (NULL): the view-direction term of dL_dmeans3D is still due.  Rare call shape
+        // (a C-ABI caller; the autograd wrapper always asks for dL_dsh): coefficients straight from global memory.
+        if (visible) {
+            float row[PB_ROW];
+            const int Lc = 3 * (p.D + 1) * (p.D + 1);
+#pragma unroll
+            for (int k = 0; k < PB_ROW; k++) {
+                float v = 0.f;
+                if (k < Lc) v = !SPLIT ? __ldg(p.shs + (size_t)idx * sh_row + k)
+                                       : (k < 3 ? __ldg(p.sh_dc + (size_t)idx * 3 + k) : __ldg(p.shs + (size_t)idx * rest_row + (k - 3)));
+                row[k] = v;
+            }
+            float dL_dRGB[3];
+#pragma unroll
+            for (int c = 0; c < 3; c++) dL_dRGB[c] = ((clamped_bits >> c) & 1) ? 0.f : dL_dcolor[c];
+            const float3 dir_orig = {mean.x - s_cam[0], mean.y - s_cam[1], mean.z - s_cam[2]};
+            const float3 dm = sh_backward<false>(row, sh_row, p.D, dir_orig, dL_dRGB);
+            dL_dmean.x += dm.x; dL_dmean.y += dm.y; dL_dmean.z += dm.z;
+        }
+    }
+    if (has_sh && want_sh) {
         float* ws = sh_smem[warp];
         constexpr int KIND = VEC ? (SPLIT ? 2 : 1) : 0;
         const RowLayout lay = {KIND, sh_row};
@@ -511,8 +547,8 @@ preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord*
                 const float3 dm = sh_backward_smem<false, KIND>(ws, lane, lay, p.D, dir_orig, dL_dRGB);
                 dL_dmean.x += dm.x; dL_dmean.y += dm.y; dL_dmean.z += dm.z;
             }
-            if (blockIdx.x == 0 && threadIdx.x == 0)     // a plain store to a multicast address reaches every replica
-                *reinterpret_cast<float4*>(io.xchg_campos) = make_float4(s_cam[0], s_cam[1], s_cam[2], 1.f);
+            if (blockIdx.x == 0 && threadIdx.x == 0)     // this rank's camera centre, into its slot of every replica
+                store4<MM>(io.xchg_campos, make_float4(s_cam[0], s_cam[1], s_cam[2], 1.f));
             if (!mine) return;
             if (io.dL_dmeans2D) {
                 io.dL_dmeans2D[3 * idx] = dL_dmean2D.x; io.dL_dmeans2D[3 * idx + 1] = dL_dmean2D.y; io.dL_dmeans2D[3 * idx + 2] = 0.f;
