@@ -96,7 +96,7 @@ EXPORTS = (
     "gsr_mark_visible", "gsr_debug_sorted_keys", "gsr_debug_state_ptrs", "gsr_flat_grad_floats",
     "gsr_debug_count_work",
     "gsr_profile_enable", "gsr_profile_collect", "gsr_stage_name", "gsr_launch_count", "gsr_adam_update",
-    "gsr_ssim_partials", "gsr_ssim_forward", "gsr_ssim_backward", "gsr_exchange_expand",
+    "gsr_ssim_partials", "gsr_ssim_forward", "gsr_ssim_forward_noalloc", "gsr_ssim_backward", "gsr_exchange_expand",
     "gsr_densify_plan_words", "gsr_densify_plan", "gsr_densify_apply", "gsr_densify_stats", "gsr_reset_opacity",
     "gsr_ply_pack", "gsr_ply_unpack",
 )
@@ -179,6 +179,8 @@ def load():
     lib.gsr_ssim_partials.argtypes = [C.c_int32] * 4
     lib.gsr_ssim_forward.restype = C.c_int
     lib.gsr_ssim_forward.argtypes = [PS] + [C.c_void_p] * 7
+    lib.gsr_ssim_forward_noalloc.restype = C.c_int
+    lib.gsr_ssim_forward_noalloc.argtypes = [PS] + [C.c_void_p] * 6
     lib.gsr_ssim_backward.restype = C.c_int
     lib.gsr_ssim_backward.argtypes = [PS] + [C.c_void_p] * 7
     bind_densify(lib)

@@ -23,6 +23,7 @@
 // per-CTA partial sums + a one-block fp64 finish, so the map never has to be written.
 #include <algorithm>
 #include <limits>
+#include <mutex>
 #include "common.cuh"
 
 namespace gsr {
@@ -327,6 +328,37 @@ static int ssim_check(const GsrSsimParams* p, const char* who) {
     return GSR_OK;
 }
 
+// ---- allocation-free variant (gsr_ssim_forward_noalloc) --------------------------------------------------
+// The per-tile partial sums of the mean live in a file-scope device array instead of caller-provided scratch, so
+// the call needs no cudaMalloc (CUDA-graph capture, serving loops, harnesses that forbid allocation).  Every GPU
+// that loads the library holds these GSR_SSIM_NOALLOC_MAX_TILES floats (256 KB) until the process exits.
+static __device__ __align__(256) float g_ssim_static_partials[GSR_SSIM_NOALLOC_MAX_TILES];
+
+// In host code the array's name is a host-side stand-in, not a device address: the address a kernel can use comes
+// from cudaGetSymbolAddress, looked up once per device with that device current.
+static int ssim_static_partials(float** out) {
+    static std::mutex mu;
+    static float* ptr[64] = {};
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= 64) {
+        set_error("gsr_ssim_forward_noalloc: cudaGetDevice failed or device index out of range: %s", cudaGetErrorString(e));
+        return GSR_ERR_CUDA;
+    }
+    std::lock_guard<std::mutex> lock(mu);
+    if (ptr[dev] == nullptr) {
+        void* q = nullptr;
+        e = cudaGetSymbolAddress(&q, g_ssim_static_partials);
+        if (e != cudaSuccess || q == nullptr) {
+            set_error("gsr_ssim_forward_noalloc: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+            return GSR_ERR_CUDA;
+        }
+        ptr[dev] = static_cast<float*>(q);
+    }
+    *out = ptr[dev];
+    return GSR_OK;
+}
+
 }  // namespace gsr
 
 extern "C" int64_t gsr_ssim_partials(int32_t B, int32_t CH, int32_t H, int32_t W) {
@@ -394,4 +426,47 @@ extern "C" int gsr_ssim_backward(const GsrSsimParams* p, const float* dL_dmap, c
                    dm_dsigma1_sq, dm_dsigma12, dL_dimg1, p->H, p->W, p->crop);
     }
     return check_stage("ssim backward", false, st);
+}
+
+// Same work as gsr_ssim_forward with mean_out, but the partial sums go to the library's own static device array:
+// no cudaMalloc / cudaFree / allocating call anywhere on this path.  Every tile's slot is rewritten by each call and
+// only the first `tiles` slots are read, so nothing has to be cleared between calls; the array is shared by every
+// call on the device, so two calls that overlap on the GPU (different streams, no ordering) race.
+extern "C" int gsr_ssim_forward_noalloc(const GsrSsimParams* p, float* ssim_map, float* dm_dmu1, float* dm_dsigma1_sq,
+                                        float* dm_dsigma12, float* mean_out, void* stream) {
+    using namespace gsr;
+    if (int rc = ssim_check(p, "gsr_ssim_forward_noalloc")) return rc;
+    if (!mean_out) {
+        set_error("gsr_ssim_forward_noalloc: mean_out is required (without it the forward needs no scratch: use gsr_ssim_forward)");
+        return GSR_ERR_INVALID_ARG;
+    }
+    const bool train = dm_dmu1 || dm_dsigma1_sq || dm_dsigma12;
+    if (train && !(dm_dmu1 && dm_dsigma1_sq && dm_dsigma12)) {
+        set_error("gsr_ssim_forward_noalloc: pass all three derivative maps or none");
+        return GSR_ERR_INVALID_ARG;
+    }
+    const long long tiles = ssim_tiles(p->B, p->CH, p->H, p->W);
+    if (tiles > (long long)GSR_SSIM_NOALLOC_MAX_TILES) {
+        set_error("gsr_ssim_forward_noalloc: %lld tiles of 32x32 exceed the static scratch of %d (GSR_SSIM_NOALLOC_MAX_TILES); "
+                  "use gsr_ssim_forward with caller-provided partials", tiles, (int)GSR_SSIM_NOALLOC_MAX_TILES);
+        return GSR_ERR_CAPACITY;
+    }
+    float* part = nullptr;
+    if (int rc = ssim_static_partials(&part)) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    ssim_init_once();
+    if (tiles > 0) {
+        const dim3 grid((p->W + SS_T - 1) / SS_T, (p->H + SS_T - 1) / SS_T, p->B * p->CH);
+        if (train)
+            GSR_LAUNCH(ssim_fwd_kernel<true>, grid, SS_THREADS, 0, st, p->img1, p->img2, ssim_map, dm_dmu1, dm_dsigma1_sq,
+                       dm_dsigma12, part, p->H, p->W, p->C1, p->C2, p->crop);
+        else
+            GSR_LAUNCH(ssim_fwd_kernel<false>, grid, SS_THREADS, 0, st, p->img1, p->img2, ssim_map, dm_dmu1, dm_dsigma1_sq,
+                       dm_dsigma12, part, p->H, p->W, p->C1, p->C2, p->crop);
+    }
+    const long long ch = std::max(0, p->H - 2 * p->crop), cw = std::max(0, p->W - 2 * p->crop);
+    const double count = (double)p->B * p->CH * ch * cw;
+    const double inv = count > 0 ? 1.0 / count : std::numeric_limits<double>::quiet_NaN();
+    GSR_LAUNCH(ssim_mean_kernel, 1, 1024, 0, st, (const float*)part, tiles, inv, mean_out);
+    return check_stage("ssim forward (no-alloc)", false, st);
 }

@@ -215,6 +215,18 @@ int64_t gsr_ssim_partials(int32_t B, int32_t CH, int32_t H, int32_t W);
  * fixed order; needs `partials`. */
 int gsr_ssim_forward(const GsrSsimParams* p, float* ssim_map, float* dm_dmu1, float* dm_dsigma1_sq,
                      float* dm_dsigma12, float* mean_out, float* partials, void* stream);
+/* Allocation-free variant of gsr_ssim_forward (mean_out required).  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA-graph capture, tight serving loops,
+ * harnesses that forbid allocation).  The per-tile partial sums go to a static device array inside the library
+ * (GSR_SSIM_NOALLOC_MAX_TILES floats = 256 KB, held by every GPU that loads the library until the process exits);
+ * the call makes no cudaMalloc / cudaFree / allocating library call.  Inputs and outputs are still the caller's.
+ * Limit: B*CH*ceil(H/32)*ceil(W/32) <= GSR_SSIM_NOALLOC_MAX_TILES (e.g. 3 x 2160 x 3840, or 5 x 5 x 1080 x 1920),
+ * larger sizes return GSR_ERR_CAPACITY.  All calls on a device share the array: calls that overlap on the GPU
+ * (different streams without ordering) race; calls ordered on one stream are safe, and nothing needs clearing
+ * between them (every slot read is rewritten by the same call). */
+#define GSR_SSIM_NOALLOC_MAX_TILES 65536
+int gsr_ssim_forward_noalloc(const GsrSsimParams* p, float* ssim_map, float* dm_dmu1, float* dm_dsigma1_sq,
+                             float* dm_dsigma12, float* mean_out, void* stream);
 /* dL_dimg1 [B,CH,H,W] from either dL_dmap (full-size map gradient, ssim.cu:283-365) or, when
  * dL_dmap == NULL, the device scalar *dL_dmean = dL/d(mean of the cropped map). */
 int gsr_ssim_backward(const GsrSsimParams* p, const float* dL_dmap, const float* dL_dmean,
