@@ -45,8 +45,8 @@ FP32_LANES_PER_SM = 128
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=30)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=50)      # 10 warm-up, >= 50 timed iterations
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="C3", help="C1|C2|C3|C4 (SURVEY.md §8d) or C3 with --P override")
     ap.add_argument("--P", type=int, default=None, help="override the Gaussian count")
@@ -189,13 +189,23 @@ def make_steps(module, wl, device, flat=None):
     tgt_host = torch.cat([wl["target"].reshape(-1), wl["target_d"].reshape(-1)]).pin_memory()
     cam_dev = torch.empty_like(cam_host, device=device)
     tgt_dev = torch.empty_like(tgt_host, device=device)
-    loss_host = torch.zeros(1).pin_memory()
+    loss_host = torch.zeros(2).pin_memory()      # ring of two slots: step i's loss is read while step i+1 is enqueued
+    loss_ready = [torch.cuda.Event(), torch.cuda.Event()]
+    pending = []                                 # [(slot)] of the step whose loss has not been read yet
+    losses = []
     bg_dev = wl["s"]["bg"].to(device)
     h2d = cam_host.numel() * 4 + tgt_host.numel() * 4
     d2h = 4
 
     copy_stream = torch.cuda.Stream(device=device)
     copied = torch.cuda.Event()
+    counter = [0]
+
+    def drain():
+        while pending:
+            slot = pending.pop(0)
+            loss_ready[slot].synchronize()
+            losses.append(float(loss_host[slot]))
 
     def step_e2e():
         clear()
@@ -219,41 +229,88 @@ def make_steps(module, wl, device, flat=None):
         loss.backward()
         if flat is not None:
             flat.all_reduce()
-        loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
-        torch.cuda.current_stream().synchronize()
-        return float(loss_host[0])
+        # Every step's loss crosses to the host; it is READ one step late (event-guarded pinned slot), so the host
+        # enqueues step i+1 while the device finishes step i instead of idling the device during the host's set-up.
+        slot = counter[0] & 1
+        counter[0] += 1
+        loss_host[slot:slot + 1].copy_(loss.detach().reshape(1), non_blocking=True)
+        loss_ready[slot].record(torch.cuda.current_stream(device))
+        pending.append(slot)
+        if len(pending) > 1:
+            s0 = pending.pop(0)
+            loss_ready[s0].synchronize()
+            losses.append(float(loss_host[s0]))
 
+    step_e2e.drain = drain
+    step_e2e.losses = losses
     return step_resident, step_forward_only, step_e2e, (h2d, d2h)
 
 
-def timed_loop(step, steps, warmup, world, device, on_start=None):
+def timed_loop(step, steps, warmup, world, device, on_start=None, per_step=None, drain=None):
     """W untimed steps, then exactly K steps between barrier + synchronize; device time by CUDA
-    events on the launching stream, max over ranks.  Returns (ms_total_max, wall t0, wall t1)."""
+    events on the launching stream, max over ranks.  Returns (ms_total_max, wall t0, wall t1).
+    per_step: list that receives this rank's K step durations (an event after every step).
+    drain: called after the last step, inside the timed region (a pipelined step's pending read-back)."""
     for _ in range(warmup):
         step()
+    if drain is not None:
+        drain()
     torch.cuda.synchronize(device)
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize(device)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
     if on_start is not None:
         on_start()
     t0 = time.time()
-    e0.record()
-    for _ in range(steps):
+    ev[0].record()
+    for i in range(steps):
         step()
-    e1.record()
+        ev[i + 1].record()
+    if drain is not None:
+        drain()
     torch.cuda.synchronize(device)
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize(device)
     t1 = time.time()
-    ms = e0.elapsed_time(e1)
+    ms = ev[0].elapsed_time(ev[-1])
+    if per_step is not None:
+        per_step.extend(ev[i].elapsed_time(ev[i + 1]) for i in range(steps))
     if world > 1:
         t = torch.tensor([ms], device=device, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t[0])
     return ms, t0, t1
+
+
+def percentiles(ms_list):
+    """median / p10 / p90 of the per-step device times."""
+    if not ms_list:
+        return None
+    v = sorted(ms_list)
+    q = lambda f: v[min(len(v) - 1, max(0, int(round(f * (len(v) - 1)))))]  # noqa: E731
+    return {"median": round(q(0.5), 4), "p10": round(q(0.1), 4), "p90": round(q(0.9), 4), "n": len(v)}
+
+
+def measure_fp32_peak(device):
+    """Scalar-FFMA rate of this GPU at its clocks right now (gsr_debug_fp32_peak), TFLOP/s; best of 5 launches."""
+    import ctypes as C
+    from gaussian_splatting_b200 import _lib
+    lib = _lib.load()
+    sink = torch.zeros(1, device=device)
+    flops = C.c_double(0.0)
+    st = torch.cuda.current_stream(device).cuda_stream
+    best = 0.0
+    for i in range(6):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        _lib.check(lib.gsr_debug_fp32_peak(SM_COUNT_B200 * 16, 4096, sink.data_ptr(), C.byref(flops), st))
+        e1.record()
+        e1.synchronize()
+        if i:
+            best = max(best, flops.value / (e0.elapsed_time(e1) * 1e-3) / 1e12)
+    return best
 
 
 # ------------------------------------------------------------------ roofline bookkeeping
@@ -262,29 +319,36 @@ def stage_model(work):
     HBM stages: minimum bytes the stage must move; render stages: FLOP model of SURVEY.md §8d."""
     P, V, R, T, N = work["P"], work["V"], work["R"], work["T"], work["N"]
     Wf, Wb, Bp = work["Wf"], work["Wb"], work["Bp"]
-    tile_passes = max(1, (max(T, 1).bit_length() + 7) // 8)
-    return {
+    C = work.get("chunks", 1)            # chunks of depth ranks in the tile-list construction (common.cuh: tile_bin_plan)
+    world = work.get("world", 1)
+    m = {
         # means 12 + radii 4 + depth key 8 + rect 8 for all; scales/rot/opacity/SH 224 read + record 64 written for visible
         "preprocess": ("hbm", 32 * P + 288 * V),
-        # 4 LSD passes over P 8-byte items: histogram read + scatter read + scatter write
-        "depth_sort": ("hbm", 4 * 24 * P),
-        # sorted keys 8 + rect gather 8 + counts write 4, then read 4 + write 4
-        "scan": ("hbm", 28 * P),
-        # key 8 + rect 8 + offset 4 per Gaussian, 8 per instance written
-        "emit": ("hbm", 20 * P + 8 * R),
-        # per pass: histogram read 8 + scatter read 8 + write 8 (last pass writes 4 + 4)
-        "tile_sort": ("hbm", tile_passes * 24 * R),
-        "tile_ranges": ("hbm", 4 * R + 8 * T),
+        # one histogram read (8 P) + 4 LSD passes that read and write the 8-byte items once each (16 P)
+        "depth_sort": ("hbm", 72 * P),
+        # key 8 + rect gather 8 + depth-ordered rect 8 per visible Gaussian; the (chunk, tile) counts written (4 C T),
+        # read and rewritten as prefixes (8 C T); totals 4 T written + read, ranges 8 T written
+        "tile_count": ("hbm", 24 * V + 12 * C * T + 16 * T),
+        # key 8 + rect 8 per visible Gaussian, the chunk prefixes 4 C T + tile starts 8 T read, 4 bytes per instance written
+        "tile_fill": ("hbm", 16 * V + 4 * C * T + 8 * T + 4 * R),
         "render_fwd": ("fp32", 14 * Wf + 11 * Bp),
         "render_bwd": ("fp32", 14 * Wb + 75 * Bp),
         # SURVEY.md §8d S4b: dense outputs for every Gaussian + visible reads (+ 48 B accumulator)
         "preprocess_bwd": ("hbm", 236 * P + 287 * V + 48 * V),
     }
+    if world > 1:
+        # factored exchange: the sender branch writes dL_dmeans2D densely (12 P) and publishes 64 B per contributing
+        # Gaussian instead of 236 B rows; the expand pass reads one 16 B colour-gradient slot per rank, the 48 B
+        # record and the mean of every Gaussian and writes the 236 B dense gradient row
+        m["preprocess_bwd"] = ("hbm", 12 * P + (287 + 48 + 64) * V)
+        m["exchange"] = ("hbm", (16 * world + 48 + 12 + 236) * P)
+    return m
 
 
 def rooflines(stage_ms, work, peaks, sm_mhz):
     model = stage_model(work)
-    fp32_peak = SM_COUNT_B200 * FP32_LANES_PER_SM * 2 * peaks["sm_max_mhz"] * 1e6 / 1e12   # TFLOP/s at max clock
+    # measured scalar-FFMA rate when available (gsr_debug_fp32_peak), else the nominal CUDA-core peak at max clock
+    fp32_peak = peaks.get("fp32_tflops") or SM_COUNT_B200 * FP32_LANES_PER_SM * 2 * peaks["sm_max_mhz"] * 1e6 / 1e12
     out = []
     for name, (ms_total, calls) in stage_ms.items():
         if not calls or name not in model:
@@ -303,21 +367,38 @@ def rooflines(stage_ms, work, peaks, sm_mhz):
     return out
 
 
+STAGE_KERNELS = {"render_bwd": ("render_bwd_kernel", "render_bwd.cu"), "render_fwd": ("render_fwd_kernel", "render_fwd.cu"),
+                 "preprocess_bwd": ("preprocess_bwd_kernel", "preprocess_bwd.cu"),
+                 "preprocess": ("preprocess_fwd_kernel", "preprocess.cu")}
+
+
+def source_sha1(src):
+    import hashlib
+    return hashlib.sha1(open(os.path.join(ROOT, "gaussian_splatting_b200", "csrc", src), "rb").read()).hexdigest()[:16]
+
+
 def ncu_evidence(stage):
-    """DRAM traffic per launch and issue-slot utilisation of a stage's kernel from the committed
-    `ncu --set full` capture of this same workload (newest profiles/r*_kernels.json); None if absent."""
+    """DRAM traffic per launch and issue-slot utilisation of a stage's kernel from a committed `ncu --set full`
+    capture of this same workload (profiles/**/r*_kernels*.json; profiles/ncu_kernels_json.py stamps every entry with
+    the sha1 of the kernel's source file at capture time).  Returns None when there is no capture of the kernel as it
+    is now, so that a stale number never rides on a fresh line."""
     import glob
-    found = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_kernels.json")))
-    path = found[-1] if found else ""
-    kernel = {"render_bwd": "render_bwd_kernel", "render_fwd": "render_fwd_kernel",
-              "preprocess_bwd": "preprocess_bwd_kernel", "preprocess": "preprocess_fwd_kernel"}.get(stage)
-    if kernel is None or not os.path.exists(path):
+    if stage not in STAGE_KERNELS:
         return None
-    for k in json.load(open(path)):
-        if k["kernel"].startswith(kernel):
-            return dict(traffic=int((k["dram_read_MB"] + k["dram_write_MB"]) * 1e6),
-                        issue_active=round(k["issue_active_pct"] / 100.0, 3),
-                        source="profiles/" + os.path.basename(path))
+    kernel, src = STAGE_KERNELS[stage]
+    now = source_sha1(src)
+    found = sorted(glob.glob(os.path.join(ROOT, "profiles", "**", "r*_kernels*.json"), recursive=True))
+    for path in reversed(found):
+        try:
+            entries = json.load(open(path))
+        except Exception:   # noqa: BLE001
+            continue
+        for k in entries:
+            if k.get("kernel", "").startswith(kernel) and k.get("src_sha1") == now:
+                return dict(traffic=int((k["dram_read_MB"] + k["dram_write_MB"]) * 1e6),
+                            issue_active=round(k["issue_active_pct"] / 100.0, 3),
+                            source="profiles/" + os.path.relpath(path, os.path.join(ROOT, "profiles")),
+                            src_sha1=now)
     return None
 
 
@@ -334,8 +415,11 @@ def measure_work(wl, device):
                                                          p["rotations"], e, state_out=st)
     c = st["work_counts"].cpu().tolist()
     W, H = wl["W"], wl["H"]
-    return dict(P=wl["P"], V=int((radii > 0).sum()), R=int(R), T=((W + 15) // 16) * ((H + 15) // 16), N=W * H,
-                Wf=int(c[0]), Bp=int(c[1]), Wb=int(c[2]))
+    gx, gy = (W + 15) // 16, (H + 15) // 16
+    band_rows = max(1, min(gy, 512, 8192 // gx))                       # common.cuh: tile_bin_plan
+    chunks = max(1, min(888 // ((gy + band_rows - 1) // band_rows), wl["P"] // 64))
+    return dict(P=wl["P"], V=int((radii > 0).sum()), R=int(R), T=gx * gy, N=W * H,
+                Wf=int(c[0]), Bp=int(c[1]), Wb=int(c[2]), chunks=chunks)
 
 
 # ------------------------------------------------------------------ CPU baseline (oracle port)
@@ -381,6 +465,64 @@ def base_line(args, wl, world, impl):
     }
 
 
+def reduce_check(module, wl, device, world):
+    """N > 1: the gradients the fused exchange delivers against the same gradients computed per rank without it and
+    summed with dist.all_reduce.  Raises above 1e-5 (norm-wise), so a SCALE line only exists for correct sums."""
+    from gaussian_splatting_b200 import rasterizer as rz
+    params, means2D = wl["params"], wl["means2D"]
+    rast = module.GaussianRasterizer(settings_of(module, wl["s"], device))
+    dc, dd = wl["dc_dev"], wl["dd_dev"]
+
+    def grads():
+        for t in list(params.values()) + [means2D]:
+            t.grad = None
+        color, radii, invd = rast(means3D=params["means3D"], means2D=means2D, opacities=params["opacities"],
+                                  shs=params["shs"], scales=params["scales"], rotations=params["rotations"])
+        torch.autograd.backward([color, invd], [dc, dd])
+        torch.cuda.synchronize(device)
+        return {k: v.grad.detach().clone() for k, v in params.items()}
+
+    fused = grads()
+    red = rz._gradient_reducer
+    rz.set_gradient_reducer(None)
+    try:
+        plain = grads()
+    finally:
+        rz.set_gradient_reducer(red)
+    worst = 0.0
+    per = {}
+    for k, g in plain.items():
+        dist.all_reduce(g, op=dist.ReduceOp.SUM)
+        err = float((fused[k] - g).abs().max() / g.abs().max().clamp_min(1e-30))
+        per[k] = float(f"{err:.3e}")
+        worst = max(worst, err)
+    t = torch.tensor([worst], device=device, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    worst = float(t[0])
+    if not worst < 1e-5:
+        raise SystemExit(f"reduce_check failed: fused exchange differs from all_reduce by {worst:.3e} ({per})")
+    return {"max_rel_err": float(f"{worst:.3e}"), "ranks": world, "per_tensor_rank0": per,
+            "what": "||fused - all_reduce(unfused)||inf / ||all_reduce(unfused)||inf, max over tensors and ranks"}
+
+
+def traced_gaps(step, device, n=10):
+    """Mean device-time gaps between the phase boundaries of a step on this rank (events on the launching stream):
+    bwd0->begun = wait for the all-ranks-cleared barrier, begun->sent = blend backward + publishing kernel,
+    sent->barrier = all-ranks-published barrier, barrier->expanded = gsr_exchange_expand."""
+    from gaussian_splatting_b200 import rasterizer as rz
+    was = rz._TRACE
+    rz._TRACE = True
+    try:
+        rz.trace_reset()
+        for _ in range(n):
+            step()
+        torch.cuda.synchronize(device)
+        return rz.trace_summary()
+    finally:
+        rz._TRACE = was
+        rz.trace_reset()
+
+
 def run_gpu_arm(args, module, impl, rank, world, local):
     device = torch.device("cuda", local)
     torch.cuda.set_device(device)
@@ -409,6 +551,7 @@ def run_gpu_arm(args, module, impl, rank, world, local):
     if ours:
         from gaussian_splatting_b200 import _lib
         work = measure_work(wl, device)
+        work["world"] = world
 
     sampler = ClockSampler(local)
     sampler.start()
@@ -423,7 +566,8 @@ def run_gpu_arm(args, module, impl, rank, world, local):
     def on_start_all():
         on_start()
         _rz.trace_reset()
-    ms, t0, t1 = timed_loop(step, args.steps, args.warmup, world, device, on_start_all)
+    per_step = []
+    ms, t0, t1 = timed_loop(step, args.steps, args.warmup, world, device, on_start_all, per_step=per_step)
     trace = _rz.trace_summary() if ours else {}
     clocks = sampler.stop(t0, t1)
     line = base_line(args, wl, world, impl)
@@ -435,23 +579,31 @@ def run_gpu_arm(args, module, impl, rank, world, local):
         _lib.profile_enable(False)
     ms_step = ms / args.steps
     line.update(value=round(world * 1000.0 / ms_step, 3), ms_per_step=round(ms_step, 4), clocks=clocks)
+    line["ms_per_step_percentiles"] = percentiles(per_step)      # this rank's steps (median / p10 / p90)
 
     # forward-only FPS
     ms_f, _, _ = timed_loop(step_fwd, args.steps, 3, world, device)
     line["fwd_fps"] = round(world * 1000.0 * args.steps / ms_f, 2)
 
     if not args.no_e2e:
-        ms_e, _, _ = timed_loop(step_e2e, args.steps, 3, world, device)
+        per_e = []
+        ms_e, _, _ = timed_loop(step_e2e, args.steps, 3, world, device, per_step=per_e, drain=step_e2e.drain)
         line["e2e"] = {"value": round(world * 1000.0 * args.steps / ms_e, 3), "unit": UNIT,
                        "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                       "ms_per_step_percentiles": percentiles(per_e),
                        "what": "camera + target image/depth from pinned host memory (targets on a copy stream, overlapped with the forward), L1 losses in torch, "
-                               "backward, loss scalar read back; Gaussian parameters stay resident (they "
-                               "are the model)"}
+                               "backward, loss scalar copied to pinned memory every step and read by the host one step "
+                               "late (event-guarded ring of two slots; the last one is drained inside the timed region); "
+                               "Gaussian parameters stay resident (they are the model)"}
+    if ours and world > 1:
+        line["reduce_check"] = reduce_check(module, wl, device, world)
+        line["trace_ms"] = traced_gaps(step, device)
     if ours:
         peaks = load_peaks()
+        peaks["fp32_tflops"] = round(measure_fp32_peak(device), 2)
         stages = rooflines(stage_ms, work, peaks, clocks.get("sm_mhz"))
         line["gpu_launches"] = int(launches)
-        if trace:
+        if trace and "trace_ms" not in line:
             line["trace_ms"] = trace          # GSR_TRACE_EVENTS=1: mean gaps between phase boundaries on this rank
         line["work"] = work
         line["stages"] = stages
@@ -468,11 +620,13 @@ def run_gpu_arm(args, module, impl, rank, world, local):
                             "peak": top["peak"], "unit": top["unit"], "frac": top["frac"], "traffic": None,
                             "ms": top["ms"],
                             "peak_source": (f"{peaks['source']} copy bandwidth (MEASURED_PEAKS.json)" if top["bound"] == "hbm"
-                                            else "FP32 CUDA-core peak = 148 SMs x 128 lanes x 2 x max SM clock")}
+                                            else "scalar FFMA rate measured in this run (gsr_debug_fp32_peak, best of 5 "
+                                                 "launches; nominal 148 SMs x 128 lanes x 2 x max SM clock = "
+                                                 f"{SM_COUNT_B200 * FP32_LANES_PER_SM * 2 * peaks['sm_max_mhz'] / 1e6:.1f})")}
         ev = ncu_evidence(top["stage"]) if wl["cfg"].name == "C3" and wl["P"] == wl["cfg"].P else None
         if ev:
             line["roofline"].update(traffic=ev["traffic"], issue_slot_utilisation=ev["issue_active"],
-                                    ncu_source=ev["source"])
+                                    ncu_source=ev["source"], ncu_src_sha1=ev["src_sha1"])
         hbm = [s for s in stages if s["bound"] == "hbm"]
         if hbm:
             line["roofline_hbm"] = hbm[0]

@@ -37,7 +37,7 @@ class GsrBuffers(C.Structure):
         ("img", _fp), ("img_bytes", C.c_size_t),
         ("bin", _fp), ("bin_bytes", C.c_size_t),
         ("scratch", _fp), ("scratch_bytes", C.c_size_t),
-        ("num_rendered_host", _fp),
+        ("num_rendered_host", _fp), ("num_rendered_event", _fp),
     ]
 
 
@@ -94,13 +94,13 @@ EXPORTS = (
     "gsr_version", "gsr_last_error", "gsr_geom_bytes", "gsr_img_bytes", "gsr_bin_bytes",
     "gsr_scratch_bytes", "gsr_forward_stage1", "gsr_forward_stage2", "gsr_forward", "gsr_backward",
     "gsr_mark_visible", "gsr_debug_sorted_keys", "gsr_debug_state_ptrs", "gsr_flat_grad_floats",
-    "gsr_debug_count_work",
+    "gsr_debug_count_work", "gsr_debug_fp32_peak",
     "gsr_profile_enable", "gsr_profile_collect", "gsr_stage_name", "gsr_launch_count", "gsr_adam_update",
     "gsr_ssim_partials", "gsr_ssim_forward", "gsr_ssim_forward_noalloc", "gsr_ssim_backward", "gsr_exchange_expand",
     "gsr_densify_plan_words", "gsr_densify_plan", "gsr_densify_apply", "gsr_densify_stats", "gsr_reset_opacity",
     "gsr_ply_pack", "gsr_ply_unpack",
 )
-STAGE_COUNT = 9
+STAGE_COUNT = 8
 
 _lib = None
 
@@ -163,6 +163,8 @@ def load():
     lib.gsr_debug_state_ptrs.argtypes = [PP, PB, C.c_int64] + [C.POINTER(C.c_void_p)] * 5
     lib.gsr_debug_count_work.restype = C.c_int
     lib.gsr_debug_count_work.argtypes = [PP, PB, C.c_int64, C.c_void_p, C.c_void_p]
+    lib.gsr_debug_fp32_peak.restype = C.c_int
+    lib.gsr_debug_fp32_peak.argtypes = [C.c_int32, C.c_int32, C.c_void_p, C.POINTER(C.c_double), C.c_void_p]
     lib.gsr_profile_enable.restype = C.c_int
     lib.gsr_profile_enable.argtypes = [C.c_int]
     lib.gsr_profile_collect.restype = C.c_int

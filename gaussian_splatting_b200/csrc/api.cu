@@ -65,8 +65,8 @@ static int validate(const GsrParams* p, const GsrBuffers* buf) {
     if (!p || !buf) { set_error("null argument"); return GSR_ERR_INVALID_ARG; }
     if (p->P <= 0) { set_error("P must be > 0 (P == 0 is handled by the caller)"); return GSR_ERR_INVALID_ARG; }
     if (p->W <= 0 || p->H <= 0) { set_error("image size must be positive"); return GSR_ERR_INVALID_ARG; }
-    if ((p->W + TILE_X - 1) / TILE_X > 65535 || (p->H + TILE_Y - 1) / TILE_Y > 65535) {
-        set_error("image too large: tile grid exceeds 65535 per axis"); return GSR_ERR_INVALID_ARG;
+    if ((p->W + TILE_X - 1) / TILE_X > TB_MAX_GX || (p->H + TILE_Y - 1) / TILE_Y > 65535) {
+        set_error("image too large: tile grid exceeds %d columns or 65535 rows", TB_MAX_GX); return GSR_ERR_INVALID_ARG;
     }
     if (!p->means3D || !p->opacities || !p->background || !p->viewmatrix || !p->projmatrix || !p->campos) {
         set_error("means3D, opacities, background, viewmatrix, projmatrix, campos are required");
@@ -121,6 +121,13 @@ static int validate_R(const GsrParams* p, const GsrBuffers* buf, int64_t R) {
     return GSR_OK;
 }
 
+// the 64-bit instance count as the two words stage 1 copies to the host
+static int read_num_rendered(const int32_t* host, int64_t* R) {
+    if (host[1] != 0 || host[0] < 0) { set_error("num_rendered exceeds int32"); return GSR_ERR_OVERFLOW; }
+    *R = host[0];
+    return GSR_OK;
+}
+
 // Host-side resources for the banded backward: one non-blocking side stream and a few events per
 // device, created on first use and kept for the life of the process (no device memory).
 struct SideStream {
@@ -168,8 +175,8 @@ size_t gsr_bin_bytes(int64_t R) {
     size_t b; BinState::carve(nullptr, (size_t)(R > 0 ? R : 0), &b); return b;
 }
 size_t gsr_scratch_bytes(int32_t P, int32_t W, int32_t H, int64_t R) {
-    (void)W; (void)H;
-    size_t b; Scratch::carve(nullptr, (size_t)(P > 0 ? P : 1), (size_t)(R > 0 ? R : 0), &b); return b;
+    (void)R;    // no R-sized scratch: the (Gaussian, tile) instances are never materialised outside `bin`
+    size_t b; Scratch::carve(nullptr, (size_t)(P > 0 ? P : 1), W, H, &b); return b;
 }
 
 int gsr_profile_enable(int on) {
@@ -197,8 +204,8 @@ int gsr_profile_collect(double* ms_sum, int64_t* calls) {
 }
 
 const char* gsr_stage_name(int stage) {
-    static const char* names[GSR_STAGE_COUNT] = {"preprocess", "depth_sort", "scan", "emit", "tile_sort",
-                                                 "tile_ranges", "render_fwd", "render_bwd", "preprocess_bwd"};
+    static const char* names[GSR_STAGE_COUNT] = {"preprocess", "depth_sort", "tile_count", "tile_fill",
+                                                 "render_fwd", "render_bwd", "preprocess_bwd", "exchange"};
     return stage >= 0 && stage < GSR_STAGE_COUNT ? names[stage] : "?";
 }
 
@@ -217,11 +224,11 @@ int gsr_forward_stage1(const GsrParams* p, const GsrBuffers* buf, const GsrForwa
     }
     cudaStream_t st = (cudaStream_t)stream;
     GeomState g = GeomState::carve(buf->geom, p->P, nullptr);
-    // the P-sized part of the scratch layout does not depend on R
-    Scratch s = Scratch::carve(buf->scratch, p->P, 0, nullptr);
+    ImgState im = ImgState::carve(buf->img, (size_t)p->W * p->H, tiles_of(p->W, p->H), nullptr);
+    Scratch s = Scratch::carve(buf->scratch, p->P, p->W, p->H, nullptr);
     rc = launch_preprocess(*p, g, s, out->radii, st);
     if (rc) return rc;
-    return launch_depth_order_and_scan(*p, g, s, buf->num_rendered_host, st);
+    return launch_depth_order_and_count(*p, g, im, s, buf->num_rendered_host, buf->num_rendered_event, st);
 }
 
 int gsr_forward_stage2(const GsrParams* p, const GsrBuffers* buf, const GsrForwardOut* out, int64_t R,
@@ -237,8 +244,8 @@ int gsr_forward_stage2(const GsrParams* p, const GsrBuffers* buf, const GsrForwa
     GeomState g = GeomState::carve(buf->geom, p->P, nullptr);
     ImgState im = ImgState::carve(buf->img, (size_t)p->W * p->H, tiles_of(p->W, p->H), nullptr);
     BinState b = BinState::carve(buf->bin, (size_t)R, nullptr);
-    Scratch s = Scratch::carve(buf->scratch, p->P, (size_t)R, nullptr);
-    rc = launch_binning(*p, g, im, b, s, R, st);
+    Scratch s = Scratch::carve(buf->scratch, p->P, p->W, p->H, nullptr);
+    rc = launch_tile_lists(*p, g, im, b, s, R, st);
     if (rc) return rc;
     return launch_render_forward(*p, g, im, b, out->out_color, out->out_invdepth, st);
 }
@@ -249,8 +256,9 @@ int gsr_forward(const GsrParams* p, const GsrBuffers* buf, const GsrForwardOut* 
     int rc = gsr_forward_stage1(p, buf, out, stream);
     if (rc) return rc;
     GSR_CUDA_TRY(cudaStreamSynchronize((cudaStream_t)stream));
-    if (buf->num_rendered_host[1]) { set_error("num_rendered exceeds int32"); return GSR_ERR_OVERFLOW; }
-    const int64_t R = buf->num_rendered_host[0];
+    int64_t R = 0;
+    rc = read_num_rendered(buf->num_rendered_host, &R);
+    if (rc) return rc;
     if (num_rendered) *num_rendered = R;
     return gsr_forward_stage2(p, buf, out, R, stream);
 }
@@ -266,7 +274,7 @@ int gsr_backward(const GsrParams* p, const GsrBuffers* buf, int64_t R, const int
     GeomState g = GeomState::carve(buf->geom, p->P, nullptr);
     ImgState im = ImgState::carve(buf->img, (size_t)p->W * p->H, tiles_of(p->W, p->H), nullptr);
     BinState b = BinState::carve(buf->bin, (size_t)R, nullptr);
-    Scratch s = Scratch::carve(buf->scratch, p->P, (size_t)R, nullptr);
+    Scratch s = Scratch::carve(buf->scratch, p->P, p->W, p->H, nullptr);
     const int gy = (p->H + TILE_Y - 1) / TILE_Y;
     const bool have_invdepth = io->dL_dout_invdepth != nullptr;
     const bool fact = io->xchg_records != nullptr;

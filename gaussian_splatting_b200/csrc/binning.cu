@@ -1,15 +1,20 @@
-// binning.cu — kernel group 2 of the path: depth ordering, tile-count scan, instance
-// emission, stable tile ordering, tile ranges.
+// binning.cu — kernel group 2 of the path: depth ordering and the per-tile, depth-ordered Gaussian lists.
 //
 // Replaces cub::DeviceScan::InclusiveSum + duplicateWithKeys + cub::DeviceRadixSort::
 // SortPairs<u64,u32> + identifyTileRanges (DGR/cuda_rasterizer/rasterizer_impl.cu:78-164,
-// 309-350).  The reference sorts R (tile|depth) 64-bit keys in 6 radix passes.  Here the
-// same total order (tile, depth bits, Gaussian id) is produced in two cheaper steps:
-//   1. stable LSD radix sort of the P Gaussians by depth bits (4 passes over P items);
-//   2. instances are emitted in that depth order and then stably ordered by tile id
-//      only: ceil(getHigherMsb(T)/8) passes over R items (2 at every benchmark size).
-// Stability makes the result identical to the reference's stable sort of
-// (tile<<32 | depth) keys with emission order (id, tile) as the tie-break.
+// 309-350).  The reference materialises R (tile|depth, id) pairs and sorts them in 6 radix
+// passes.  The same total order (tile, depth bits, Gaussian id) is produced here without ever
+// sorting the R instances:
+//   1. stable LSD radix sort of the P Gaussians by depth bits (4 onesweep passes over P items);
+//   2. the depth-ordered Gaussians are cut into chunks; every (chunk, tile) count comes from a
+//      2-D difference grid (4 shared-memory adds per Gaussian + a prefix sum), a prefix over
+//      the chunks of each tile gives every chunk its first slot in every tile list, a scan
+//      over the tiles gives the tile ranges and num_rendered;
+//   3. one warp per chunk walks its Gaussians in depth order and appends each to the lists of
+//      the tiles of its rectangle (lanes = tiles of one Gaussian, running slots in shared memory).
+// A tile's list is filled in depth order (chunks in order, Gaussians in order inside a chunk);
+// ties in depth keep Gaussian-id order because the depth sort is stable: the result equals the
+// reference's stable sort of (tile<<32 | depth) keys emitted in (id, tile) order, bit for bit.
 #include "common.cuh"
 #include "block_scan.cuh"
 
@@ -52,15 +57,12 @@ radix_rowscan_kernel(uint32_t* __restrict__ hist, uint32_t nb, uint32_t* __restr
     if (threadIdx.x == 0) digit_tot[blockIdx.x] = total;
 }
 
-// Stable scatter of one 8-bit digit.  SPLIT: final pass, write low word to out_lo
-// (Gaussian id) and high word to out_hi (tile id) instead of the u64 item.
-template <bool SPLIT>
+// Stable scatter of one 8-bit digit.
 __global__ void __launch_bounds__(SORT_THREADS)
 radix_scatter_kernel(const uint64_t* __restrict__ in, uint32_t n, int shift,
                      const uint32_t* __restrict__ hist, uint32_t nb,
                      const uint32_t* __restrict__ digit_tot,
-                     uint64_t* __restrict__ out, uint32_t* __restrict__ out_lo,
-                     uint32_t* __restrict__ out_hi) {
+                     uint64_t* __restrict__ out) {
     __shared__ uint32_t wh[8][256];
     __shared__ uint64_t stage[SORT_CHUNK];
     __shared__ uint32_t s_gbase[256];
@@ -131,13 +133,7 @@ radix_scatter_kernel(const uint64_t* __restrict__ in, uint32_t n, int shift,
         if (idx < n_block) {
             uint64_t it = stage[idx];
             uint32_t d = (uint32_t)(it >> shift) & 255u;
-            uint32_t pos = s_gbase[d] + idx;
-            if (SPLIT) {
-                out_lo[pos] = (uint32_t)it;
-                out_hi[pos] = (uint32_t)(it >> 32);
-            } else {
-                out[pos] = it;
-            }
+            out[s_gbase[d] + idx] = it;
         }
     }
 }
@@ -202,11 +198,9 @@ radix_bases_kernel(const uint32_t* __restrict__ ghist, uint32_t* __restrict__ gb
 #ifndef OS_MIN_BLOCKS
 #define OS_MIN_BLOCKS 3
 #endif
-template <bool SPLIT>
 __global__ void __launch_bounds__(OS_THREADS, OS_MIN_BLOCKS)
 onesweep_kernel(const uint64_t* __restrict__ in, uint32_t n, int shift, const uint32_t* __restrict__ gbase,
-                uint32_t* status, uint32_t* ticket,
-                uint64_t* __restrict__ out, uint32_t* __restrict__ out_lo, uint32_t* __restrict__ out_hi) {
+                uint32_t* status, uint32_t* ticket, uint64_t* __restrict__ out) {
     __shared__ uint16_t wh[OS_WARPS][256];           // per-warp digit counts (<= 256), then prefixes (<= 4096)
     __shared__ uint64_t stage[OS_TILE];
     __shared__ uint32_t s_gbase[256];
@@ -319,36 +313,16 @@ onesweep_kernel(const uint64_t* __restrict__ in, uint32_t n, int shift, const ui
         if (idx < n_block) {
             const uint64_t it = stage[idx];
             const uint32_t d = (uint32_t)(it >> shift) & 255u;
-            const uint32_t pos = s_gbase[d] + idx;
-            if (SPLIT) {
-                out_lo[pos] = (uint32_t)it;
-                out_hi[pos] = (uint32_t)(it >> 32);
-            } else {
-                out[pos] = it;
-            }
+            out[s_gbase[d] + idx] = it;
         }
     }
 }
 
 // Stable LSD sort of n u64 items on `passes` 8-bit digits from bit `shift` (a -> b -> a ...).
-// split_last: the final pass writes low words to out_lo and high words to out_hi instead.
-// Returns through *result the buffer holding the sorted items (unused with split_last).
-static int radix_sort_reset(uint32_t n, int passes, Scratch s, cudaStream_t st) {
-    const uint32_t nb = div_up(n, OS_TILE);
-    GSR_CUDA_TRY(cudaMemsetAsync(s.sort_ctl, 0, (SORT_CTL_STATUS + (size_t)passes * 256 * nb) * sizeof(uint32_t), st));
-    return GSR_OK;
-}
-
-// have_hist: the digit histograms were already accumulated into the (reset) control block by the
-// producer of the items (instance emission), so the input is not read an extra time.
-static int radix_sort_onesweep(uint64_t* a, uint64_t* b, uint32_t n, int shift, int passes, Scratch s,
-                               bool split_last, uint32_t* out_lo, uint32_t* out_hi, uint64_t** result,
-                               bool have_hist, cudaStream_t st) {
+static int radix_sort_onesweep(uint64_t* a, uint64_t* b, uint32_t n, int shift, int passes, Scratch s, cudaStream_t st) {
     const uint32_t nb = div_up(n, OS_TILE);
     uint32_t* ctl = s.sort_ctl;
-    if (!have_hist) {
-    int rc = radix_sort_reset(n, passes, s, st);
-    if (rc) return rc;
+    GSR_CUDA_TRY(cudaMemsetAsync(ctl, 0, (SORT_CTL_STATUS + (size_t)passes * 256 * nb) * sizeof(uint32_t), st));
     const uint32_t hist_blocks = min(div_up(n, 512u), 148u * 8u);
     switch (passes) {
         case 1: GSR_LAUNCH(radix_hist_multi_kernel<1>, hist_blocks, 256, 0, st, a, n, shift, ctl + SORT_CTL_HIST); break;
@@ -356,204 +330,206 @@ static int radix_sort_onesweep(uint64_t* a, uint64_t* b, uint32_t n, int shift, 
         case 3: GSR_LAUNCH(radix_hist_multi_kernel<3>, hist_blocks, 256, 0, st, a, n, shift, ctl + SORT_CTL_HIST); break;
         default: GSR_LAUNCH(radix_hist_multi_kernel<4>, hist_blocks, 256, 0, st, a, n, shift, ctl + SORT_CTL_HIST); break;
     }
-    }
     GSR_LAUNCH(radix_bases_kernel, passes, 256, 0, st, ctl + SORT_CTL_HIST, ctl + SORT_CTL_BASE);
     for (int pass = 0; pass < passes; pass++) {
         uint32_t* status = ctl + SORT_CTL_STATUS + (size_t)pass * 256 * nb;
-        const bool split = split_last && pass == passes - 1;
-        if (split)
-            GSR_LAUNCH(onesweep_kernel<true>, nb, OS_THREADS, 0, st, a, n, shift + 8 * pass, ctl + SORT_CTL_BASE + pass * 256,
-                                                            status, ctl + SORT_CTL_TICKET + pass, nullptr, out_lo, out_hi);
-        else
-            GSR_LAUNCH(onesweep_kernel<false>, nb, OS_THREADS, 0, st, a, n, shift + 8 * pass, ctl + SORT_CTL_BASE + pass * 256,
-                                                             status, ctl + SORT_CTL_TICKET + pass, b, nullptr, nullptr);
+        GSR_LAUNCH(onesweep_kernel, nb, OS_THREADS, 0, st, a, n, shift + 8 * pass, ctl + SORT_CTL_BASE + pass * 256,
+                                                    status, ctl + SORT_CTL_TICKET + pass, b);
         uint64_t* tmp = a; a = b; b = tmp;
     }
-    if (result) *result = a;
     return GSR_OK;
 }
 
-// One LSD pass src -> dst on digit `shift`. split => final pass with split outputs.
-static int radix_pass(const uint64_t* src, uint64_t* dst, uint32_t n, int shift, Scratch s,
-                      bool split, uint32_t* out_lo, uint32_t* out_hi, cudaStream_t st) {
+// One LSD pass src -> dst on digit `shift` (3 kernels; only for n >= 2^30, where look-back counts do not fit).
+static int radix_pass(const uint64_t* src, uint64_t* dst, uint32_t n, int shift, Scratch s, cudaStream_t st) {
     const uint32_t nb = div_up(n, SORT_CHUNK);
     GSR_LAUNCH(radix_hist_kernel, nb, SORT_THREADS, 0, st, src, n, shift, s.hist, nb);
     GSR_LAUNCH(radix_rowscan_kernel, 256, 256, 0, st, s.hist, nb, s.digit_tot);
-    if (split)
-        GSR_LAUNCH(radix_scatter_kernel<true>, nb, SORT_THREADS, 0, st, src, n, shift, s.hist, nb, s.digit_tot,
-                                                                nullptr, out_lo, out_hi);
-    else
-        GSR_LAUNCH(radix_scatter_kernel<false>, nb, SORT_THREADS, 0, st, src, n, shift, s.hist, nb, s.digit_tot,
-                                                                 dst, nullptr, nullptr);
+    GSR_LAUNCH(radix_scatter_kernel, nb, SORT_THREADS, 0, st, src, n, shift, s.hist, nb, s.digit_tot, dst);
     return GSR_OK;
 }
 
-// ---------------------------------------------------------------- tile-count scan
-__device__ __forceinline__ uint32_t rect_tiles(uint2 r) {
-    uint32_t w = (r.y & 0xffffu) - (r.x & 0xffffu);
-    uint32_t h = (r.y >> 16) - (r.x >> 16);
-    return w * h;
+// ---------------------------------------------------------------- per-tile lists
+// Unit of work = (chunk of consecutive depth ranks, band of tile rows).  The band keeps a unit's
+// tile counters in shared memory (<= TB_MAX_CELLS tiles); at 1080p the whole image is one band.
+// Chunks cover the V visible Gaussians (they sort before the culled ones, whose keys are all-ones);
+// V is counted by the preprocess kernel.  A culled Gaussian's rectangle is empty, so a stray one
+// inside a chunk adds nothing.
+__device__ __forceinline__ void unit_ranks(const int32_t* counters, const TileBinPlan& pl, uint32_t chunk,
+                                           uint32_t& k0, uint32_t& k1) {
+    const unsigned long long V = (uint32_t)counters[CNT_VISIBLE];
+    k0 = (uint32_t)(V * chunk / pl.n_chunks);
+    k1 = (uint32_t)(V * (chunk + 1) / pl.n_chunks);
 }
 
-// Phase 1: tiles touched by the Gaussian at each depth rank -> offsets[] (raw counts)
-// and the per-block sums.
-__global__ void __launch_bounds__(SCAN_THREADS)
-scan_count_kernel(const uint64_t* __restrict__ sorted, const uint2* __restrict__ rects, uint32_t P,
-                  uint32_t* __restrict__ offsets, uint32_t* __restrict__ block_sums) {
-    __shared__ uint32_t s_w[8];
-    const uint32_t base = blockIdx.x * SCAN_CHUNK;
-    uint32_t sum = 0;
-#pragma unroll
-    for (int i = 0; i < SCAN_ITEMS; i++) {
-        uint32_t idx = base + i * SCAN_THREADS + threadIdx.x;
-        if (idx < P) {
-            uint32_t c = rect_tiles(rects[(uint32_t)sorted[idx]]);
-            offsets[idx] = c;
-            sum += c;
-        }
-    }
-    uint32_t total;
-    block_excl_scan_256(sum, s_w, &total);
-    if (threadIdx.x == 0) block_sums[blockIdx.x] = total;
+// Part of rectangle r inside tile rows [r0, r1): first local tile index, width, tile count (0 = outside).
+__device__ __forceinline__ void clip_rect(uint2 r, uint32_t r0, uint32_t r1, uint32_t& x0, uint32_t& x1,
+                                          uint32_t& ya, uint32_t& yb) {
+    x0 = r.x & 0xffffu; x1 = r.y & 0xffffu;
+    ya = max(r.x >> 16, r0); yb = min(r.y >> 16, r1);
 }
 
-// Phase 2: one block; exclusive scan of the block sums in place, total -> counters.
-__global__ void __launch_bounds__(256)
-scan_blocksums_kernel(uint32_t* __restrict__ block_sums, uint32_t nb, int32_t* __restrict__ counters) {
-    __shared__ uint32_t s_w[8];
-    unsigned long long carry = 0;
-    for (uint32_t b0 = 0; b0 < nb; b0 += 256) {
-        uint32_t b = b0 + threadIdx.x;
-        uint32_t v = b < nb ? block_sums[b] : 0u;
-        uint32_t total;
-        uint32_t ex = block_excl_scan_256(v, s_w, &total);
-        if (b < nb) block_sums[b] = (uint32_t)carry + ex;
-        carry += total;
-    }
-    if (threadIdx.x == 0) {
-        counters[0] = carry > 0x7fffffffull ? 0x7fffffff : (int32_t)carry;
-        counters[1] = carry > 0x7fffffffull ? 1 : 0;   // reference: int num_rendered (rasterizer_impl.cu:312)
-    }
-}
-
-// Phase 3: inclusive scan inside each block + block prefix, in place.
-__global__ void __launch_bounds__(SCAN_THREADS)
-scan_apply_kernel(uint32_t* __restrict__ offsets, uint32_t P, const uint32_t* __restrict__ block_sums) {
-    __shared__ uint32_t s_w[8];
-    const uint32_t base = blockIdx.x * SCAN_CHUNK + threadIdx.x * SCAN_ITEMS;
-    uint32_t v[SCAN_ITEMS];
-    uint32_t sum = 0;
-#pragma unroll
-    for (int i = 0; i < SCAN_ITEMS; i++) {
-        v[i] = (base + i < P) ? offsets[base + i] : 0u;
-        sum += v[i];
-    }
-    uint32_t run = block_excl_scan_256(sum, s_w, nullptr) + block_sums[blockIdx.x];
-#pragma unroll
-    for (int i = 0; i < SCAN_ITEMS; i++) {
-        run += v[i];
-        if (base + i < P) offsets[base + i] = run;
-    }
-}
-
-// ---------------------------------------------------------------- instance emission
-// duplicateWithKeys (rasterizer_impl.cu:78-126) in depth order; item = tile<<32 | id.
-// Warp-cooperative: a warp owns 32 consecutive depth ranks, whose instances occupy one contiguous
-// range of the output; lane j writes instance first + j, first + j + 32, ... (coalesced 8 B stores)
-// after locating its Gaussian among the warp's 32 inclusive offsets with a 5-step shuffle search.
-// The 8-bit digit histograms of the tile ids (what the following radix sort needs) are accumulated
-// on the way, so the instance list is not read again for them.
-constexpr int EMIT_THREADS = 256;
-constexpr int EMIT_ROUNDS = 4;                     // 1024 Gaussians per CTA
-
-template <int PASSES>
-__global__ void __launch_bounds__(EMIT_THREADS)
-emit_instances_kernel(const uint64_t* __restrict__ sorted, const uint2* __restrict__ rects,
-                      const uint32_t* __restrict__ offsets, uint32_t P, uint32_t grid_x,
-                      uint64_t* __restrict__ inst, uint32_t* __restrict__ ghist) {
-    __shared__ uint32_t s_hist[PASSES][256];
-#pragma unroll
-    for (int p = 0; p < PASSES; p++) s_hist[p][threadIdx.x] = 0;
+// Step 2a.  count[chunk][tile] = Gaussians of the chunk whose rectangle covers the tile: +-1 at the four
+// corners of every rectangle in a difference grid (order-free shared-memory adds), then a 2-D prefix sum.
+// The units of band 0 also write the rectangles in depth order (srects), so that the list-filling kernel
+// streams them instead of gathering by id.
+__global__ void __launch_bounds__(TB_COUNT_THREADS)
+tile_count_kernel(const uint64_t* __restrict__ sorted, const uint2* __restrict__ rects,
+                  const int32_t* __restrict__ counters, TileBinPlan pl,
+                  uint32_t* __restrict__ M, uint2* __restrict__ srects) {
+    __shared__ int32_t D[TB_COUNT_CELLS];
+    const uint32_t t = threadIdx.x, chunk = blockIdx.x, band = blockIdx.y;
+    const uint32_t r0 = band * pl.band_rows, r1 = min(pl.gy, r0 + pl.band_rows);
+    const uint32_t rows = r1 - r0, S = pl.stride, gx = pl.gx;
+    uint32_t k0, k1;
+    unit_ranks(counters, pl, chunk, k0, k1);
+    for (uint32_t i = t; i < (rows + 1) * S; i += TB_COUNT_THREADS) D[i] = 0;
     __syncthreads();
-    const uint32_t lane = threadIdx.x & 31u;
-    const uint32_t last_incl = offsets[P - 1];
-    for (int round = 0; round < EMIT_ROUNDS; round++) {
-        const uint32_t i = (blockIdx.x * EMIT_ROUNDS + round) * EMIT_THREADS + threadIdx.x;
-        uint32_t g = 0, x0 = 0, y0 = 0, w = 1, incl = last_incl, cnt = 0;
-        if (i < P) {
-            const uint64_t it = sorted[i];
-            incl = offsets[i];
-            if ((uint32_t)(it >> 32) != 0xFFFFFFFFu) {          // not culled
-                g = (uint32_t)it;
-                const uint2 r = rects[g];
-                x0 = r.x & 0xffffu; y0 = r.x >> 16;
-                w = (r.y & 0xffffu) - x0;
-                cnt = w * ((r.y >> 16) - y0);
-            }
-        }
-        const uint32_t excl = incl - cnt;
-        const uint32_t first = __shfl_sync(0xffffffffu, excl, 0);
-        const uint32_t total = __shfl_sync(0xffffffffu, incl, 31) - first;
-        const uint32_t xy = x0 | (y0 << 16);
-        for (uint32_t j = lane; j < ((total + 31u) & ~31u); j += 32) {      // uniform trip count: shuffles inside
-            const uint32_t target = first + j;
-            // L = number of lanes whose inclusive offset is <= target = owner of instance `target`
-            uint32_t L = 0;
-#pragma unroll
-            for (int step = 16; step > 0; step >>= 1) {
-                const uint32_t probe = __shfl_sync(0xffffffffu, incl, (L + step - 1) & 31);
-                if (L + step <= 32 && probe <= target) L += step;
-            }
-            const uint32_t src = L & 31;
-            const uint32_t o_excl = __shfl_sync(0xffffffffu, excl, src);
-            const uint32_t o_w = __shfl_sync(0xffffffffu, w, src);
-            const uint32_t o_xy = __shfl_sync(0xffffffffu, xy, src);
-            const uint32_t o_g = __shfl_sync(0xffffffffu, g, src);
-            if (j < total) {
-                const uint32_t local = target - o_excl;
-                const uint32_t ry = local / o_w, rx = local - ry * o_w;
-                const uint32_t tile = ((o_xy >> 16) + ry) * grid_x + (o_xy & 0xffffu) + rx;
-                inst[target] = ((uint64_t)tile << 32) | o_g;
-#pragma unroll
-                for (int p = 0; p < PASSES; p++) atomicAdd(&s_hist[p][(tile >> (8 * p)) & 255u], 1u);
-            }
+    for (uint32_t k = k0 + t; k < k1; k += TB_COUNT_THREADS) {
+        const uint2 r = rects[(uint32_t)sorted[k]];
+        if (band == 0) srects[k] = r;
+        uint32_t x0, x1, ya, yb;
+        clip_rect(r, r0, r1, x0, x1, ya, yb);
+        if (x1 > x0 && yb > ya) {
+            const uint32_t a = (ya - r0) * S, b = (yb - r0) * S;
+            atomicAdd(&D[a + x0], 1);
+            atomicAdd(&D[a + x1], -1);
+            atomicAdd(&D[b + x0], -1);
+            atomicAdd(&D[b + x1], 1);
         }
     }
     __syncthreads();
-#pragma unroll
-    for (int p = 0; p < PASSES; p++) {
-        const uint32_t c = s_hist[p][threadIdx.x];
-        if (c) atomicAdd(&ghist[p * 256 + threadIdx.x], c);
+    for (uint32_t r = t; r < rows; r += TB_COUNT_THREADS) {          // along x (S is odd: conflict-free)
+        int32_t run = 0;
+        for (uint32_t x = 0; x < gx; x++) { run += D[r * S + x]; D[r * S + x] = run; }
+    }
+    __syncthreads();
+    uint32_t* out = M + (size_t)chunk * pl.T + (size_t)r0 * gx;
+    for (uint32_t x = t; x < gx; x += TB_COUNT_THREADS) {            // along y, fused with the store
+        int32_t run = 0;
+        for (uint32_t r = 0; r < rows; r++) { run += D[r * S + x]; out[r * gx + x] = (uint32_t)run; }
     }
 }
 
-// identifyTileRanges (rasterizer_impl.cu:132-164) on the sorted tile ids; 4 instances per thread.
-__global__ void __launch_bounds__(256)
-tile_ranges_kernel(const uint32_t* __restrict__ tile_ids, uint32_t L, uint2* __restrict__ ranges) {
-    const uint32_t i0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
-    if (i0 >= L) return;
-    uint32_t v[4];
-    if (i0 + 3 < L) {
-        const uint4 q = *reinterpret_cast<const uint4*>(tile_ids + i0);
-        v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
-    } else {
-#pragma unroll
-        for (int k = 0; k < 4; k++) v[k] = i0 + k < L ? tile_ids[i0 + k] : 0u;
+// Step 2b.  Per tile: exclusive prefix of the counts over the chunks, in place, and the tile's total.
+// 32 tiles x TB_CP_GROUPS chunk groups per CTA; each thread sums its group, the group totals are combined
+// through shared memory, a second sweep writes the prefixes.
+constexpr int TB_CP_GROUPS = 8;
+__global__ void __launch_bounds__(32 * TB_CP_GROUPS)
+tile_chunk_prefix_kernel(uint32_t* __restrict__ M, TileBinPlan pl, uint32_t* __restrict__ totals) {
+    __shared__ uint32_t s_tot[TB_CP_GROUPS][32];
+    const uint32_t lane = threadIdx.x & 31u, grp = threadIdx.x >> 5;
+    const uint32_t t = blockIdx.x * 32 + lane, T = pl.T;
+    const uint32_t c0 = pl.n_chunks * grp / TB_CP_GROUPS, c1 = pl.n_chunks * (grp + 1) / TB_CP_GROUPS;
+    uint32_t sum = 0;
+    if (t < T) {
+#pragma unroll 8
+        for (uint32_t c = c0; c < c1; c++) sum += M[(size_t)c * T + t];
     }
-    uint32_t prev = i0 > 0 ? tile_ids[i0 - 1] : 0u;
+    s_tot[grp][lane] = sum;
+    __syncthreads();
+    uint32_t run = 0;
+    for (uint32_t g = 0; g < grp; g++) run += s_tot[g][lane];
+    if (t >= T) return;
+    for (uint32_t c = c0; c < c1; c += 8) {
+        uint32_t v[8];
 #pragma unroll
-    for (int k = 0; k < 4; k++) {
-        const uint32_t idx = i0 + k;
-        if (idx >= L) break;
-        const uint32_t cur = v[k];
-        if (idx == 0)
-            ranges[cur].x = 0;
-        else if (cur != prev) {
-            ranges[prev].y = idx;
-            ranges[cur].x = idx;
+        for (int j = 0; j < 8; j++) v[j] = c + j < c1 ? M[(size_t)(c + j) * T + t] : 0u;
+#pragma unroll
+        for (int j = 0; j < 8; j++)
+            if (c + j < c1) { M[(size_t)(c + j) * T + t] = run; run += v[j]; }
+    }
+    if (grp == TB_CP_GROUPS - 1) totals[t] = run;
+}
+
+// Step 2c.  One CTA: exclusive scan of the tile totals -> ranges (identifyTileRanges, rasterizer_impl.cu:
+// 132-164: [start, end) per tile, (0, 0) for a tile nobody touches -- the reference memsets and never writes it).
+constexpr int TB_SCAN_THREADS = 1024;
+__global__ void __launch_bounds__(TB_SCAN_THREADS)
+tile_ranges_kernel(const uint32_t* __restrict__ totals, uint32_t T, uint2* __restrict__ ranges) {
+    __shared__ uint32_t s_w[32];
+    const uint32_t t = threadIdx.x, lane = t & 31u, warp = t >> 5;
+    const uint32_t per = div_up(T, TB_SCAN_THREADS);
+    const uint32_t b0 = min(T, t * per), b1 = min(T, b0 + per);
+    uint32_t sum = 0;
+    for (uint32_t i = b0; i < b1; i++) sum += totals[i];
+    const uint32_t inc = warp_incl_scan(sum, lane);
+    if (lane == 31) s_w[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        const uint32_t w = s_w[lane];
+        s_w[lane] = warp_incl_scan(w, lane) - w;
+    }
+    __syncthreads();
+    uint32_t run = s_w[warp] + inc - sum;
+    for (uint32_t i = b0; i < b1; i++) {
+        const uint32_t c = totals[i];
+        ranges[i] = c ? make_uint2(run, run + c) : make_uint2(0u, 0u);
+        run += c;
+    }
+}
+
+// Step 3.  One warp per unit.  run[tile] = next free slot of the tile's list for this chunk.  32 Gaussians are
+// tested against the band at a time; the warp then takes the ones that intersect it one after the other, lanes =
+// tiles of the rectangle (row-major): slot = run[tile]++ , point_list[slot] = id.  Within one Gaussian all tiles
+// differ, and Gaussians are taken in depth order, so every list is filled in order without any ranking.
+__global__ void __launch_bounds__(32)
+tile_fill_kernel(const uint64_t* __restrict__ sorted, const uint2* __restrict__ srects,
+                 const int32_t* __restrict__ counters, TileBinPlan pl,
+                 const uint32_t* __restrict__ M, const uint2* __restrict__ ranges,
+                 uint32_t* __restrict__ point_list) {
+    __shared__ uint32_t run[TB_MAX_CELLS];
+    const uint32_t lane = threadIdx.x, chunk = blockIdx.x, band = blockIdx.y;
+    const uint32_t r0 = band * pl.band_rows, r1 = min(pl.gy, r0 + pl.band_rows);
+    const uint32_t gx = pl.gx, cells = (r1 - r0) * gx;
+    uint32_t k0, k1;
+    unit_ranks(counters, pl, chunk, k0, k1);
+    if (k0 >= k1) return;
+    {
+        const uint32_t* m = M + (size_t)chunk * pl.T + (size_t)r0 * gx;
+        const uint2* rg = ranges + (size_t)r0 * gx;
+        for (uint32_t i = lane; i < cells; i += 32) run[i] = rg[i].x + m[i];
+    }
+    __syncwarp();
+    // one batch of 32 Gaussians is fetched ahead of the one being walked
+    uint64_t item_n = k0 + lane < k1 ? sorted[k0 + lane] : 0ull;
+    uint2 rect_n = k0 + lane < k1 ? srects[k0 + lane] : make_uint2(0u, 0u);
+    for (uint32_t k = k0; k < k1; k += 32) {
+        const uint32_t id = (uint32_t)item_n;
+        const uint2 r = rect_n;
+        const uint32_t kn = k + 32 + lane;
+        item_n = kn < k1 ? sorted[kn] : 0ull;
+        rect_n = kn < k1 ? srects[kn] : make_uint2(0u, 0u);
+        uint32_t x0, x1, ya, yb;
+        clip_rect(r, r0, r1, x0, x1, ya, yb);
+        uint32_t n = 0, w = 0, first = 0, magic = 0;
+        if (x1 > x0 && yb > ya) {
+            w = x1 - x0;
+            n = w * (yb - ya);
+            first = (ya - r0) * gx + x0;
+            magic = w > 1 ? 0xFFFFFFFFu / w + 1u : 0u;      // ceil(2^32 / w): l / w == umulhi(l, magic) while l * w < 2^32
         }
-        if (idx == L - 1) ranges[cur].y = L;
-        prev = cur;
+        uint32_t bits = __ballot_sync(0xffffffffu, n != 0);
+        while (bits != 0) {
+            const int b = __ffs((int)bits) - 1;
+            bits &= bits - 1;
+            const uint32_t g_id = __shfl_sync(0xffffffffu, id, b);
+            const uint32_t g_n = __shfl_sync(0xffffffffu, n, b);
+            const uint32_t g_w = __shfl_sync(0xffffffffu, w, b);
+            const uint32_t g_first = __shfl_sync(0xffffffffu, first, b);
+            const uint32_t g_magic = __shfl_sync(0xffffffffu, magic, b);
+            for (uint32_t base = 0; base < g_n; base += 32) {
+                const uint32_t l = base + lane;
+                if (l < g_n) {
+                    const uint32_t ry = g_w > 1 ? __umulhi(l, g_magic) : l;
+                    const uint32_t cell = g_first + ry * gx + (l - ry * g_w);
+                    const uint32_t slot = run[cell];
+                    run[cell] = slot + 1;
+                    point_list[slot] = g_id;
+                }
+                __syncwarp();            // the next Gaussian's lanes may read the counters this one wrote
+            }
+        }
     }
 }
 
@@ -569,20 +545,26 @@ __global__ void rebuild_keys_kernel(const uint2* __restrict__ ranges, uint32_t T
 }
 
 // ---------------------------------------------------------------- launchers
-int launch_depth_order_and_scan(const GsrParams& p, GeomState g, Scratch s, int32_t* num_rendered_host,
-                                cudaStream_t st) {
+// Stage 1 of the forward after preprocess: num_rendered to the host, depth order, per-tile counts and ranges.
+int launch_depth_order_and_count(const GsrParams& p, GeomState g, ImgState im, Scratch s, int32_t* num_rendered_host,
+                                 void* num_rendered_event, cudaStream_t st) {
     const uint32_t P = (uint32_t)p.P;
+    // {num_rendered (64-bit), V} were accumulated by the preprocess kernel: the host can size `bin` while the
+    // device is still ordering (the reference blocks on this copy after its scan, rasterizer_impl.cu:313)
+    if (num_rendered_host)
+        GSR_CUDA_TRY(cudaMemcpyAsync(num_rendered_host, s.counters, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    if (num_rendered_event) GSR_CUDA_TRY(cudaEventRecord((cudaEvent_t)num_rendered_event, st));
     // depth_a holds depth_bits<<32 | id (written by preprocess). 4 stable LSD passes.
     uint64_t* a = s.depth_a;
     uint64_t* b = s.depth_b;
     {
         StageTimer tm(GSR_STAGE_DEPTH_SORT, st);
         if (P < OS_MAX_N) {
-            int rc = radix_sort_onesweep(a, b, P, 32, 4, s, false, nullptr, nullptr, nullptr, false, st);
+            int rc = radix_sort_onesweep(a, b, P, 32, 4, s, st);
             if (rc) return rc;
         } else {
             for (int pass = 0; pass < 4; pass++) {
-                radix_pass(a, b, P, 32 + 8 * pass, s, false, nullptr, nullptr, st);
+                radix_pass(a, b, P, 32 + 8 * pass, s, st);
                 uint64_t* tmp = a; a = b; b = tmp;
             }
         }
@@ -590,74 +572,27 @@ int launch_depth_order_and_scan(const GsrParams& p, GeomState g, Scratch s, int3
     int rc = check_stage("depth sort", p.debug, st);
     if (rc) return rc;
     // a == s.depth_a again (even number of passes)
+    const TileBinPlan pl = tile_bin_plan(p.P, p.W, p.H);
     {
-        StageTimer tm(GSR_STAGE_SCAN, st);
-        const uint32_t nb = div_up(P, SCAN_CHUNK);
-        GSR_LAUNCH(scan_count_kernel, nb, SCAN_THREADS, 0, st, a, s.rects, P, s.offsets, s.scan_blocks);
-        GSR_LAUNCH(scan_blocksums_kernel, 1, 256, 0, st, s.scan_blocks, nb, s.counters);
-        GSR_LAUNCH(scan_apply_kernel, nb, SCAN_THREADS, 0, st, s.offsets, P, s.scan_blocks);
+        StageTimer tm(GSR_STAGE_TILE_COUNT, st);
+        GSR_LAUNCH(tile_count_kernel, dim3(pl.n_chunks, pl.n_bands), TB_COUNT_THREADS, 0, st, a, s.rects, s.counters, pl,
+                                                      s.tile_chunk, s.srects);
+        GSR_LAUNCH(tile_chunk_prefix_kernel, div_up(pl.T, 32), 32 * TB_CP_GROUPS, 0, st, s.tile_chunk, pl, s.tile_total);
+        GSR_LAUNCH(tile_ranges_kernel, 1, TB_SCAN_THREADS, 0, st, s.tile_total, pl.T, im.ranges);
     }
-    rc = check_stage("tile-count scan", p.debug, st);
-    if (rc) return rc;
-    if (num_rendered_host)
-        GSR_CUDA_TRY(cudaMemcpyAsync(num_rendered_host, s.counters, 2 * sizeof(int32_t),
-                                     cudaMemcpyDeviceToHost, st));
-    return GSR_OK;
+    return check_stage("tile counts", p.debug, st);
 }
 
-int launch_binning(const GsrParams& p, GeomState g, ImgState im, BinState b, Scratch s, int64_t R,
-                   cudaStream_t st) {
-    const uint32_t P = (uint32_t)p.P;
-    const uint32_t gx = div_up(p.W, TILE_X), gy = div_up(p.H, TILE_Y);
-    const uint32_t T = gx * gy;
-    GSR_CUDA_TRY(cudaMemsetAsync(im.ranges, 0, (size_t)T * sizeof(uint2), st));   // rasterizer_impl.cu:342
+// Stage 2 of the forward before the blend: fill point_list.
+int launch_tile_lists(const GsrParams& p, GeomState g, ImgState im, BinState b, Scratch s, int64_t R, cudaStream_t st) {
     if (R <= 0) return GSR_OK;
-    const uint32_t n = (uint32_t)R;
-    // reference sorts bits [0, 32+getHigherMsb(T)) (rasterizer_impl.cu:332-340); the low 32
-    // (depth) are already in order, so only the tile bits remain.
-    const int bits = (int)higher_msb(T);
-    const int passes = (bits + 7) / 8;
-    const bool fused_hist = n < OS_MAX_N;
-    int rc = GSR_OK;
+    const TileBinPlan pl = tile_bin_plan(p.P, p.W, p.H);
     {
-        StageTimer tm(GSR_STAGE_EMIT, st);
-        const uint32_t eb = div_up(P, EMIT_THREADS * EMIT_ROUNDS);
-        uint32_t* gh = s.sort_ctl + SORT_CTL_HIST;
-        if (fused_hist) {
-            rc = radix_sort_reset(n, passes, s, st);
-            if (rc) return rc;
-        }
-        switch (fused_hist ? passes : 0) {
-            case 1: GSR_LAUNCH(emit_instances_kernel<1>, eb, EMIT_THREADS, 0, st, s.depth_a, s.rects, s.offsets, P, gx, s.inst_a, gh); break;
-            case 2: GSR_LAUNCH(emit_instances_kernel<2>, eb, EMIT_THREADS, 0, st, s.depth_a, s.rects, s.offsets, P, gx, s.inst_a, gh); break;
-            case 3: GSR_LAUNCH(emit_instances_kernel<3>, eb, EMIT_THREADS, 0, st, s.depth_a, s.rects, s.offsets, P, gx, s.inst_a, gh); break;
-            default: GSR_LAUNCH(emit_instances_kernel<4>, eb, EMIT_THREADS, 0, st, s.depth_a, s.rects, s.offsets, P, gx, s.inst_a,
-                                s.hist /* unused scratch */); break;
-        }
+        StageTimer tm(GSR_STAGE_TILE_FILL, st);
+        GSR_LAUNCH(tile_fill_kernel, dim3(pl.n_chunks, pl.n_bands), 32, 0, st, s.depth_a, s.srects, s.counters, pl,
+                                                     s.tile_chunk, im.ranges, b.point_list);
     }
-    rc = check_stage("emit instances", p.debug, st);
-    if (rc) return rc;
-    uint64_t* a = s.inst_a;
-    uint64_t* c = s.inst_b;
-    {
-        StageTimer tm(GSR_STAGE_TILE_SORT, st);
-        if (fused_hist) {
-            rc = radix_sort_onesweep(a, c, n, 32, passes, s, true, b.point_list, s.tile_ids, nullptr, true, st);
-            if (rc) return rc;
-        } else
-        for (int pass = 0; pass < passes; pass++) {
-            const bool last = pass == passes - 1;
-            radix_pass(a, c, n, 32 + 8 * pass, s, last, b.point_list, s.tile_ids, st);
-            uint64_t* tmp = a; a = c; c = tmp;
-        }
-    }
-    rc = check_stage("tile sort", p.debug, st);
-    if (rc) return rc;
-    {
-        StageTimer tm(GSR_STAGE_TILE_RANGES, st);
-        GSR_LAUNCH(tile_ranges_kernel, div_up(n, 1024), 256, 0, st, s.tile_ids, n, im.ranges);
-    }
-    return check_stage("tile ranges", p.debug, st);
+    return check_stage("tile lists", p.debug, st);
 }
 
 int launch_rebuild_keys(const GsrParams& p, GeomState g, ImgState im, BinState b, int64_t R,

@@ -3,7 +3,7 @@
 // Data layout in HBM:
 //   GsRecord[P]   64 B per Gaussian, written by preprocess, gathered by the
 //                 render kernels with one 48 B (fwd) / 64 B (bwd) bulk copy.
-//   rects[P]      packed tile rectangle (4 x u16), consumed by instance emission.
+//   rects[P]      packed tile rectangle (4 x u16), consumed by the tile-list construction.
 //   point_list[R] Gaussian ids ordered by (tile, depth, id)  == the reference's
 //                 sorted value list (rasterizer_impl.cu:335-340).
 //   ranges[T]     per-tile [start,end) into point_list (rasterizer_impl.cu:132-164).
@@ -105,9 +105,6 @@ struct BinState {           // persists forward -> backward
 constexpr int SORT_THREADS = 256;
 constexpr int SORT_ITEMS = 16;
 constexpr int SORT_CHUNK = SORT_THREADS * SORT_ITEMS;   // 4096 items per block
-constexpr int SCAN_THREADS = 256;
-constexpr int SCAN_ITEMS = 8;
-constexpr int SCAN_CHUNK = SCAN_THREADS * SCAN_ITEMS;   // 2048 items per block
 
 // Control block of one radix sort (up to 4 digit passes):
 //   [0, 1024)            digit histograms of all passes (256 each)
@@ -118,46 +115,78 @@ constexpr int SORT_MAX_PASSES = 4;
 constexpr size_t SORT_CTL_HIST = 0, SORT_CTL_BASE = 1024, SORT_CTL_TICKET = 2048, SORT_CTL_STATUS = 2112;
 inline size_t sort_ctl_words(size_t nb) { return SORT_CTL_STATUS + (size_t)SORT_MAX_PASSES * 256 * nb; }
 
+// Per-tile list construction (binning.cu): a unit of work is (chunk of depth ranks, band of tile rows).
+#ifndef GSR_TB_MAX_CELLS
+#define GSR_TB_MAX_CELLS 8192                            // (tests lower it to reach several bands at small sizes)
+#endif
+constexpr int TB_MAX_CELLS = GSR_TB_MAX_CELLS;           // tile counters of one unit in shared memory (32 KB)
+constexpr int TB_MAX_BAND_ROWS = 512;
+constexpr int TB_MAX_GX = 2048;                          // widest tile grid (32 768 px)
+constexpr int TB_COUNT_CELLS = 10304;                    // difference grid: ((gx + 1) | 1) x (band_rows + 1) <= this
+constexpr int TB_COUNT_THREADS = 256;
+constexpr int TB_TARGET_UNITS = 888;                     // 148 SMs x 6 resident single-warp CTAs of the fill kernel
+constexpr int TB_MIN_CHUNK = 64;                         // Gaussians
+
+struct TileBinPlan { uint32_t gx, gy, T, band_rows, n_bands, n_chunks, stride; };
+inline TileBinPlan tile_bin_plan(int P, int W, int H) {
+    TileBinPlan pl;
+    pl.gx = (uint32_t)(W + TILE_X - 1) / TILE_X;
+    pl.gy = (uint32_t)(H + TILE_Y - 1) / TILE_Y;
+    pl.T = pl.gx * pl.gy;
+    uint32_t rows = (uint32_t)TB_MAX_CELLS / (pl.gx ? pl.gx : 1u);
+    if (rows < 1) rows = 1;
+    if (rows > (uint32_t)TB_MAX_BAND_ROWS) rows = TB_MAX_BAND_ROWS;
+    if (rows > pl.gy) rows = pl.gy ? pl.gy : 1u;
+    pl.band_rows = rows;
+    pl.n_bands = (pl.gy + rows - 1) / rows;
+    pl.stride = (pl.gx + 1) | 1u;
+    uint32_t chunks = (uint32_t)TB_TARGET_UNITS / (pl.n_bands ? pl.n_bands : 1u);
+    const uint32_t most = (uint32_t)(P > 0 ? P : 1) / TB_MIN_CHUNK;
+    if (chunks > most) chunks = most;
+    if (chunks < 1) chunks = 1;
+    pl.n_chunks = chunks;
+    return pl;
+}
+
+// device counters (int32[8]): [0..1] num_rendered as one 64-bit sum, [2] visible Gaussians (both accumulated by
+// the preprocess kernel)
+constexpr int CNT_RENDERED = 0, CNT_VISIBLE = 2;
+
 // band_ctl layout (u32 words): per-band counts, exclusive offsets, fill cursors, exclusive upper tile row
 constexpr int MAX_BANDS = 16;
 constexpr int BAND_CNT = 0, BAND_OFF = 16, BAND_CUR = 32, BAND_HI = 48, BAND_CTL_WORDS = 64;
 
-struct Scratch {            // only live inside one forward or backward call
+struct Scratch {            // only live inside one forward or backward call; does not depend on num_rendered
     // forward
     uint2*    rects;        // P   packed rect {min.x | min.y<<16, max.x | max.y<<16}
-    uint64_t* depth_a;      // P   depth_bits<<32 | id   (ping)
+    uint64_t* depth_a;      // P   depth_bits<<32 | id   (ping; holds the depth order after the sort)
     uint64_t* depth_b;      // P   (pong)
-    uint32_t* offsets;      // P   inclusive scan of tiles_touched in depth order
-    uint32_t* scan_blocks;  // ceil(P / SCAN_CHUNK) + 1
+    uint2*    srects;       // P   rectangles in depth order
     uint32_t* sort_ctl;     // onesweep control words, see SORT_CTL_* (zeroed per sort)
-    uint32_t* hist;         // 256 * max(blocks(P), blocks(R))   (legacy 3-kernel pass, n >= 2^30)
+    uint32_t* hist;         // 256 * blocks(P)   (3-kernel radix pass, P >= 2^30)
     uint32_t* digit_tot;    // 256
-    uint64_t* inst_a;       // R   tile<<32 | id (ping)
-    uint64_t* inst_b;       // R   (pong)
-    uint32_t* tile_ids;     // R   sorted tile id per instance
-    int32_t*  counters;     // 8   device-side {R, overflow, ...}
+    uint32_t* tile_chunk;   // n_chunks * T   per (chunk, tile): count, then first slot relative to the tile's start
+    uint32_t* tile_total;   // T
+    int32_t*  counters;     // 8   see CNT_*
     // backward
     float*    acc;          // P * ACC_FLOATS
     uint32_t* band_list;    // P   visible Gaussian ids grouped by tile-row band (multimem mode)
     uint32_t* band_ctl;     // BAND_CTL_WORDS: counts, offsets, cursors, band limits
-    static Scratch carve(void* chunk, size_t P, size_t R, size_t* bytes) {
+    static Scratch carve(void* chunk, size_t P, int W, int H, size_t* bytes) {
         Carver c(chunk); Scratch s;
-        size_t Rn = R > 0 ? R : 1;
         size_t Pn = P > 0 ? P : 1;
-        size_t nb = (Pn > Rn ? Pn : Rn) / SORT_CHUNK + 2;
+        size_t nb = Pn / SORT_CHUNK + 2;
+        const TileBinPlan pl = tile_bin_plan((int)(Pn > 0x7fffffff ? 0x7fffffff : Pn), W, H);
         s.counters = c.take<int32_t>(8);
         s.rects = c.take<uint2>(Pn);
         s.depth_a = c.take<uint64_t>(Pn);
         s.depth_b = c.take<uint64_t>(Pn);
-        s.offsets = c.take<uint32_t>(Pn);
-        s.scan_blocks = c.take<uint32_t>(Pn / SCAN_CHUNK + 2);
+        s.srects = c.take<uint2>(Pn);
         s.sort_ctl = c.take<uint32_t>(sort_ctl_words(nb));
         s.hist = c.take<uint32_t>(256 * nb);
         s.digit_tot = c.take<uint32_t>(256);
-        s.inst_a = c.take<uint64_t>(Rn);
-        s.inst_b = c.take<uint64_t>(Rn);
-        s.tile_ids = c.take<uint32_t>(Rn);
-        // the backward accumulator aliases the forward instance buffers when it fits
+        s.tile_chunk = c.take<uint32_t>((size_t)pl.n_chunks * pl.T);
+        s.tile_total = c.take<uint32_t>(pl.T);
         s.acc = c.take<float>(Pn * ACC_FLOATS);
         s.band_list = c.take<uint32_t>(Pn);
         s.band_ctl = c.take<uint32_t>(BAND_CTL_WORDS);
@@ -206,8 +235,9 @@ struct StageTimer {     // brackets a launcher's work with events when profiling
 // ---- stage launchers (defined in the per-stage .cu files) ------------------
 int launch_preprocess(const GsrParams& p, GeomState g, Scratch s, int32_t* radii, cudaStream_t st);
 int launch_mark_visible(int P, const float* means, const float* view, uint8_t* present, cudaStream_t st);
-int launch_depth_order_and_scan(const GsrParams& p, GeomState g, Scratch s, int32_t* num_rendered_host, cudaStream_t st);
-int launch_binning(const GsrParams& p, GeomState g, ImgState im, BinState b, Scratch s, int64_t R, cudaStream_t st);
+int launch_depth_order_and_count(const GsrParams& p, GeomState g, ImgState im, Scratch s, int32_t* num_rendered_host,
+                                 void* num_rendered_event, cudaStream_t st);
+int launch_tile_lists(const GsrParams& p, GeomState g, ImgState im, BinState b, Scratch s, int64_t R, cudaStream_t st);
 int launch_render_forward(const GsrParams& p, GeomState g, ImgState im, BinState b,
                           float* out_color, float* out_invdepth, cudaStream_t st);
 int launch_render_backward(const GsrParams& p, GeomState g, ImgState im, BinState b, Scratch s,

@@ -177,7 +177,7 @@ extern "C" int gsr_exchange_expand(const GsrParams* p, int32_t world, float* rec
         return GSR_ERR_INVALID_ARG;
     }
     const bool bulk = dL_dsh && p->M == 16 && !misaligned(dL_dsh) && !misaligned(dL_dsh_dc);
-    StageTimer tm(GSR_STAGE_PREPROCESS_BWD, st);      // accounted with the per-Gaussian backward
+    StageTimer tm(GSR_STAGE_EXCHANGE, st);
 #define XE_LAUNCH(B) GSR_LAUNCH(exchange_expand_kernel<B>, blocks, XE_THREADS, 0, st, p->P, p->D, p->M, (int)world, \
                                 p->means3D, reinterpret_cast<float4*>(records), reinterpret_cast<float4*>(rgb), \
                                 reinterpret_cast<const float4*>(campos), dL_dmeans3D, dL_dopacity, dL_dsh, dL_dscales, \

@@ -52,9 +52,12 @@ __device__ __forceinline__ float sh_channel(const float* lo, const float* sh, in
 __global__ void __launch_bounds__(PRE_THREADS)
 preprocess_fwd_kernel(GsrParams p, float focal_x, float focal_y, int gx, int gy,
                       GsRecord* __restrict__ rec, uint2* __restrict__ rects,
-                      uint64_t* __restrict__ depth_keys, int32_t* __restrict__ radii) {
+                      uint64_t* __restrict__ depth_keys, int32_t* __restrict__ radii,
+                      int32_t* __restrict__ counters) {
     __shared__ __align__(16) float sh_smem[PRE_WARPS][32 * SH_ROW_PAD];
     __shared__ float s_view[16], s_proj[16], s_cam[3];
+    __shared__ uint32_t s_visible, s_tiles;
+    if (threadIdx.x == 0) { s_visible = 0; s_tiles = 0; }
     if (threadIdx.x < 16) {
         s_view[threadIdx.x] = p.viewmatrix[threadIdx.x];
         s_proj[threadIdx.x] = p.projmatrix[threadIdx.x];
@@ -205,20 +208,37 @@ preprocess_fwd_kernel(GsrParams p, float focal_x, float focal_y, int gx, int gy,
         }
     }
 
-    if (!in_range) return;
     const int tiles = visible ? (int)((maxy - miny) * (maxx - minx)) : 0;
-    radii[idx] = visible ? (int)my_radius : 0;
-    // invisible Gaussians sort behind every visible one and emit nothing
-    depth_keys[idx] = ((uint64_t)(visible ? __float_as_uint(depth) : 0xFFFFFFFFu) << 32) | (uint32_t)idx;
-    rects[idx] = visible ? make_uint2(minx | (miny << 16), maxx | (maxy << 16)) : make_uint2(0u, 0u);
-    if (visible) {
-        GsRecord r;
-        r.q0 = make_float4(pix.x, pix.y, conic.x, conic.y);
-        r.q1 = make_float4(conic.z, opacity_aa, rgb[0], rgb[1]);
-        const float2 ext = cull_extent(conic.x, conic.y, conic.z, opacity_aa);     // render_common.cuh
-        r.q2 = make_float4(rgb[2], 1.f / depth, ext.x, ext.y);
-        r.q3 = make_float4(__int_as_float(clamped_bits), __int_as_float(tiles), depth, __int_as_float((int)my_radius));
-        rec[idx] = r;
+    if (in_range) {
+        radii[idx] = visible ? (int)my_radius : 0;
+        // invisible Gaussians sort behind every visible one and have an empty rectangle
+        depth_keys[idx] = ((uint64_t)(visible ? __float_as_uint(depth) : 0xFFFFFFFFu) << 32) | (uint32_t)idx;
+        rects[idx] = visible ? make_uint2(minx | (miny << 16), maxx | (maxy << 16)) : make_uint2(0u, 0u);
+        if (visible) {
+            GsRecord r;
+            r.q0 = make_float4(pix.x, pix.y, conic.x, conic.y);
+            r.q1 = make_float4(conic.z, opacity_aa, rgb[0], rgb[1]);
+            const float2 ext = cull_extent(conic.x, conic.y, conic.z, opacity_aa);     // render_common.cuh
+            r.q2 = make_float4(rgb[2], 1.f / depth, ext.x, ext.y);
+            r.q3 = make_float4(__int_as_float(clamped_bits), __int_as_float(tiles), depth, __int_as_float((int)my_radius));
+            rec[idx] = r;
+        }
+    }
+    // num_rendered (the reference's InclusiveSum total, rasterizer_impl.cu:309-313) and the number of visible
+    // Gaussians, one pair of global adds per CTA (a CTA's tiles fit 32 bits: 128 x 65535 x 2048 does not, but the
+    // sum is only meaningful below 2^31 and the 64-bit total still flags the overflow)
+    const unsigned vis = __ballot_sync(0xffffffffu, visible);
+    uint32_t tsum = (uint32_t)tiles;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) tsum += __shfl_xor_sync(0xffffffffu, tsum, o);
+    if (lane == 0 && vis != 0) {
+        atomicAdd(&s_visible, (uint32_t)__popc(vis));
+        atomicAdd(&s_tiles, tsum);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && s_visible != 0) {
+        atomicAdd(reinterpret_cast<unsigned long long*>(counters + CNT_RENDERED), (unsigned long long)s_tiles);
+        atomicAdd(reinterpret_cast<uint32_t*>(counters + CNT_VISIBLE), s_visible);
     }
 }
 
@@ -237,8 +257,9 @@ int launch_preprocess(const GsrParams& p, GeomState g, Scratch s, int32_t* radii
     const int gx = (p.W + TILE_X - 1) / TILE_X, gy = (p.H + TILE_Y - 1) / TILE_Y;
     const int blocks = (p.P + PRE_THREADS - 1) / PRE_THREADS;
     StageTimer tm(GSR_STAGE_PREPROCESS, st);
+    GSR_CUDA_TRY(cudaMemsetAsync(s.counters, 0, 8 * sizeof(int32_t), st));
     GSR_LAUNCH(preprocess_fwd_kernel, blocks, PRE_THREADS, 0, st, p, focal_x, focal_y, gx, gy, g.rec, s.rects,
-                                                          s.depth_a, radii);
+                                                          s.depth_a, radii, s.counters);
     return check_stage("preprocess", p.debug, st);
 }
 

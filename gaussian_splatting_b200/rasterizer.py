@@ -54,6 +54,9 @@ class _DeviceWorkspace:
         self.device = device
         self.scratch = torch.empty(0, dtype=torch.uint8, device=device)
         self.pinned = torch.zeros(2, dtype=torch.int32).pin_memory()
+        # recorded by stage 1 right after the copy into `pinned`; the host waits on it, not on the stream
+        self.counted = torch.cuda.Event()
+        self.counted.record(torch.cuda.current_stream(device))     # materialises the cudaEvent_t handle
         self.last_R = 0
         self.regrows = 0
 
@@ -69,6 +72,7 @@ class _DeviceWorkspace:
 
 
 _workspaces = {}
+_MAX_WORKSPACES = 8        # arenas of streams that went away are dropped, least recently used first
 
 
 def _workspace(device):
@@ -76,9 +80,14 @@ def _workspace(device):
     # share scratch; calls on one stream are ordered
     index = device.index if device.index is not None else torch.cuda.current_device()
     key = (device.type, index, torch.cuda.current_stream(index).cuda_stream)
-    ws = _workspaces.get(key)
+    ws = _workspaces.pop(key, None)
     if ws is None:
-        ws = _workspaces[key] = _DeviceWorkspace(device)
+        ws = _DeviceWorkspace(device)
+        while len(_workspaces) >= _MAX_WORKSPACES:
+            # a short-lived stream must not pin an arena for the life of the process; the tensor is returned to
+            # the caching allocator, which keeps it alive until the work queued on it has run
+            _workspaces.pop(next(iter(_workspaces)))
+    _workspaces[key] = ws                                # most recently used last
     return ws
 
 
@@ -201,27 +210,25 @@ def _forward_native(rs, means3D, sh, colors_precomp, opacities, scales, rotation
         stream = torch.cuda.current_stream(device)
         geom = torch.empty(lib.gsr_geom_bytes(P), dtype=torch.uint8, device=device)
         img = torch.empty(lib.gsr_img_bytes(W, H), dtype=torch.uint8, device=device)
-        # speculate the instance count from the previous frame so the arena rarely regrows
-        R_guess = max(int(ws.last_R * 1.1), 4 * P)
-        ws.ensure(lib.gsr_scratch_bytes(P, W, H, R_guess))
+        ws.ensure(lib.gsr_scratch_bytes(P, W, H, 0))        # no part of the arena depends on num_rendered
 
         buf = GsrBuffers()
         buf.geom, buf.geom_bytes = geom.data_ptr(), geom.numel()
         buf.img, buf.img_bytes = img.data_ptr(), img.numel()
         buf.scratch, buf.scratch_bytes = ws.scratch.data_ptr(), ws.scratch.numel()
         buf.num_rendered_host = ws.pinned.data_ptr()
+        buf.num_rendered_event = ws.counted.cuda_event
         out = GsrForwardOut(color.data_ptr(), invdepth.data_ptr(), radii.data_ptr())
 
         _lib.check(lib.gsr_forward_stage1(C.byref(p), C.byref(buf), C.byref(out), stream.cuda_stream))
-        stream.synchronize()                         # the one host sync of the path (rasterizer_impl.cu:313)
-        R, overflow = int(ws.pinned[0]), int(ws.pinned[1])
-        if overflow:
+        # The one host wait of the path (the reference blocks in cudaMemcpy, rasterizer_impl.cu:313).  The count
+        # is ready as soon as the preprocess kernel has run: the depth sort and the tile counting go on while the
+        # host sizes `bin` and enqueues stage 2.
+        ws.counted.synchronize()
+        R, R_hi = int(ws.pinned[0]), int(ws.pinned[1])
+        if R_hi != 0 or R < 0:
             raise RuntimeError("num_rendered exceeds int32 (the reference stores it in an int)")
         ws.last_R = R
-        need = lib.gsr_scratch_bytes(P, W, H, R)
-        if ws.scratch.numel() < need:
-            ws.ensure(need, keep_prefix=lib.gsr_scratch_bytes(P, W, H, 0))
-            buf.scratch, buf.scratch_bytes = ws.scratch.data_ptr(), ws.scratch.numel()
         binb = torch.empty(lib.gsr_bin_bytes(R), dtype=torch.uint8, device=device)
         buf.bin, buf.bin_bytes = binb.data_ptr(), binb.numel()
         _lib.check(lib.gsr_forward_stage2(C.byref(p), C.byref(buf), C.byref(out), R, stream.cuda_stream))

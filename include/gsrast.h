@@ -93,7 +93,12 @@ typedef struct GsrBuffers {
     void*  img;     size_t img_bytes;      /* >= gsr_img_bytes(W,H) */
     void*  bin;     size_t bin_bytes;      /* >= gsr_bin_bytes(R) */
     void*  scratch; size_t scratch_bytes;  /* >= gsr_scratch_bytes(P,W,H,R) */
-    int32_t* num_rendered_host;            /* pinned host int32[2]: {R, overflow flag} */
+    int32_t* num_rendered_host;            /* pinned host int32[2]: the 64-bit instance count as {low word, high word};
+                                            * it overflows the reference's int (rasterizer_impl.cu:312) when
+                                            * [1] != 0 || [0] < 0 */
+    void*    num_rendered_event;           /* optional cudaEvent_t recorded by stage 1 right after the copy into
+                                            * num_rendered_host: waiting on it (instead of the stream) lets the host
+                                            * size `bin` while the device is still ordering the Gaussians */
 } GsrBuffers;
 
 typedef struct GsrForwardOut {
@@ -146,16 +151,19 @@ size_t gsr_bin_bytes(int64_t R);
 size_t gsr_scratch_bytes(int32_t P, int32_t W, int32_t H, int64_t R);
 
 /* Forward, stage 1: preprocess (projection, EWA + antialiasing, SH->RGB, tile
- * rects), stable depth ordering and the tile-count scan.  Enqueues an async
- * copy of {num_rendered, overflow} into buf->num_rendered_host; the caller
- * waits for the stream (or an event) before reading it and before stage 2.
- * Replaces rasterizer_impl.cu:279-313. */
+ * rects, num_rendered), then stable depth ordering, per-tile counts and tile
+ * ranges.  The async copy of num_rendered into buf->num_rendered_host is
+ * enqueued right after the preprocess kernel (and buf->num_rendered_event
+ * recorded, when given); the caller waits for that event or for the stream
+ * before reading it and before stage 2.  Needs buf->img (the ranges live
+ * there).  Replaces rasterizer_impl.cu:279-313 and 342-350. */
 int gsr_forward_stage1(const GsrParams* p, const GsrBuffers* buf,
                        const GsrForwardOut* out, void* stream);
 
-/* Forward, stage 2: instance emission, stable tile ordering, tile ranges and
- * alpha blending.  R must be the value produced by stage 1; buf->bin must hold
- * gsr_bin_bytes(R).  Replaces rasterizer_impl.cu:315-368. */
+/* Forward, stage 2: fills the per-tile, depth-ordered Gaussian lists
+ * (point_list == the reference's sorted value list) and blends.  R must be
+ * the value produced by stage 1; buf->bin must hold gsr_bin_bytes(R).
+ * Replaces rasterizer_impl.cu:315-340 and 352-368. */
 int gsr_forward_stage2(const GsrParams* p, const GsrBuffers* buf,
                        const GsrForwardOut* out, int64_t R, void* stream);
 
@@ -337,6 +345,12 @@ int gsr_debug_state_ptrs(const GsrParams* p, const GsrBuffers* buf, int64_t R,
 
 #define GSR_RECORD_FLOATS 16
 
+/* Measurement hook (no counterpart in the reference): launches `blocks` CTAs of 256 threads that do nothing but
+ * 8 independent scalar FFMA chains for 4*iters steps each; *flops gets the floating-point operations of the launch.
+ * The caller times it with events on `stream`: the FP32 rate the blend kernels' roofline is quoted against
+ * (SURVEY.md 8d asks for the peak at run time, not a nominal one).  sink: one device float, never written. */
+int gsr_debug_fp32_peak(int32_t blocks, int32_t iters, float* sink, double* flops, void* stream);
+
 /* Measurement hooks used by bench.py (no effect on results).
  * gsr_profile_enable(1): every stage launcher brackets its launches with CUDA events recorded
  * on the launching stream (cudaEventRecord only; no synchronisation).  gsr_profile_collect
@@ -345,14 +359,13 @@ int gsr_debug_state_ptrs(const GsrParams* p, const GsrBuffers* buf, int64_t R,
  * gsr_launch_count: kernels launched by this library in this process so far. */
 #define GSR_STAGE_PREPROCESS      0
 #define GSR_STAGE_DEPTH_SORT      1
-#define GSR_STAGE_SCAN            2
-#define GSR_STAGE_EMIT            3
-#define GSR_STAGE_TILE_SORT       4
-#define GSR_STAGE_TILE_RANGES     5
-#define GSR_STAGE_RENDER_FWD      6
-#define GSR_STAGE_RENDER_BWD      7
-#define GSR_STAGE_PREPROCESS_BWD  8
-#define GSR_STAGE_COUNT           9
+#define GSR_STAGE_TILE_COUNT      2
+#define GSR_STAGE_TILE_FILL       3
+#define GSR_STAGE_RENDER_FWD      4
+#define GSR_STAGE_RENDER_BWD      5
+#define GSR_STAGE_PREPROCESS_BWD  6
+#define GSR_STAGE_EXCHANGE        7
+#define GSR_STAGE_COUNT           8
 int         gsr_profile_enable(int on);
 int         gsr_profile_collect(double* ms_sum, int64_t* calls);
 const char* gsr_stage_name(int stage);

@@ -35,6 +35,8 @@ class _Stream:
 
 
 class _Event:
+    cuda_event = None        # the emulated library records nothing (its stream is synchronous)
+
     def __init__(self, *a, **k):
         pass
 

@@ -23,7 +23,7 @@ from tests.helpers import np_inputs, np_settings, rel_err, run_oracle, small_sce
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "..", "gaussian_splatting_b200", "csrc")
 EMU = os.path.join(HERE, "host_emul", "cuda_emul")
-UNITS = ("api", "preprocess", "binning", "render_fwd", "render_bwd", "preprocess_bwd", "adam", "ssim", "exchange", "densify")
+UNITS = ("api", "preprocess", "binning", "render_fwd", "render_bwd", "preprocess_bwd", "adam", "ssim", "exchange", "densify", "peak")
 VP = C.c_void_p
 
 
@@ -389,9 +389,10 @@ def test_debug_mode_and_error_reporting(klib):
     assert klib.gsr_forward_stage1(C.byref(small.p), C.byref(small.b), C.byref(small.o), None) == _lib.GSR_ERR_CAPACITY
 
 
-def test_more_than_65536_tiles_three_pass_tile_sort(klib, oracle):
-    """257 x 257 tiles: tile ids need 17 bits, so the tile sort takes three 8-bit passes (binning.cu) — the path the GPU
-    suite covers with test_three_pass_tile_sort.  Small Gaussians keep the emulation at about a minute."""
+def test_more_than_65536_tiles_nine_bands(klib, oracle):
+    """257 x 257 tiles: more tiles than one unit of the tile-list construction keeps in shared memory, so the image is
+    cut into 9 bands of 31 tile rows (binning.cu) — the path the GPU suite covers with test_large_image_many_bands.
+    Small Gaussians keep the emulation at about a minute."""
     gs, s = small_scene(P=300, W=4112, H=4112, seed=5, scale_mult=0.1, antialiasing=True)
     er = check_against_oracle(klib, oracle, gs, s)
     assert ((er.W + 15) // 16) * ((er.H + 15) // 16) > 65536 and er.R > 10000
@@ -405,6 +406,17 @@ def test_radix_fallback_pass_for_counts_beyond_30_bits(oracle):
     gs, s = small_scene(P=700, W=80, H=48, seed=13, scale_mult=4.0, antialiasing=True)
     er = check_against_oracle(lib, oracle, gs, s)
     assert er.P > 64 and er.R > 64
+
+
+@pytest.mark.parametrize("P,W,H,scale", [(700, 80, 48, 4.0), (2500, 200, 120, 1.0), (130, 33, 17, 30.0)])
+def test_tile_lists_many_chunks_and_bands(oracle, P, W, H, scale):
+    """The tile-list construction at small sizes with its shared-memory budget lowered to 16 tiles (-DGSR_TB_MAX_CELLS=16):
+    bands of one or two tile rows, several chunks per band, rectangles that straddle bands and (scale 30) cover the whole
+    image with more than 32 tiles per Gaussian.  point_list, ranges and the rebuilt keys stay bit-exact."""
+    lib = load_full_emul(defines=("GSR_TB_MAX_CELLS=16",), tag="bands")
+    gs, s = small_scene(P=P, W=W, H=H, seed=21, scale_mult=scale, antialiasing=True)
+    er = check_against_oracle(lib, oracle, gs, s)
+    assert er.R > 64
 
 
 def test_adam_scalar_path_and_unmasked(klib):
@@ -540,8 +552,10 @@ def test_profiling_hooks_and_argument_errors(klib):
     ok(klib, klib.gsr_profile_collect(ms, n))
     klib.gsr_profile_enable(0)
     names = [klib.gsr_stage_name(i).decode() for i in range(_lib.STAGE_COUNT)]
-    assert all(c == 1 for c in n) and "render_bwd" in names and klib.gsr_stage_name(99) == b"?"
-    assert klib.gsr_launch_count() - l0 >= 15
+    assert all(c == 1 for c, name in zip(n, names) if name != "exchange") and klib.gsr_stage_name(99) == b"?"
+    assert names == ["preprocess", "depth_sort", "tile_count", "tile_fill", "render_fwd", "render_bwd", "preprocess_bwd",
+                     "exchange"]
+    assert klib.gsr_launch_count() - l0 >= 13
     # argument errors come back as codes with the reference's messages, never as aborts
     e = EmulRasterizer(klib, gs, s)
     e.p.scales = None

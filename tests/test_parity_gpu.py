@@ -2,8 +2,12 @@
 Python API against (a) the CPU oracle and (b) the reference's own CUDA rasterizer built for
 sm_100 (oracle/_ref, see oracle/build_ref.py), on the same seeded inputs.
 
-Tolerances (BASELINE.json north_star): bit-exact sorted keys / values / tile ranges / radii /
-num_rendered; image and inverse depth <= 1e-5 max-abs; gradients <= 1e-3 relative.
+Tolerances (BASELINE.json north_star): bit-exact sorted values (point_list) / tile ranges / radii /
+num_rendered / n_contrib (and the reference's sorted keys as REBUILT from ranges, point_list and the records'
+depth by a test hook: the product never materialises tile<<32|depth); image and inverse depth <= 1e-5 max-abs;
+gradients <= 1e-3 norm-wise (||a-b||inf / ||b||inf) AND <= 1e-2 per element for every element above
+1e-4 * ||b||inf (SURVEY.md 8c asks for the per-element check; 1e-4 is what the reference's own atomic-order
+noise allows against the mean of 3 of its runs).
 """
 import numpy as np
 import pytest
@@ -47,7 +51,10 @@ def _upstream(W, H, seed=5, depth=True):
     return dc, dd
 
 
-def _check_grads(got, want, keys, tol=GRAD_TOL, elem_floor=1e-2):
+ELEM_FLOOR = 1e-4
+
+
+def _check_grads(got, want, keys, tol=GRAD_TOL, elem_floor=ELEM_FLOOR):
     for k in keys:
         a, b = got[k], want[k].reshape(got[k].shape)
         assert rel_err(a, b) < tol, (k, rel_err(a, b))
@@ -85,16 +92,36 @@ def test_backward_vs_oracle(dgr, oracle, antialiasing, bg):
     _check_grads(got["grads"], want["grads"], ("means3D", "means2D", "opacities", "shs", "scales", "rotations"))
 
 
-def test_backward_without_depth_gradient(dgr, oracle):
+def _ref_mean(ref, gs, s, dc, dd, runs=3):
+    """Mean gradients of `runs` runs of the reference CUDA build (its atomics are order-nondeterministic)."""
+    outs = [run_module(ref, gs, s, dc, dd) for _ in range(runs)]
+    want = dict(outs[0])
+    want["grads"] = {k: np.mean([o["grads"][k] for o in outs], axis=0) for k in outs[0]["grads"]}
+    return want
+
+
+def _checker(name, oracle, ref_restored):
+    """'oracle' -> the C restatement on the CPU, 'reference' -> the reference's own CUDA build on this GPU."""
+    if name == "oracle":
+        return lambda gs, s, dc, dd: run_oracle(oracle, gs, s, dc, dd)
+    return lambda gs, s, dc, dd: _ref_mean(ref_restored, gs, s, dc, dd)
+
+
+CHECKERS = ["oracle", "reference"]
+
+
+@pytest.mark.parametrize("checker", CHECKERS)
+def test_backward_without_depth_gradient(dgr, oracle, ref_restored, checker):
     W, H = 64, 48
     gs, s = small_scene(P=500, W=W, H=H, bg=(0.5, 0.5, 0.5), seed=3)
     dc, _ = _upstream(W, H)
-    want = run_oracle(oracle, gs, s, dc, None)
+    want = _checker(checker, oracle, ref_restored)(gs, s, dc, None)
     got = run_module(dgr, gs, s, dc, None)
     _check_grads(got["grads"], want["grads"], ("means3D", "means2D", "opacities", "shs", "scales", "rotations"))
 
 
-def test_precomputed_colour_and_covariance(dgr, oracle):
+@pytest.mark.parametrize("checker", CHECKERS)
+def test_precomputed_colour_and_covariance(dgr, oracle, ref_restored, checker):
     W, H, P = 72, 56, 600
     gs, s = small_scene(P=P, W=W, H=H, antialiasing=True, bg=(0.1, 0.2, 0.3), seed=9)
     from oracle import autograd_ref
@@ -106,21 +133,22 @@ def test_precomputed_colour_and_covariance(dgr, oracle):
     gs2 = dict(means3D=gs["means3D"], opacities=gs["opacities"], colors_precomp=torch.rand(P, 3, generator=g),
                cov3D_precomp=cov6.float().contiguous())
     dc, dd = _upstream(W, H)
-    want = run_oracle(oracle, gs2, s, dc, dd)
+    want = _checker(checker, oracle, ref_restored)(gs2, s, dc, dd)
     got = run_module(dgr, gs2, s, dc, dd)
     assert np.array_equal(got["radii"], want["radii"])
     assert np.abs(got["color"] - want["color"]).max() <= IMG_TOL
     _check_grads(got["grads"], want["grads"], ("means3D", "means2D", "opacities", "colors_precomp", "cov3D_precomp"))
 
 
+@pytest.mark.parametrize("checker", CHECKERS)
 @pytest.mark.parametrize("deg,M", [(0, 1), (0, 16), (1, 4), (2, 9), (2, 16), (3, 16)])
-def test_sh_degrees(dgr, oracle, deg, M):
+def test_sh_degrees(dgr, oracle, ref_restored, deg, M, checker):
     W, H, P = 56, 40, 400
     gs, s = small_scene(P=P, W=W, H=H, sh_degree=3, seed=30 + deg)
     gs["shs"] = gs["shs"][:, :M, :].contiguous()
     s["sh_degree"] = deg
     dc, dd = _upstream(W, H)
-    want = run_oracle(oracle, gs, s, dc, dd)
+    want = _checker(checker, oracle, ref_restored)(gs, s, dc, dd)
     got = run_module(dgr, gs, s, dc, dd)
     assert np.abs(got["color"] - want["color"]).max() <= IMG_TOL
     assert got["grads"]["shs"].shape == (P, M, 3)
@@ -172,8 +200,9 @@ def test_mark_visible(dgr, oracle, ref_restored):
     assert (got.cpu().numpy() != cpu).sum() <= 2
 
 
-def test_three_pass_tile_sort(dgr, oracle, ref_restored):
-    """T = 257*257 = 66049 tiles > 2^16: the tile ordering needs 3 radix passes (17 key bits)."""
+def test_large_image_many_bands(dgr, oracle, ref_restored):
+    """T = 257*257 = 66049 tiles: 9 bands of 31 tile rows in the tile-list construction (binning.cu); the reference
+    sorts 17 tile bits here."""
     W = H = 4112
     gs, s = small_scene(P=3000, W=W, H=H, scale_mult=2.0, seed=12)
     want = run_oracle(oracle, gs, s)["fw"]
@@ -201,6 +230,7 @@ REF_CASES = [
     (20000, 320, 240, 2.0, False, (0.0, 0.0, 0.0)),
     (20000, 333, 247, 3.0, True, (1.0, 1.0, 1.0)),
     (200000, 800, 800, 1.0, True, (0.2, 0.4, 0.7)),
+    (100000, 1297, 840, 1.5, False, (0.3, 0.6, 0.1)),      # antialiasing off above 320x240, ragged right / bottom tiles
 ]
 
 
@@ -355,6 +385,32 @@ def test_full_size_c3_vs_reference_cuda(dgr, ref_restored):
     torch.cuda.empty_cache()
     dc, dd = _upstream(cfg.W, cfg.H)
     a = run_module(dgr, gs, s, dc, dd)
-    b = run_module(ref_restored, gs, s, dc, dd)
-    for k in ("means3D", "means2D", "opacities", "shs", "scales", "rotations"):
-        assert rel_err(a["grads"][k], b["grads"][k]) < GRAD_TOL, (k, rel_err(a["grads"][k], b["grads"][k]))
+    b = _ref_mean(ref_restored, gs, s, dc, dd, runs=2)
+    _check_grads(a["grads"], b["grads"], ("means3D", "means2D", "opacities", "shs", "scales", "rotations"))
+
+
+@pytest.mark.parametrize("name", ["C2", "C4"])
+def test_full_size_c2_c4_vs_reference_cuda(dgr, ref_restored, name):
+    """C2 (1M Gaussians, 1297x840: ragged right / bottom tile edge at scale) and C4 (6M Gaussians, 3840x2160:
+    32 400 tiles, four bands of tile rows) of BASELINE.json against the reference's CUDA build: binning state and
+    n_contrib bit-exact, image / depth <= 1e-5, gradients as _check_grads."""
+    from gaussian_splatting_b200 import synthetic
+    cfg = synthetic.CONFIGS[name]
+    gs, cam = synthetic.make_scene(cfg)
+    s = dict(cam)
+    s.update(bg=torch.tensor([0.1, 0.2, 0.3]), scale_modifier=1.0, sh_degree=3, prefiltered=False, debug=False)
+    want = ref_forward_state(ref_restored, gs, s)
+    got = ours_forward_state(gs, s)
+    assert got["num_rendered"] == want["num_rendered"] > 1_000_000
+    assert np.array_equal(got["radii"], want["radii"])
+    assert np.array_equal(got["point_list"], want["point_list"])
+    assert np.array_equal(got["ranges"], want["ranges"])
+    assert np.array_equal(got["n_contrib"], want["n_contrib"])
+    assert np.abs(got["color"] - want["color"]).max() <= IMG_TOL
+    assert np.abs(got["invdepth"] - want["invdepth"]).max() <= IMG_TOL
+    del want, got
+    torch.cuda.empty_cache()
+    dc, dd = _upstream(cfg.W, cfg.H)
+    a = run_module(dgr, gs, s, dc, dd)
+    b = _ref_mean(ref_restored, gs, s, dc, dd, runs=2)
+    _check_grads(a["grads"], b["grads"], ("means3D", "means2D", "opacities", "shs", "scales", "rotations"))
