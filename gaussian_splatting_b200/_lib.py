@@ -11,6 +11,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("GSR_LIB") or os.path.join(_HERE, "libgsrast.so")
 
 GSR_OK = 0
+RAW_SCALES, RAW_ROTATIONS, RAW_OPACITIES = 1, 2, 4
 GSR_ERR_INVALID_ARG = -1
 GSR_ERR_CUDA = -2
 GSR_ERR_CAPACITY = -3
@@ -24,7 +25,7 @@ class GsrParams(C.Structure):
         ("P", C.c_int32), ("D", C.c_int32), ("M", C.c_int32), ("W", C.c_int32), ("H", C.c_int32),
         ("tanfovx", C.c_float), ("tanfovy", C.c_float), ("scale_modifier", C.c_float),
         ("prefiltered", C.c_int32), ("antialiasing", C.c_int32), ("debug", C.c_int32),
-        ("reserved0", C.c_int32),
+        ("raw_inputs", C.c_int32),
         ("background", _fp), ("means3D", _fp), ("shs", _fp), ("colors_precomp", _fp),
         ("opacities", _fp), ("scales", _fp), ("rotations", _fp), ("cov3D_precomp", _fp),
         ("viewmatrix", _fp), ("projmatrix", _fp), ("campos", _fp), ("sh_dc", _fp),

@@ -80,11 +80,24 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
     return ok != 0;
 }
 
-// Bounded wait: a lost copy traps (launch failure reported to the host) instead of
-// hanging the GPU.
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+// A wait that lasts longer than this can only be a lost copy / a lost predecessor: trap (launch failure reported to
+// the host) instead of hanging the GPU.  The bound is wall time, not a poll count, so profiler replay, time-slicing
+// or a debugger stretching a healthy kernel do not trip it.
+constexpr unsigned long long SPIN_LIMIT_NS = 4000000000ull;
+
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    for (uint32_t spins = 0; !mbar_try_wait(bar, parity); ++spins) {
-        if (spins > (1u << 22)) __trap();
+    unsigned long long t0 = 0;
+    for (uint32_t spins = 1; !mbar_try_wait(bar, parity); ++spins) {
+        if ((spins & 0xfffu) == 0) {
+            const unsigned long long now = global_timer_ns();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > SPIN_LIMIT_NS) __trap();
+        }
     }
 }
 

@@ -17,6 +17,7 @@
 // reference's stable sort of (tile<<32 | depth) keys emitted in (id, tile) order, bit for bit.
 #include "common.cuh"
 #include "block_scan.cuh"
+#include "async_copy.cuh"
 
 namespace gsr {
 
@@ -280,10 +281,20 @@ onesweep_kernel(const uint64_t* __restrict__ in, uint32_t n, int shift, const ui
         if (tile > 0) {
             int look = (int)tile - 1;
             uint32_t spins = 0;
+            unsigned long long t0 = 0;
             while (true) {
                 const uint32_t v = vstatus[(size_t)look * 256 + t];
                 if ((v >> 30) == 0) {
-                    if (++spins > (1u << 24)) __trap();       // a lost predecessor must not hang the GPU
+#ifndef GSR_HOST_EMUL
+                    if ((++spins & 0xfffu) == 0) {             // a lost predecessor must not hang the GPU (wall-time bound)
+                        const unsigned long long now = global_timer_ns();
+                        if (t0 == 0) t0 = now;
+                        else if (now - t0 > SPIN_LIMIT_NS) __trap();
+                    }
+#else
+                    if (++spins > (1u << 24)) __trap();
+                    (void)t0;
+#endif
                     continue;
                 }
                 excl += v & OS_COUNT_MASK;
@@ -352,44 +363,141 @@ static int radix_pass(const uint64_t* src, uint64_t* dst, uint32_t n, int shift,
 // ---------------------------------------------------------------- per-tile lists
 // Unit of work = (chunk of consecutive depth ranks, band of tile rows).  The band keeps a unit's
 // tile counters in shared memory (<= TB_MAX_CELLS tiles); at 1080p the whole image is one band.
-// Chunks cover the V visible Gaussians (they sort before the culled ones, whose keys are all-ones);
-// V is counted by the preprocess kernel.  A culled Gaussian's rectangle is empty, so a stray one
-// inside a chunk adds nothing.
-__device__ __forceinline__ void unit_ranks(const int32_t* counters, const TileBinPlan& pl, uint32_t chunk,
-                                           uint32_t& k0, uint32_t& k1) {
-    const unsigned long long V = (uint32_t)counters[CNT_VISIBLE];
-    k0 = (uint32_t)(V * chunk / pl.n_chunks);
-    k1 = (uint32_t)(V * (chunk + 1) / pl.n_chunks);
-}
+// Chunks cover the V visible Gaussians (they sort before the culled ones, whose keys are all-ones;
+// V is counted by the preprocess kernel) and are cut so that every chunk holds about the same number
+// of list-filling steps (a step appends one Gaussian to up to 32 tiles): near Gaussians cover hundreds
+// of tiles, far ones a few, so equal Gaussian counts would leave the first chunks 6x the work.
+// A culled Gaussian's rectangle is empty, so a stray one inside a chunk adds nothing.
 
-// Part of rectangle r inside tile rows [r0, r1): first local tile index, width, tile count (0 = outside).
+// Shared-memory word access by shared-window address (the compiler otherwise rebuilds the window base in every
+// step of the list-filling loop), and the fence between two steps of a warp.  On the device a warp runs the
+// filling loop converged (every branch in it is warp-uniform) and the volatile accesses stay in program order, so
+// one step's store precedes the next step's load in the same warp's instruction stream; the CPU emulation runs the
+// lanes as fibers and needs the scheduling point.
+#ifndef GSR_HOST_EMUL
+__device__ __forceinline__ uint32_t lds_u32(uint32_t a) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts_u32(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+__device__ __forceinline__ void step_fence() {}
+#else
+__device__ __forceinline__ uint32_t lds_u32(uint32_t a) { return *reinterpret_cast<uint32_t*>(smem_ptr(a)); }
+__device__ __forceinline__ void sts_u32(uint32_t a, uint32_t v) { *reinterpret_cast<uint32_t*>(smem_ptr(a)) = v; }
+__device__ __forceinline__ void step_fence() { __syncwarp(); }
+#endif
+
+#ifndef GSR_TB_FILL_WARPS
+#define GSR_TB_FILL_WARPS 8
+#endif
+constexpr int TB_FILL_WARPS = GSR_TB_FILL_WARPS;       // warps (= stripes of tile rows) per CTA of the list-filling kernel
+
+// Part of rectangle r inside tile rows [r0, r1).
 __device__ __forceinline__ void clip_rect(uint2 r, uint32_t r0, uint32_t r1, uint32_t& x0, uint32_t& x1,
                                           uint32_t& ya, uint32_t& yb) {
     x0 = r.x & 0xffffu; x1 = r.y & 0xffffu;
     ya = max(r.x >> 16, r0); yb = min(r.y >> 16, r1);
 }
 
-// Step 2a.  count[chunk][tile] = Gaussians of the chunk whose rectangle covers the tile: +-1 at the four
+// ceil(2^31 / w): (2 l) * magic >> 32 == l / w while l * w < 2^31 (here l < 2^20 tiles of a band, w <= 2^11 columns)
+__device__ __forceinline__ uint32_t div_magic(uint32_t w) { return 0x7FFFFFFFu / (w ? w : 1u) + 1u; }
+
+// Step 2a.  The Gaussians in depth order as 16-byte records {rect.x, rect.y, div_magic(width), id} (what the two
+// following kernels stream instead of gathering by id) and, per weight block of pl.wblock consecutive depth ranks,
+// the number of list-filling steps they need.  One CTA per weight block.
+__global__ void __launch_bounds__(256)
+tile_weights_kernel(const uint64_t* __restrict__ sorted, const uint2* __restrict__ rects,
+                    const int32_t* __restrict__ counters, uint32_t wblock,
+                    uint4* __restrict__ srects, uint32_t* __restrict__ weights) {
+    __shared__ uint32_t s_sum;
+    if (threadIdx.x == 0) s_sum = 0;
+    __syncthreads();
+    const uint32_t V = (uint32_t)counters[CNT_VISIBLE];
+    const uint32_t k0 = blockIdx.x * wblock, k1 = min(V, k0 + wblock);
+    uint32_t steps = 0;
+    for (uint32_t k = k0 + threadIdx.x; k < k1; k += 256) {
+        const uint32_t id = (uint32_t)sorted[k];
+        const uint2 r = rects[id];
+        const uint32_t w = (r.y & 0xffffu) - (r.x & 0xffffu);
+        srects[k] = make_uint4(r.x, r.y, div_magic(w), id);
+        steps += (w * ((r.y >> 16) - (r.x >> 16)) + 31u) >> 5;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) steps += __shfl_xor_sync(0xffffffffu, steps, o);
+    if ((threadIdx.x & 31u) == 0 && steps) atomicAdd(&s_sum, steps);
+    __syncthreads();
+    if (threadIdx.x == 0) weights[blockIdx.x] = s_sum;
+}
+
+// Step 2b.  One CTA: exclusive scan of the (<= TB_MAX_WBLOCKS) weights in shared memory; chunk c starts where the
+// running weight reaches c / n_chunks of the total, interpolated linearly inside a weight block (the cut only
+// balances work: any monotone bounds with bounds[0] = 0 and bounds[n_chunks] = V give the same lists).
+constexpr int TB_SCAN_THREADS = 1024;
+__global__ void __launch_bounds__(TB_SCAN_THREADS)
+tile_bounds_kernel(const uint32_t* __restrict__ weights, uint32_t n_wblocks, uint32_t wblock,
+                   const int32_t* __restrict__ counters, uint32_t n_chunks, uint32_t* __restrict__ bounds) {
+    __shared__ uint32_t s_e[TB_MAX_WBLOCKS + 1];     // exclusive prefixes, s_e[n_wblocks] = total
+    __shared__ uint32_t s_w[32];
+    const uint32_t t = threadIdx.x, lane = t & 31u, warp = t >> 5;
+    constexpr uint32_t PER = TB_MAX_WBLOCKS / TB_SCAN_THREADS;
+    uint32_t v[PER], sum = 0;
+#pragma unroll
+    for (uint32_t j = 0; j < PER; j++) {
+        const uint32_t i = t * PER + j;
+        v[j] = i < n_wblocks ? weights[i] : 0u;
+        sum += v[j];
+    }
+    const uint32_t inc = warp_incl_scan(sum, lane);
+    if (lane == 31) s_w[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        const uint32_t w = s_w[lane];
+        s_w[lane] = warp_incl_scan(w, lane) - w;
+    }
+    __syncthreads();
+    uint32_t run = s_w[warp] + inc - sum;
+#pragma unroll
+    for (uint32_t j = 0; j < PER; j++) {
+        s_e[t * PER + j] = run;
+        run += v[j];
+    }
+    if (t == TB_SCAN_THREADS - 1) s_e[TB_MAX_WBLOCKS] = run;      // total (entries past n_wblocks hold the total too)
+    __syncthreads();
+    const unsigned long long total = s_e[TB_MAX_WBLOCKS];
+    const uint32_t V = (uint32_t)counters[CNT_VISIBLE];
+    for (uint32_t c = t; c <= n_chunks; c += TB_SCAN_THREADS) {
+        unsigned long long rank = V;
+        if (c < n_chunks) {
+            const uint32_t target = (uint32_t)(total * c / n_chunks);
+            uint32_t lo = 0, hi = n_wblocks;                       // last block with prefix <= target
+            while (hi - lo > 1) {
+                const uint32_t mid = (lo + hi) >> 1;
+                if (s_e[mid] <= target) lo = mid; else hi = mid;
+            }
+            const uint32_t wb = s_e[lo + 1] - s_e[lo];
+            rank = (unsigned long long)lo * wblock + (wb ? (unsigned long long)(target - s_e[lo]) * wblock / wb : 0ull);
+        }
+        bounds[c] = rank < V ? (uint32_t)rank : V;
+    }
+}
+
+// Step 2c.  count[chunk][tile] = Gaussians of the chunk whose rectangle covers the tile: +-1 at the four
 // corners of every rectangle in a difference grid (order-free shared-memory adds), then a 2-D prefix sum.
-// The units of band 0 also write the rectangles in depth order (srects), so that the list-filling kernel
-// streams them instead of gathering by id.
 __global__ void __launch_bounds__(TB_COUNT_THREADS)
-tile_count_kernel(const uint64_t* __restrict__ sorted, const uint2* __restrict__ rects,
-                  const int32_t* __restrict__ counters, TileBinPlan pl,
-                  uint32_t* __restrict__ M, uint2* __restrict__ srects) {
+tile_count_kernel(const uint4* __restrict__ srects, const uint32_t* __restrict__ bounds, TileBinPlan pl,
+                  uint32_t* __restrict__ M) {
     __shared__ int32_t D[TB_COUNT_CELLS];
-    const uint32_t t = threadIdx.x, chunk = blockIdx.x, band = blockIdx.y;
+    const uint32_t t = threadIdx.x, lane = t & 31u, warp = t >> 5, chunk = blockIdx.x, band = blockIdx.y;
     const uint32_t r0 = band * pl.band_rows, r1 = min(pl.gy, r0 + pl.band_rows);
     const uint32_t rows = r1 - r0, S = pl.stride, gx = pl.gx;
-    uint32_t k0, k1;
-    unit_ranks(counters, pl, chunk, k0, k1);
+    const uint32_t k0 = bounds[chunk], k1 = bounds[chunk + 1];
     for (uint32_t i = t; i < (rows + 1) * S; i += TB_COUNT_THREADS) D[i] = 0;
     __syncthreads();
     for (uint32_t k = k0 + t; k < k1; k += TB_COUNT_THREADS) {
-        const uint2 r = rects[(uint32_t)sorted[k]];
-        if (band == 0) srects[k] = r;
         uint32_t x0, x1, ya, yb;
-        clip_rect(r, r0, r1, x0, x1, ya, yb);
+        const uint4 g = srects[k];
+        clip_rect(make_uint2(g.x, g.y), r0, r1, x0, x1, ya, yb);
         if (x1 > x0 && yb > ya) {
             const uint32_t a = (ya - r0) * S, b = (yb - r0) * S;
             atomicAdd(&D[a + x0], 1);
@@ -399,9 +507,15 @@ tile_count_kernel(const uint64_t* __restrict__ sorted, const uint2* __restrict__
         }
     }
     __syncthreads();
-    for (uint32_t r = t; r < rows; r += TB_COUNT_THREADS) {          // along x (S is odd: conflict-free)
-        int32_t run = 0;
-        for (uint32_t x = 0; x < gx; x++) { run += D[r * S + x]; D[r * S + x] = run; }
+    // along x: one warp per row, 32 columns at a time
+    for (uint32_t r = warp; r < rows; r += TB_COUNT_THREADS / 32) {
+        uint32_t carry = 0;
+        for (uint32_t x = 0; x < gx; x += 32) {
+            const uint32_t v = x + lane < gx ? (uint32_t)D[r * S + x + lane] : 0u;
+            const uint32_t inc = warp_incl_scan(v, lane) + carry;
+            if (x + lane < gx) D[r * S + x + lane] = (int32_t)inc;
+            carry = __shfl_sync(0xffffffffu, inc, 31);
+        }
     }
     __syncthreads();
     uint32_t* out = M + (size_t)chunk * pl.T + (size_t)r0 * gx;
@@ -411,10 +525,10 @@ tile_count_kernel(const uint64_t* __restrict__ sorted, const uint2* __restrict__
     }
 }
 
-// Step 2b.  Per tile: exclusive prefix of the counts over the chunks, in place, and the tile's total.
+// Step 2d.  Per tile: exclusive prefix of the counts over the chunks, in place, and the tile's total.
 // 32 tiles x TB_CP_GROUPS chunk groups per CTA; each thread sums its group, the group totals are combined
 // through shared memory, a second sweep writes the prefixes.
-constexpr int TB_CP_GROUPS = 8;
+constexpr int TB_CP_GROUPS = 32;
 __global__ void __launch_bounds__(32 * TB_CP_GROUPS)
 tile_chunk_prefix_kernel(uint32_t* __restrict__ M, TileBinPlan pl, uint32_t* __restrict__ totals) {
     __shared__ uint32_t s_tot[TB_CP_GROUPS][32];
@@ -442,94 +556,157 @@ tile_chunk_prefix_kernel(uint32_t* __restrict__ M, TileBinPlan pl, uint32_t* __r
     if (grp == TB_CP_GROUPS - 1) totals[t] = run;
 }
 
-// Step 2c.  One CTA: exclusive scan of the tile totals -> ranges (identifyTileRanges, rasterizer_impl.cu:
+// Step 2e.  One CTA: exclusive scan of the tile totals -> ranges (identifyTileRanges, rasterizer_impl.cu:
 // 132-164: [start, end) per tile, (0, 0) for a tile nobody touches -- the reference memsets and never writes it).
-constexpr int TB_SCAN_THREADS = 1024;
+// Totals pass through registers in slabs of 8 per thread, loaded and stored coalesced through shared memory.
+//
+// Also: tile_start[T + 1] (the exclusive prefix of every tile, empty ones included) and, per band, the tile rows at
+// which the list-filling kernel cuts the band into TB_FILL_WARPS stripes of about equal instance counts (rows near
+// the image centre are denser: equal row counts would leave most warps of a CTA waiting for one).
 __global__ void __launch_bounds__(TB_SCAN_THREADS)
-tile_ranges_kernel(const uint32_t* __restrict__ totals, uint32_t T, uint2* __restrict__ ranges) {
+tile_ranges_kernel(const uint32_t* __restrict__ totals, TileBinPlan pl, uint2* __restrict__ ranges,
+                   uint32_t* __restrict__ tile_start, uint32_t* __restrict__ stripes) {
+    const uint32_t T = pl.T;
+    constexpr uint32_t PER = 8, SLAB = PER * TB_SCAN_THREADS;
+    __shared__ uint32_t s_v[SLAB + SLAB / 32];       // padded: thread t reads 8 consecutive words conflict-free
     __shared__ uint32_t s_w[32];
     const uint32_t t = threadIdx.x, lane = t & 31u, warp = t >> 5;
-    const uint32_t per = div_up(T, TB_SCAN_THREADS);
-    const uint32_t b0 = min(T, t * per), b1 = min(T, b0 + per);
-    uint32_t sum = 0;
-    for (uint32_t i = b0; i < b1; i++) sum += totals[i];
-    const uint32_t inc = warp_incl_scan(sum, lane);
-    if (lane == 31) s_w[warp] = inc;
-    __syncthreads();
-    if (warp == 0) {
-        const uint32_t w = s_w[lane];
-        s_w[lane] = warp_incl_scan(w, lane) - w;
+    uint32_t carry = 0;
+    for (uint32_t base = 0; base < T; base += SLAB) {
+        for (uint32_t j = 0; j < PER; j++) {
+            const uint32_t i = j * TB_SCAN_THREADS + t;
+            s_v[i + (i >> 5)] = base + i < T ? totals[base + i] : 0u;
+        }
+        __syncthreads();
+        uint32_t v[PER], sum = 0;
+#pragma unroll
+        for (uint32_t j = 0; j < PER; j++) {
+            const uint32_t i = t * PER + j;
+            v[j] = s_v[i + (i >> 5)];
+            sum += v[j];
+        }
+        const uint32_t inc = warp_incl_scan(sum, lane);
+        if (lane == 31) s_w[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            const uint32_t w = s_w[lane];
+            s_w[lane] = warp_incl_scan(w, lane) - w;
+        }
+        __syncthreads();
+        uint32_t run = carry + s_w[warp] + inc - sum;
+#pragma unroll
+        for (uint32_t j = 0; j < PER; j++) {
+            const uint32_t i = t * PER + j;
+            s_v[i + (i >> 5)] = run;                 // exclusive prefix = start of the tile's list
+            run += v[j];
+        }
+        __syncthreads();
+        if (t == TB_SCAN_THREADS - 1) s_w[0] = run;  // slab total + carry
+        for (uint32_t j = 0; j < PER; j++) {
+            const uint32_t i = j * TB_SCAN_THREADS + t;
+            if (base + i < T) {
+                const uint32_t start = s_v[i + (i >> 5)], c = totals[base + i];
+                ranges[base + i] = c ? make_uint2(start, start + c) : make_uint2(0u, 0u);
+                tile_start[base + i] = start;
+            }
+        }
+        __syncthreads();
+        carry = s_w[0];
+        __syncthreads();
     }
-    __syncthreads();
-    uint32_t run = s_w[warp] + inc - sum;
-    for (uint32_t i = b0; i < b1; i++) {
-        const uint32_t c = totals[i];
-        ranges[i] = c ? make_uint2(run, run + c) : make_uint2(0u, 0u);
-        run += c;
+    if (t == 0) tile_start[T] = carry;
+    __syncthreads();                     // tile_start (written by this CTA) is visible to all of its threads
+    // stripes[band][w], w = 0..TB_FILL_WARPS: first tile row of stripe w (relative cuts at equal instance counts)
+    for (uint32_t i = t; i < pl.n_bands * (TB_FILL_WARPS + 1); i += TB_SCAN_THREADS) {
+        const uint32_t band = i / (TB_FILL_WARPS + 1), w = i % (TB_FILL_WARPS + 1);
+        const uint32_t r0 = band * pl.band_rows, r1 = min(pl.gy, r0 + pl.band_rows);
+        const uint32_t lo_v = tile_start[r0 * pl.gx], hi_v = tile_start[r1 * pl.gx];
+        const uint32_t target = lo_v + (uint32_t)((unsigned long long)(hi_v - lo_v) * w / TB_FILL_WARPS);
+        uint32_t lo = r0, hi = r1;       // first row whose start reaches the target
+        if (w == 0) hi = r0;
+        else if (w == TB_FILL_WARPS) lo = r1;
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (tile_start[mid * pl.gx] >= target) hi = mid; else lo = mid + 1;
+        }
+        stripes[i] = lo;
     }
 }
 
-// Step 3.  One warp per unit.  run[tile] = next free slot of the tile's list for this chunk.  32 Gaussians are
-// tested against the band at a time; the warp then takes the ones that intersect it one after the other, lanes =
-// tiles of the rectangle (row-major): slot = run[tile]++ , point_list[slot] = id.  Within one Gaussian all tiles
-// differ, and Gaussians are taken in depth order, so every list is filled in order without any ranking.
-__global__ void __launch_bounds__(32)
-tile_fill_kernel(const uint64_t* __restrict__ sorted, const uint2* __restrict__ srects,
-                 const int32_t* __restrict__ counters, TileBinPlan pl,
-                 const uint32_t* __restrict__ M, const uint2* __restrict__ ranges,
-                 uint32_t* __restrict__ point_list) {
-    __shared__ uint32_t run[TB_MAX_CELLS];
-    const uint32_t lane = threadIdx.x, chunk = blockIdx.x, band = blockIdx.y;
+// Step 3.  One CTA of TB_FILL_WARPS warps per unit.  run[tile] = next free slot of the tile's list for this chunk.
+// Every warp owns a stripe of the band's tile rows (cut by tile_ranges_kernel at equal instance counts) and walks
+// ALL Gaussians of the chunk in depth order, 32 at a time: each lane clips one rectangle to the stripe and the ones
+// that reach it are compacted (in order) into a parameter list in shared memory; the warp then takes them one after
+// the other, lanes = tiles of the clipped rectangle (row-major): slot = run[tile]++, point_list[slot] = id.
+// Within one Gaussian all tiles differ, a tile belongs to one warp, and a warp takes Gaussians in depth order: every
+// list is filled in order without any ranking.  Lanes beyond the rectangle do the same read-modify-write on a
+// scratch word of their own (no branch in the step).  The warps of a CTA never wait for each other after the
+// counters are set up.
+#ifndef GSR_TB_FILL_BLOCKS
+#define GSR_TB_FILL_BLOCKS 6            // CTAs per SM: 37 KB of shared memory each
+#endif
+__global__ void __launch_bounds__(32 * TB_FILL_WARPS, GSR_TB_FILL_BLOCKS)
+tile_fill_kernel(const uint4* __restrict__ srects, const uint32_t* __restrict__ bounds, TileBinPlan pl,
+                 const uint32_t* __restrict__ M, const uint32_t* __restrict__ tile_start,
+                 const uint32_t* __restrict__ stripes, uint32_t* __restrict__ point_list) {
+    __shared__ uint32_t run[TB_MAX_CELLS + 32 * TB_FILL_WARPS];  // tile counters, then one scratch word per thread
+    __shared__ __align__(16) uint4 s_par[TB_FILL_WARPS][32];     // {id, first cell, n | (gx - w) << 21, div_magic(w)}
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, chunk = blockIdx.x, band = blockIdx.y;
     const uint32_t r0 = band * pl.band_rows, r1 = min(pl.gy, r0 + pl.band_rows);
-    const uint32_t gx = pl.gx, cells = (r1 - r0) * gx;
-    uint32_t k0, k1;
-    unit_ranks(counters, pl, chunk, k0, k1);
+    const uint32_t rows = r1 - r0, gx = pl.gx, cells = rows * gx;
+    const uint32_t k0 = bounds[chunk], k1 = bounds[chunk + 1];
     if (k0 >= k1) return;
     {
         const uint32_t* m = M + (size_t)chunk * pl.T + (size_t)r0 * gx;
-        const uint2* rg = ranges + (size_t)r0 * gx;
-        for (uint32_t i = lane; i < cells; i += 32) run[i] = rg[i].x + m[i];
+        const uint32_t* ts = tile_start + (size_t)r0 * gx;
+        for (uint32_t i = threadIdx.x; i < cells; i += 32 * TB_FILL_WARPS) run[i] = ts[i] + m[i];
     }
-    __syncwarp();
+    __syncthreads();
+    const uint32_t s0 = stripes[band * (TB_FILL_WARPS + 1) + warp], s1 = stripes[band * (TB_FILL_WARPS + 1) + warp + 1];
+    if (s0 >= s1) return;                // an empty stripe (one very dense row next to it)
+    uint4* par = s_par[warp];
+    uint32_t run_s = smem_u32(run);                           // shared-window address: the steps use 32-bit addressing
+    uint32_t lane2 = lane + lane;
+    const uint32_t dummy = TB_MAX_CELLS + threadIdx.x;
+    const uint32_t lt = (1u << lane) - 1u;
+#ifndef GSR_HOST_EMUL
+    asm volatile("" : "+r"(run_s), "+r"(lane2));              // keep both in registers (ptxas otherwise rebuilds them per step)
+#endif
+    // one slot per (Gaussian, tile): lanes = tiles l, l + 32, ... of the clipped rectangle
+    auto append = [&](const uint4& q, uint32_t n, uint32_t skip, uint32_t l, uint32_t l2) {
+        const uint32_t ry = __umulhi(l2, q.w);
+        const uint32_t cell = l < n ? q.y + l + ry * skip : dummy;
+        const uint32_t a = run_s + 4u * cell;
+        const uint32_t slot = lds_u32(a);
+        sts_u32(a, slot + 1u);
+        if (l < n) point_list[slot] = q.x;
+        step_fence();                    // the next Gaussian's lanes may read the counters this one wrote
+    };
     // one batch of 32 Gaussians is fetched ahead of the one being walked
-    uint64_t item_n = k0 + lane < k1 ? sorted[k0 + lane] : 0ull;
-    uint2 rect_n = k0 + lane < k1 ? srects[k0 + lane] : make_uint2(0u, 0u);
+    uint4 next = k0 + lane < k1 ? srects[k0 + lane] : make_uint4(0u, 0u, 0u, 0u);
     for (uint32_t k = k0; k < k1; k += 32) {
-        const uint32_t id = (uint32_t)item_n;
-        const uint2 r = rect_n;
+        const uint4 g = next;
         const uint32_t kn = k + 32 + lane;
-        item_n = kn < k1 ? sorted[kn] : 0ull;
-        rect_n = kn < k1 ? srects[kn] : make_uint2(0u, 0u);
+        next = kn < k1 ? srects[kn] : make_uint4(0u, 0u, 0u, 0u);
         uint32_t x0, x1, ya, yb;
-        clip_rect(r, r0, r1, x0, x1, ya, yb);
-        uint32_t n = 0, w = 0, first = 0, magic = 0;
-        if (x1 > x0 && yb > ya) {
-            w = x1 - x0;
-            n = w * (yb - ya);
-            first = (ya - r0) * gx + x0;
-            magic = w > 1 ? 0xFFFFFFFFu / w + 1u : 0u;      // ceil(2^32 / w): l / w == umulhi(l, magic) while l * w < 2^32
+        clip_rect(make_uint2(g.x, g.y), s0, s1, x0, x1, ya, yb);
+        const bool hit = x1 > x0 && yb > ya;
+        const uint32_t bits = __ballot_sync(0xffffffffu, hit);
+        if (bits == 0) continue;
+        if (hit) {
+            const uint32_t w = x1 - x0;
+            par[__popc(bits & lt)] = make_uint4(g.w, (ya - r0) * gx + x0, (w * (yb - ya)) | ((gx - w) << 21), g.z);
         }
-        uint32_t bits = __ballot_sync(0xffffffffu, n != 0);
-        while (bits != 0) {
-            const int b = __ffs((int)bits) - 1;
-            bits &= bits - 1;
-            const uint32_t g_id = __shfl_sync(0xffffffffu, id, b);
-            const uint32_t g_n = __shfl_sync(0xffffffffu, n, b);
-            const uint32_t g_w = __shfl_sync(0xffffffffu, w, b);
-            const uint32_t g_first = __shfl_sync(0xffffffffu, first, b);
-            const uint32_t g_magic = __shfl_sync(0xffffffffu, magic, b);
-            for (uint32_t base = 0; base < g_n; base += 32) {
-                const uint32_t l = base + lane;
-                if (l < g_n) {
-                    const uint32_t ry = g_w > 1 ? __umulhi(l, g_magic) : l;
-                    const uint32_t cell = g_first + ry * gx + (l - ry * g_w);
-                    const uint32_t slot = run[cell];
-                    run[cell] = slot + 1;
-                    point_list[slot] = g_id;
-                }
-                __syncwarp();            // the next Gaussian's lanes may read the counters this one wrote
-            }
+        __syncwarp();
+        const uint32_t cnt = __popc(bits);
+        for (uint32_t e = 0; e < cnt; e++) {
+            const uint4 q = par[e];
+            const uint32_t n = q.z & 0x1fffffu, skip = q.z >> 21;
+            append(q, n, skip, lane, lane2);
+            if (n > 32)                  // uniform and rare: a clipped rectangle of more than 32 tiles
+                for (uint32_t l = lane + 32; l - lane < n; l += 32) append(q, n, skip, l, l + l);
         }
+        __syncwarp();                    // everybody has read this batch's parameters
     }
 }
 
@@ -575,10 +752,13 @@ int launch_depth_order_and_count(const GsrParams& p, GeomState g, ImgState im, S
     const TileBinPlan pl = tile_bin_plan(p.P, p.W, p.H);
     {
         StageTimer tm(GSR_STAGE_TILE_COUNT, st);
-        GSR_LAUNCH(tile_count_kernel, dim3(pl.n_chunks, pl.n_bands), TB_COUNT_THREADS, 0, st, a, s.rects, s.counters, pl,
-                                                      s.tile_chunk, s.srects);
+        GSR_LAUNCH(tile_weights_kernel, pl.n_wblocks, 256, 0, st, a, s.rects, s.counters, pl.wblock, s.srects, s.tile_weights);
+        GSR_LAUNCH(tile_bounds_kernel, 1, TB_SCAN_THREADS, 0, st, s.tile_weights, pl.n_wblocks, pl.wblock, s.counters,
+                                                      pl.n_chunks, s.tile_bounds);
+        GSR_LAUNCH(tile_count_kernel, dim3(pl.n_chunks, pl.n_bands), TB_COUNT_THREADS, 0, st, s.srects, s.tile_bounds, pl,
+                                                      s.tile_chunk);
         GSR_LAUNCH(tile_chunk_prefix_kernel, div_up(pl.T, 32), 32 * TB_CP_GROUPS, 0, st, s.tile_chunk, pl, s.tile_total);
-        GSR_LAUNCH(tile_ranges_kernel, 1, TB_SCAN_THREADS, 0, st, s.tile_total, pl.T, im.ranges);
+        GSR_LAUNCH(tile_ranges_kernel, 1, TB_SCAN_THREADS, 0, st, s.tile_total, pl, im.ranges, s.tile_start, s.tile_stripes);
     }
     return check_stage("tile counts", p.debug, st);
 }
@@ -589,8 +769,8 @@ int launch_tile_lists(const GsrParams& p, GeomState g, ImgState im, BinState b, 
     const TileBinPlan pl = tile_bin_plan(p.P, p.W, p.H);
     {
         StageTimer tm(GSR_STAGE_TILE_FILL, st);
-        GSR_LAUNCH(tile_fill_kernel, dim3(pl.n_chunks, pl.n_bands), 32, 0, st, s.depth_a, s.srects, s.counters, pl,
-                                                     s.tile_chunk, im.ranges, b.point_list);
+        GSR_LAUNCH(tile_fill_kernel, dim3(pl.n_chunks, pl.n_bands), 32 * TB_FILL_WARPS, 0, st, s.srects,
+                                                     s.tile_bounds, pl, s.tile_chunk, s.tile_start, s.tile_stripes, b.point_list);
     }
     return check_stage("tile lists", p.debug, st);
 }

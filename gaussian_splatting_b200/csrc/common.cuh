@@ -124,10 +124,14 @@ constexpr int TB_MAX_BAND_ROWS = 512;
 constexpr int TB_MAX_GX = 2048;                          // widest tile grid (32 768 px)
 constexpr int TB_COUNT_CELLS = 10304;                    // difference grid: ((gx + 1) | 1) x (band_rows + 1) <= this
 constexpr int TB_COUNT_THREADS = 256;
-constexpr int TB_TARGET_UNITS = 888;                     // 148 SMs x 6 resident single-warp CTAs of the fill kernel
+#ifndef GSR_TB_TARGET_UNITS
+#define GSR_TB_TARGET_UNITS 888                          // 148 SMs x 6 resident CTAs of the fill kernel (37 KB of shared memory each)
+#endif
+constexpr int TB_TARGET_UNITS = GSR_TB_TARGET_UNITS;
 constexpr int TB_MIN_CHUNK = 64;                         // Gaussians
+constexpr int TB_MAX_WBLOCKS = 4096;                     // weight blocks (multiples of 256 depth ranks) used to balance the chunks
 
-struct TileBinPlan { uint32_t gx, gy, T, band_rows, n_bands, n_chunks, stride; };
+struct TileBinPlan { uint32_t gx, gy, T, band_rows, n_bands, n_chunks, stride, wblock, n_wblocks; };
 inline TileBinPlan tile_bin_plan(int P, int W, int H) {
     TileBinPlan pl;
     pl.gx = (uint32_t)(W + TILE_X - 1) / TILE_X;
@@ -145,6 +149,9 @@ inline TileBinPlan tile_bin_plan(int P, int W, int H) {
     if (chunks > most) chunks = most;
     if (chunks < 1) chunks = 1;
     pl.n_chunks = chunks;
+    const uint32_t Pn = (uint32_t)(P > 0 ? P : 1);
+    pl.wblock = ((Pn + TB_MAX_WBLOCKS - 1) / TB_MAX_WBLOCKS + 255u) / 256u * 256u;
+    pl.n_wblocks = (Pn + pl.wblock - 1) / pl.wblock;
     return pl;
 }
 
@@ -161,12 +168,16 @@ struct Scratch {            // only live inside one forward or backward call; do
     uint2*    rects;        // P   packed rect {min.x | min.y<<16, max.x | max.y<<16}
     uint64_t* depth_a;      // P   depth_bits<<32 | id   (ping; holds the depth order after the sort)
     uint64_t* depth_b;      // P   (pong)
-    uint2*    srects;       // P   rectangles in depth order
+    uint4*    srects;       // P   {rect.x, rect.y, div_magic(width), id} in depth order
     uint32_t* sort_ctl;     // onesweep control words, see SORT_CTL_* (zeroed per sort)
     uint32_t* hist;         // 256 * blocks(P)   (3-kernel radix pass, P >= 2^30)
     uint32_t* digit_tot;    // 256
     uint32_t* tile_chunk;   // n_chunks * T   per (chunk, tile): count, then first slot relative to the tile's start
     uint32_t* tile_total;   // T
+    uint32_t* tile_start;   // T + 1                 first slot of every tile's list (empty tiles included)
+    uint32_t* tile_stripes; // n_bands * 32          tile rows at which the filling kernel cuts a band between its warps
+    uint32_t* tile_weights; // TB_MAX_WBLOCKS        list-filling steps per weight block of depth ranks
+    uint32_t* tile_bounds;  // n_chunks + 1          first depth rank of every chunk
     int32_t*  counters;     // 8   see CNT_*
     // backward
     float*    acc;          // P * ACC_FLOATS
@@ -181,12 +192,16 @@ struct Scratch {            // only live inside one forward or backward call; do
         s.rects = c.take<uint2>(Pn);
         s.depth_a = c.take<uint64_t>(Pn);
         s.depth_b = c.take<uint64_t>(Pn);
-        s.srects = c.take<uint2>(Pn);
+        s.srects = c.take<uint4>(Pn);
         s.sort_ctl = c.take<uint32_t>(sort_ctl_words(nb));
         s.hist = c.take<uint32_t>(256 * nb);
         s.digit_tot = c.take<uint32_t>(256);
         s.tile_chunk = c.take<uint32_t>((size_t)pl.n_chunks * pl.T);
         s.tile_total = c.take<uint32_t>(pl.T);
+        s.tile_start = c.take<uint32_t>((size_t)pl.T + 1);
+        s.tile_stripes = c.take<uint32_t>((size_t)pl.n_bands * 32);
+        s.tile_weights = c.take<uint32_t>(TB_MAX_WBLOCKS);
+        s.tile_bounds = c.take<uint32_t>((size_t)pl.n_chunks + 1);
         s.acc = c.take<float>(Pn * ACC_FLOATS);
         s.band_list = c.take<uint32_t>(Pn);
         s.band_ctl = c.take<uint32_t>(BAND_CTL_WORDS);

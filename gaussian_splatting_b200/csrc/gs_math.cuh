@@ -170,4 +170,24 @@ GSR_HD void get_rect(float px, float py, int max_radius, int gx, int gy,
 #define GSR_SH_C3_5 1.445305721320277f
 #define GSR_SH_C3_6 -0.5900435899266435f
 
+// ---- the model's activations (scene/gaussian_model.py:32-55), applied in registers when GsrParams.raw_inputs asks
+// for it.  Same float functions torch's CUDA kernels call: expf for torch.exp, 1 / (1 + expf(-x)) for torch.sigmoid,
+// x / max(||x||_2, 1e-12) for torch.nn.functional.normalize.
+__device__ __forceinline__ float3 act_scale(float3 raw) { return make_float3(expf(raw.x), expf(raw.y), expf(raw.z)); }
+__device__ __forceinline__ float act_opacity(float raw) { return 1.0f / (1.0f + expf(-raw)); }
+__device__ __forceinline__ float4 act_rotation(float4 raw, float* inv_norm) {
+    const float n = sqrtf(raw.x * raw.x + raw.y * raw.y + raw.z * raw.z + raw.w * raw.w);
+    const float inv = 1.0f / fmaxf(n, 1e-12f);
+    if (inv_norm) *inv_norm = inv;
+    return make_float4(raw.x * inv, raw.y * inv, raw.z * inv, raw.w * inv);
+}
+// their backward: gradient w.r.t. the raw parameter from the gradient w.r.t. the activated one
+__device__ __forceinline__ float3 act_scale_bwd(float3 s, float3 g) { return make_float3(g.x * s.x, g.y * s.y, g.z * s.z); }
+__device__ __forceinline__ float act_opacity_bwd(float o, float g) { return g * o * (1.0f - o); }
+__device__ __forceinline__ float4 act_rotation_bwd(float4 q, float inv_norm, float4 g) {
+    const float d = q.x * g.x + q.y * g.y + q.z * g.z + q.w * g.w;      // the component along q does not move q / |q|
+    return make_float4((g.x - q.x * d) * inv_norm, (g.y - q.y * d) * inv_norm, (g.z - q.z * d) * inv_norm,
+                       (g.w - q.w * d) * inv_norm);
+}
+
 }  // namespace gsr

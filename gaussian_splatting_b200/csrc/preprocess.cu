@@ -98,6 +98,8 @@ preprocess_fwd_kernel(GsrParams p, float focal_x, float focal_y, int gx, int gy,
             } else {
                 float3 sc = make_float3(p.scales[3 * idx], p.scales[3 * idx + 1], p.scales[3 * idx + 2]);
                 float4 rot = reinterpret_cast<const float4*>(p.rotations)[idx];
+                if (p.raw_inputs & GSR_RAW_SCALES) sc = act_scale(sc);
+                if (p.raw_inputs & GSR_RAW_ROTATIONS) rot = act_rotation(rot, nullptr);
                 compute_cov3D(sc, p.scale_modifier, rot, cov3D);
             }
             float3 cov = compute_cov2D(p_orig, focal_x, focal_y, p.tanfovx, p.tanfovy, cov3D, s_view, nullptr);
@@ -123,7 +125,8 @@ preprocess_fwd_kernel(GsrParams p, float focal_x, float focal_y, int gx, int gy,
                 if ((maxx - minx) * (maxy - miny) != 0) {
                     visible = true;
                     depth = p_view.z;
-                    opacity_aa = p.opacities[idx] * h_convolution_scaling;
+                    const float o_raw = p.opacities[idx];
+                    opacity_aa = ((p.raw_inputs & GSR_RAW_OPACITIES) ? act_opacity(o_raw) : o_raw) * h_convolution_scaling;
                 }
             }
         }

@@ -367,12 +367,15 @@ preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord*
         float cov3D[6];
         float3 sc = {0.f, 0.f, 0.f};
         float4 rot = {0.f, 0.f, 0.f, 0.f};
+        float rot_inv_norm = 1.f;
         if (p.cov3D_precomp != nullptr) {
 #pragma unroll
             for (int k = 0; k < 6; k++) cov3D[k] = p.cov3D_precomp[6 * idx + k];
         } else {
             sc = make_float3(p.scales[3 * idx], p.scales[3 * idx + 1], p.scales[3 * idx + 2]);
             rot = reinterpret_cast<const float4*>(p.rotations)[idx];
+            if (p.raw_inputs & GSR_RAW_SCALES) sc = act_scale(sc);
+            if (p.raw_inputs & GSR_RAW_ROTATIONS) rot = act_rotation(rot, &rot_inv_norm);
             compute_cov3D(sc, p.scale_modifier, rot, cov3D);
         }
         Cov2DCtx ctx;
@@ -386,7 +389,7 @@ preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord*
         constexpr float h_var = 0.3f;
         float d_inside_root = 0.f;
         dL_dopacity = dL_dopacity_v;
-        const float opacity = p.opacities[idx];
+        const float opacity = (p.raw_inputs & GSR_RAW_OPACITIES) ? act_opacity(p.opacities[idx]) : p.opacities[idx];
         float o_blend = opacity;                     // what the blend multiplied G with (forward.cu:344)
         if (p.antialiasing) {
             const float det_cov = c_xx * c_yy - c_xy * c_xy;
@@ -482,6 +485,10 @@ preprocess_bwd_kernel(GsrParams p, float focal_x, float focal_y, const GsRecord*
         dL_dmean.z += (proj[8] * m_w - proj[11] * mul1) * dL_dmean2D.x + (proj[9] * m_w - proj[11] * mul2) * dL_dmean2D.y;
 
         if (p.scales != nullptr) cov3D_backward(sc, p.scale_modifier, rot, dL_dcov, &dL_dscale, &dL_drot);
+        // fused activations (GsrParams.raw_inputs): gradients w.r.t. the raw parameters, before any store
+        if (p.raw_inputs & GSR_RAW_SCALES) dL_dscale = act_scale_bwd(sc, dL_dscale);
+        if (p.raw_inputs & GSR_RAW_ROTATIONS) dL_drot = act_rotation_bwd(rot, rot_inv_norm, dL_drot);
+        if (p.raw_inputs & GSR_RAW_OPACITIES) dL_dopacity = act_opacity_bwd(opacity, dL_dopacity);
     }
 
     // SH rows of the warp in shared memory.  Layouts (RowLayout): dense rows of `sh_row` floats (vector path),

@@ -152,9 +152,10 @@ def _f32c(t, name):
 
 
 def _params(P, M, rs, bg, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
-            viewmatrix, projmatrix, campos, sh_dc=None):
+            viewmatrix, projmatrix, campos, sh_dc=None, raw=0):
     p = GsrParams()
     p.P, p.D, p.M = P, int(rs.sh_degree), M
+    p.raw_inputs = int(raw)
     p.W, p.H = int(rs.image_width), int(rs.image_height)
     p.tanfovx, p.tanfovy = float(rs.tanfovx), float(rs.tanfovy)
     p.scale_modifier = float(rs.scale_modifier)
@@ -168,12 +169,13 @@ def _params(P, M, rs, bg, means3D, sh, colors_precomp, opacities, scales, rotati
 
 
 def _forward_native(rs, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
-                    state_out=None, dc=None):
+                    state_out=None, dc=None, raw=0):
     """Role of _C.rasterize_gaussians (ext.cpp:16 -> rasterize_points.cu:45-146).
 
     Returns (num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, invdepths).
     state_out: optional dict that receives views of the binning / image state (parity tests).
-    dc: split SH storage — degree-0 coefficients (P,1,3); `sh` then holds coefficients 1..M-1."""
+    dc: split SH storage — degree-0 coefficients (P,1,3); `sh` then holds coefficients 1..M-1.
+    raw: bit mask _lib.RAW_*: scales / rotations / opacities are the model's raw parameters (fused activations)."""
     lib = _lib.load()
     if means3D.ndim != 2 or means3D.shape[1] != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
@@ -204,7 +206,7 @@ def _forward_native(rs, means3D, sh, colors_precomp, opacities, scales, rotation
         dc = _f32c(dc, "dc")
         M = (sh.shape[1] if sh is not None else 0) + (1 if dc is not None else 0)
         p = _params(P, M, rs, bg, means3D, sh, colors_precomp, opacities, scales, rotations,
-                    cov3Ds_precomp, viewmatrix, projmatrix, campos, dc)
+                    cov3Ds_precomp, viewmatrix, projmatrix, campos, dc, raw)
 
         ws = _workspace(device)
         stream = torch.cuda.current_stream(device)
@@ -276,7 +278,7 @@ def _grad_layout(P, M, colors_precomp, cov3Ds_precomp, sh, scales, rotations, sp
 
 
 def _backward_native(rs, means3D, radii, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
-                     grad_out_color, grad_out_depth, sh, geom, R, binb, img, dc=None):
+                     grad_out_color, grad_out_depth, sh, geom, R, binb, img, dc=None, raw=0):
     """Role of _C.rasterize_gaussians_backward (rasterize_points.cu:149-248).
 
     Returns (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales,
@@ -311,7 +313,7 @@ def _backward_native(rs, means3D, radii, colors_precomp, opacities, scales, rota
         if grad_out_color is None:
             grad_out_color = torch.zeros((3, H, W), **f32)
         p = _params(P, M, rs, bg, means3D, sh_c, colors_precomp, opacities, scales, rotations,
-                    cov3Ds_precomp, viewmatrix, projmatrix, campos, dc_c)
+                    cov3Ds_precomp, viewmatrix, projmatrix, campos, dc_c, raw)
 
         ws = _workspace(device)
         stream = torch.cuda.current_stream(device)
@@ -376,17 +378,19 @@ def _backward_native(rs, means3D, radii, colors_precomp, opacities, scales, rota
 
 
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
-                        raster_settings, dc=None):
+                        raster_settings, dc=None, raw=0):
     return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
-                                     cov3Ds_precomp, raster_settings, dc)
+                                     cov3Ds_precomp, raster_settings, dc, raw)
 
 
 class _RasterizeGaussians(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
-                raster_settings, dc=None):
+                raster_settings, dc=None, raw=0):
         """The reference's nine arguments (__init__.py:49-62) + `dc`: split SH storage (degree-0 coefficients
-        (P,1,3) separate from `sh` = coefficients 1..M-1), read by the kernels in place — no concatenation."""
+        (P,1,3) separate from `sh` = coefficients 1..M-1), read by the kernels in place — no concatenation;
+        + `raw`: bit mask of the inputs that are the model's raw parameters (activations fused into the kernels,
+        gradients returned w.r.t. the raw parameters)."""
         split = dc is not None
         _trace("fwd0", means3D.device)
         red = _gradient_reducer
@@ -397,8 +401,9 @@ class _RasterizeGaussians(torch.autograd.Function):
             xchg = hasattr(red, "use_exchange") and red.use_exchange(names)
             red.prepare(shapes, means3D.device, exchange_P=means3D.shape[0] if xchg else None)
         num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, invdepths = _forward_native(
-            raster_settings, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, dc=dc)
+            raster_settings, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, dc=dc, raw=raw)
         ctx.raster_settings = raster_settings
+        ctx.raw = raw
         ctx.num_rendered = num_rendered
         ctx.split = split
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, opacities,
@@ -417,7 +422,7 @@ class _RasterizeGaussians(torch.autograd.Function):
         (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh,
          grad_scales, grad_rotations, *grad_dc) = _backward_native(
             raster_settings, means3D, radii, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
-            grad_out_color, grad_out_depth, sh, geomBuffer, num_rendered, binningBuffer, imgBuffer, dc=dc)
+            grad_out_color, grad_out_depth, sh, geomBuffer, num_rendered, binningBuffer, imgBuffer, dc=dc, raw=ctx.raw)
         grads = (
             grad_means3D,
             grad_means2D,
@@ -429,6 +434,7 @@ class _RasterizeGaussians(torch.autograd.Function):
             grad_cov3Ds_precomp,
             None,
             grad_dc[0] if grad_dc else None,
+            None,
         )
         return grads
 
@@ -458,8 +464,15 @@ class GaussianRasterizer(nn.Module):
         return visible
 
     def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
-                cov3D_precomp=None, dc=None):
+                cov3D_precomp=None, dc=None, raw_inputs=0):
+        """raw_inputs (an extension, default off): bit mask RAW_SCALES | RAW_ROTATIONS | RAW_OPACITIES — the named
+        inputs are the model's raw parameters (log-scales, unnormalised quaternions, opacity logits); the kernels
+        apply exp / normalize / sigmoid themselves and return gradients w.r.t. the raw parameters.  Inputs that are
+        `activations.Deferred` proxies (what activations.install(GaussianModel) makes get_scaling / get_rotation /
+        get_opacity return) set their bit by themselves."""
         raster_settings = self.raster_settings
+        from . import activations as _act
+        opacities, scales, rotations, raw_inputs = _act.unwrap(opacities, scales, rotations, raw_inputs)
 
         # `dc=` is the keyword render() uses when SparseGaussianAdam is importable
         # (gaussian_renderer/__init__.py:115-125, separate_sh): degree-0 coefficients (P,1,3) and the rest
@@ -503,4 +516,5 @@ class GaussianRasterizer(nn.Module):
             cov3D_precomp,
             raster_settings,
             dc,
+            int(raw_inputs),
         )

@@ -53,6 +53,17 @@ extern "C" {
  * Field meaning follows GaussianRasterizationSettings
  * (DGR/diff_gaussian_rasterization/__init__.py:151-180) and the argument list
  * of Rasterizer::forward (rasterizer_impl.cu:227-254). */
+/* Fused activations.  The reference's model stores log-scales, unnormalised quaternions and
+ * opacity logits and activates them with three torch kernels per step before the rasterizer sees them
+ * (scene/gaussian_model.py:32-55,130-157: torch.exp, torch.nn.functional.normalize, torch.sigmoid; called from
+ * gaussian_renderer/__init__.py:77,89-90), and autograd runs their three backward kernels afterwards.  With a bit
+ * set, the corresponding input of GsrParams is the RAW parameter: the per-Gaussian kernels apply exp /
+ * x / max(|x|, 1e-12) / 1 / (1 + exp(-x)) in registers, and the backward returns the gradient with respect to the
+ * raw parameter (dL_dscales, dL_drotations, dL_dopacity and the exchange records alike). */
+#define GSR_RAW_SCALES     1
+#define GSR_RAW_ROTATIONS  2
+#define GSR_RAW_OPACITIES  4
+
 typedef struct GsrParams {
     int32_t P;                 /* number of Gaussians */
     int32_t D;                 /* active SH degree 0..3 */
@@ -63,7 +74,7 @@ typedef struct GsrParams {
     int32_t prefiltered;
     int32_t antialiasing;
     int32_t debug;             /* 1: synchronise + check after every stage and name the stage */
-    int32_t reserved0;
+    int32_t raw_inputs;        /* bit mask GSR_RAW_*: the kernels apply the model's activations themselves (below) */
 
     /* device inputs (fp32) */
     const float* background;     /* 3 */

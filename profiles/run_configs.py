@@ -75,11 +75,13 @@ def fwd_bwd_fns(module, gs, s, dev):
     return fwd, fwdbwd
 
 
-def train_step_fn(module, gs, s, dev, sparse_adam=False, ssim=None):
+def train_step_fn(module, gs, s, dev, sparse_adam=False, ssim=None, fused_act=False, fused_loss=False):
     """C2: the per-iteration work of train.py:143-251 without datasets.
     sparse_adam: the fork's accelerated branch (separate_sh / dc= keyword, optimizer.step(visible, N)).
     ssim: a fused_ssim(img1, img2) callable -> the full loss of train.py:155-162,
-    0.8 * L1 + 0.2 * (1 - SSIM), plus the inverse-depth L1 term."""
+    0.8 * L1 + 0.2 * (1 - SSIM), plus the inverse-depth L1 term.
+    fused_act: the kernels apply exp / normalize / sigmoid themselves (raw_inputs, ours only).
+    fused_loss: gaussian_splatting_b200.loss.training_loss — the whole loss in one forward and one backward launch."""
     P = gs["means3D"].shape[0]
     nnp = torch.nn.Parameter
     xyz = nnp(gs["means3D"].to(dev))
@@ -101,9 +103,16 @@ def train_step_fn(module, gs, s, dev, sparse_adam=False, ssim=None):
     def step():
         m2 = torch.zeros(P, 3, device=dev, requires_grad=True)
         kw = dict(dc=f_dc, shs=f_rest) if sparse_adam else dict(shs=torch.cat((f_dc, f_rest), dim=1))
-        color, radii, invd = rast(means3D=xyz, means2D=m2, opacities=torch.sigmoid(opacity),
-                                  scales=torch.exp(scaling), rotations=torch.nn.functional.normalize(rotation), **kw)
-        if ssim is None:
+        if fused_act:
+            color, radii, invd = rast(means3D=xyz, means2D=m2, opacities=opacity, scales=scaling, rotations=rotation,
+                                      raw_inputs=7, **kw)
+        else:
+            color, radii, invd = rast(means3D=xyz, means2D=m2, opacities=torch.sigmoid(opacity),
+                                      scales=torch.exp(scaling), rotations=torch.nn.functional.normalize(rotation), **kw)
+        if fused_loss:
+            from gaussian_splatting_b200 import loss as _loss
+            loss = _loss.training_loss(color, target, 0.2, invdepth=invd, mono_invdepth=target_d, depth_weight=0.1)
+        elif ssim is None:
             loss = (color - target).abs().mean() + 0.1 * (invd - target_d).abs().mean()
         else:
             loss = 0.8 * (color - target).abs().mean() + 0.2 * (1.0 - ssim(color.unsqueeze(0), target.unsqueeze(0))) \
@@ -168,6 +177,16 @@ def main():
                     # ours = SparseGaussianAdam + our fused SSIM, reference = torch Adam + its own fused-ssim CUDA
                     r["train_step_ssim_ms"] = round(timeit(train_step_fn(
                         m, gs, s, dev, sparse_adam=hasattr(m, "SparseGaussianAdam"), ssim=ssim_of[mname])), 3)
+                if mname == "ours":
+                    r["train_step_sparse_adam_fused_act_ms"] = round(timeit(train_step_fn(
+                        m, gs, s, dev, sparse_adam=True, fused_act=True)), 3)
+                    r["train_step_ssim_fused_act_ms"] = round(timeit(train_step_fn(
+                        m, gs, s, dev, sparse_adam=True, ssim=ssim_of.get("ours"), fused_act=True)), 3)
+                    try:
+                        r["train_step_fused_act_fused_loss_ms"] = round(timeit(train_step_fn(
+                            m, gs, s, dev, sparse_adam=True, fused_act=True, fused_loss=True)), 3)
+                    except Exception as ex:  # noqa: BLE001
+                        r["train_step_fused_act_fused_loss_ms"] = f"unavailable: {ex}"
             row[mname] = r
             torch.cuda.empty_cache()
         if "reference" in row:

@@ -98,9 +98,10 @@ def test_python_surface_matches_reference():
     assert issubclass(SparseGaussianAdam, torch.optim.Adam)
     assert list(inspect.signature(SparseGaussianAdam.__init__).parameters) == ["self", "params", "lr", "eps"]
     assert list(inspect.signature(SparseGaussianAdam.step).parameters)[:3] == ["self", "visibility", "N"]
-    # the fork's positional order of GaussianRasterizer.forward (__init__.py:218) with `dc` appended
+    # the fork's positional order of GaussianRasterizer.forward (__init__.py:218) with `dc` and `raw_inputs` appended
     assert list(inspect.signature(dgr.GaussianRasterizer.forward).parameters) == [
-        "self", "means3D", "means2D", "opacities", "shs", "colors_precomp", "scales", "rotations", "cov3D_precomp", "dc"]
+        "self", "means3D", "means2D", "opacities", "shs", "colors_precomp", "scales", "rotations", "cov3D_precomp", "dc",
+        "raw_inputs"]
 
 
 def test_fused_ssim_surface_matches_reference():

@@ -1,0 +1,53 @@
+"""GPU parity of the fused activations: the kernels take the model's raw parameters
+(GsrParams.raw_inputs) and return raw gradients.  Oracle: the reference's own activation functions
+(scene/gaussian_model.py:44-55: torch.exp, torch.nn.functional.normalize, torch.sigmoid) applied by torch on the same
+GPU + torch autograd around the unfused call."""
+import numpy as np
+import pytest
+import torch
+
+from tests.helpers import rel_err, settings_for, small_scene
+from tests.test_hostpath_emul_cpu import _raw_model_params
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("P,W,H,aa,split", [(3000, 160, 120, True, False), (200000, 800, 600, False, True)])
+@pytest.mark.parametrize("how", ["keyword", "deferred"])
+def test_raw_leaf_gradients_match_torch_autograd(P, W, H, aa, split, how):
+    import diff_gaussian_rasterization as dgr
+    from gaussian_splatting_b200 import activations as act
+    gs, s = small_scene(P=P, W=W, H=H, seed=23, antialiasing=aa, bg=(0.2, 0.1, 0.4))
+    raw_s, raw_r, raw_o = _raw_model_params(gs)
+    rast = dgr.GaussianRasterizer(settings_for(dgr, s))
+    g = torch.Generator().manual_seed(1)
+    dc = (torch.randn(3, H, W, generator=g) / (W * H) ** 0.5).cuda()
+    dd = (torch.randn(1, H, W, generator=g) / (W * H) ** 0.5).cuda()
+    outs = []
+    for fused in (False, True):
+        ls, lr, lo = (t.clone().cuda().requires_grad_(True) for t in (raw_s, raw_r, raw_o))
+        lm = gs["means3D"].clone().cuda().requires_grad_(True)
+        lsh = gs["shs"].clone().cuda().requires_grad_(True)
+        ldc = gs["shs"][:, :1].clone().cuda().requires_grad_(True)
+        lrest = gs["shs"][:, 1:].clone().cuda().requires_grad_(True)
+        m2 = torch.zeros(P, 3, device="cuda", requires_grad=True)
+        if not fused:
+            kw = dict(opacities=torch.sigmoid(lo), scales=torch.exp(ls), rotations=torch.nn.functional.normalize(lr))
+        elif how == "keyword":
+            kw = dict(opacities=lo, scales=ls, rotations=lr, raw_inputs=act.RAW_SCALES | act.RAW_ROTATIONS | act.RAW_OPACITIES)
+        else:
+            kw = dict(opacities=act.Deferred(lo, torch.sigmoid, act.RAW_OPACITIES), scales=act.Deferred(ls, torch.exp, act.RAW_SCALES),
+                      rotations=act.Deferred(lr, torch.nn.functional.normalize, act.RAW_ROTATIONS))
+        kw.update(dict(dc=ldc, shs=lrest) if split else dict(shs=lsh))
+        color, radii, invd = rast(means3D=lm, means2D=m2, **kw)
+        torch.autograd.backward([color, invd], [dc, dd])
+        sh_grad = torch.cat((ldc.grad, lrest.grad), 1) if split else lsh.grad
+        outs.append(dict(color=color.detach(), invd=invd.detach(), radii=radii, s=ls.grad, r=lr.grad, o=lo.grad,
+                         m=lm.grad, sh=sh_grad, m2=m2.grad))
+    a, b = outs
+    # the same float functions run in both paths (expf, 1 / (1 + expf(-x)), x / max(|x|, eps)); a radius could still
+    # differ where torch's norm reduction rounds the quaternion length differently: allow a handful
+    assert (a["radii"] != b["radii"]).sum().item() <= max(2, P // 100000)
+    assert (a["color"] - b["color"]).abs().max().item() <= 2e-5 and (a["invd"] - b["invd"]).abs().max().item() <= 2e-5
+    for k in ("s", "r", "o", "m", "sh", "m2"):
+        assert rel_err(b[k].cpu().numpy(), a[k].cpu().numpy()) < 1e-4, k

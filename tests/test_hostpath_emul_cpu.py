@@ -132,6 +132,104 @@ def test_dc_keyword_equals_concatenated_call(emulated_cuda):
         assert rel_err(a.numpy(), b.numpy()) < 1e-5
 
 
+def _raw_model_params(gs, seed=0):
+    """The model's raw leaves for a scene's activated values: log-scales, quaternions of arbitrary length, logits."""
+    g = torch.Generator().manual_seed(seed)
+    raw_s = gs["scales"].log()
+    raw_r = gs["rotations"] * (0.3 + 2.0 * torch.rand(gs["rotations"].shape[0], 1, generator=g))
+    o = gs["opacities"].clamp(1e-4, 1 - 1e-4)
+    raw_o = (o / (1 - o)).log()
+    return raw_s, raw_r, raw_o
+
+
+@pytest.mark.parametrize("how", ["keyword", "deferred"])
+def test_fused_activations_match_torch_autograd(emulated_cuda, how):
+    """GsrParams.raw_inputs: the kernels activate the raw parameters themselves and return raw gradients.  Oracle: the
+    reference's own activations (torch.exp / normalize / sigmoid, scene/gaussian_model.py:44-55) + torch autograd around
+    the unfused call."""
+    import diff_gaussian_rasterization as dgr
+    from gaussian_splatting_b200 import activations as act
+    from tests.helpers import settings_for
+    W, H, P = 64, 48, 400
+    gs, s = small_scene(P=P, W=W, H=H, seed=17, antialiasing=True, bg=(0.2, 0.1, 0.4))
+    raw_s, raw_r, raw_o = _raw_model_params(gs)
+    rast = dgr.GaussianRasterizer(settings_for(dgr, s, "cpu"))
+    g = torch.Generator().manual_seed(1)
+    dc, dd = torch.randn(3, H, W, generator=g) / 100, torch.randn(1, H, W, generator=g) / 100
+    outs = []
+    for fused in (False, True):
+        ls, lr, lo = (t.clone().requires_grad_(True) for t in (raw_s, raw_r, raw_o))
+        lm, lsh = gs["means3D"].clone().requires_grad_(True), gs["shs"].clone().requires_grad_(True)
+        m2 = torch.zeros(P, 3, requires_grad=True)
+        if not fused:
+            kw = dict(opacities=torch.sigmoid(lo), scales=torch.exp(ls), rotations=torch.nn.functional.normalize(lr))
+        elif how == "keyword":
+            kw = dict(opacities=lo, scales=ls, rotations=lr, raw_inputs=act.RAW_SCALES | act.RAW_ROTATIONS | act.RAW_OPACITIES)
+        else:
+            kw = dict(opacities=act.Deferred(lo, torch.sigmoid, act.RAW_OPACITIES), scales=act.Deferred(ls, torch.exp, act.RAW_SCALES),
+                      rotations=act.Deferred(lr, torch.nn.functional.normalize, act.RAW_ROTATIONS))
+        color, radii, invd = rast(means3D=lm, means2D=m2, shs=lsh, **kw)
+        torch.autograd.backward([color, invd], [dc, dd])
+        outs.append(dict(color=color.detach(), invd=invd.detach(), radii=radii, s=ls.grad, r=lr.grad, o=lo.grad,
+                         m=lm.grad, sh=lsh.grad, m2=m2.grad))
+    a, b = outs
+    assert torch.equal(a["radii"], b["radii"])
+    assert (a["color"] - b["color"]).abs().max() <= 1e-5 and (a["invd"] - b["invd"]).abs().max() <= 1e-5
+    for k in ("s", "r", "o", "m", "sh", "m2"):
+        assert rel_err(b[k].numpy(), a[k].numpy()) < 1e-4, k
+
+
+def test_deferred_activation_behaves_like_the_tensor_elsewhere():
+    """What the reference does with get_scaling / get_opacity outside render() (gaussian_model.py:324,521-535,612-619)
+    works on the proxies that activations.install() makes the properties return; a model with other activation
+    functions keeps the reference's behaviour."""
+    from gaussian_splatting_b200 import activations as act
+
+    class Model:                                       # the three properties of scene/gaussian_model.py:130-157
+        def __init__(self):
+            g = torch.Generator().manual_seed(0)
+            self._scaling = torch.randn(50, 3, generator=g)
+            self._rotation = torch.randn(50, 4, generator=g)
+            self._opacity = torch.randn(50, 1, generator=g)
+            self.scaling_activation, self.opacity_activation = torch.exp, torch.sigmoid
+            self.rotation_activation = torch.nn.functional.normalize
+
+        @property
+        def get_scaling(self):
+            return self.scaling_activation(self._scaling)
+
+        @property
+        def get_rotation(self):
+            return self.rotation_activation(self._rotation)
+
+        @property
+        def get_opacity(self):
+            return self.opacity_activation(self._opacity)
+
+    ref = Model()
+    want = dict(s=ref.get_scaling, r=ref.get_rotation, o=ref.get_opacity)
+    act.install(Model)
+    try:
+        m = Model()
+        s, r, o = m.get_scaling, m.get_rotation, m.get_opacity
+        assert all(isinstance(t, act.Deferred) for t in (s, r, o))
+        assert torch.equal(torch.max(s, dim=1).values, torch.max(want["s"], dim=1).values)
+        mask = torch.max(s, dim=1).values > 1.0
+        assert torch.equal(s[mask].repeat(2, 1), want["s"][mask].repeat(2, 1))
+        assert torch.equal(s.max(dim=1).values > 0.5, want["s"].max(dim=1).values > 0.5)
+        assert torch.equal((o < 0.4).squeeze(), (want["o"] < 0.4).squeeze())
+        assert torch.equal(torch.min(o, torch.ones_like(o) * 0.01), torch.min(want["o"], torch.ones_like(want["o"]) * 0.01))
+        assert torch.equal(s / 1.6, want["s"] / 1.6) and o.shape == (50, 1) and len(r) == 50
+        assert torch.equal(r.value(), want["r"])
+        o2, s2, r2, bits = act.unwrap(o, s, r)
+        assert o2 is m._opacity and s2 is m._scaling and r2 is m._rotation and bits == 7
+        m.scaling_activation = torch.nn.functional.softplus          # not what the kernels implement: no proxy
+        assert isinstance(m.get_scaling, torch.Tensor) and isinstance(m.get_opacity, torch.Tensor)
+    finally:
+        act.uninstall(Model)
+    assert isinstance(Model().get_scaling, torch.Tensor)
+
+
 def test_sparse_adam_and_fused_ssim(emulated_cuda):
     import diff_gaussian_rasterization as dgr
     import fused_ssim as fs
