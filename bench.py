@@ -207,7 +207,10 @@ def make_steps(module, wl, device, flat=None):
             loss_ready[slot].synchronize()
             losses.append(float(loss_host[slot]))
 
-    def step_e2e():
+    def l1_losses(color, invd, tgt, tgt_d):
+        return (color - tgt).abs().mean() + 0.1 * (invd - tgt_d).abs().mean()
+
+    def step_e2e(loss_fn=l1_losses):
         clear()
         main = torch.cuda.current_stream(device)
         cam_dev.copy_(cam_host, non_blocking=True)          # 140 B: needed before the first kernel
@@ -225,7 +228,7 @@ def make_steps(module, wl, device, flat=None):
         main.wait_event(copied)
         tgt = tgt_dev[:3 * H * W].view(3, H, W)
         tgt_d = tgt_dev[3 * H * W:].view(1, H, W)
-        loss = (color - tgt).abs().mean() + 0.1 * (invd - tgt_d).abs().mean()
+        loss = loss_fn(color, invd, tgt, tgt_d)
         loss.backward()
         if flat is not None:
             flat.all_reduce()
@@ -595,6 +598,28 @@ def run_gpu_arm(args, module, impl, rank, world, local):
                                "backward, loss scalar copied to pinned memory every step and read by the host one step "
                                "late (event-guarded ring of two slots; the last one is drained inside the timed region); "
                                "Gaussian parameters stay resident (they are the model)"}
+    if ours and not args.no_e2e and world == 1:
+        # second figure (this repo only; the arms' common protocol above stays the headline): the same end-to-end step
+        # with the FULL loss of train.py:155-174 (0.8 L1 + 0.2 (1 - SSIM) + 0.1 inverse-depth L1), once as the
+        # reference's train.py would compute it on top of this repo's drop-in packages (torch L1 terms + fused_ssim)
+        # and once as one fused forward + one fused backward launch (gaussian_splatting_b200.loss)
+        import fused_ssim as _fs
+        from gaussian_splatting_b200 import loss as _loss
+
+        def full_unfused(color, invd, tgt, tgt_d):
+            return 0.8 * (color - tgt).abs().mean() + 0.2 * (1.0 - _fs.fused_ssim(color.unsqueeze(0), tgt.unsqueeze(0))) \
+                + 0.1 * (invd - tgt_d).abs().mean()
+
+        def full_fused(color, invd, tgt, tgt_d):
+            return _loss.training_loss(color, tgt, 0.2, invdepth=invd, mono_invdepth=tgt_d, depth_weight=0.1)
+
+        fig = {}
+        for name, fn in (("torch_l1_plus_fused_ssim", full_unfused), ("fused_training_loss", full_fused)):
+            ms_x, _, _ = timed_loop(lambda: step_e2e(fn), args.steps, 3, world, device, drain=step_e2e.drain)
+            fig[name] = round(1000.0 * args.steps / ms_x, 3)
+        fig["unit"] = UNIT
+        fig["what"] = "e2e protocol with the full loss of train.py:155-174 (lambda_dssim 0.2, depth weight 0.1)"
+        line["e2e_full_loss"] = fig
     if ours and world > 1:
         line["reduce_check"] = reduce_check(module, wl, device, world)
         line["trace_ms"] = traced_gaps(step, device)

@@ -64,6 +64,15 @@ class GsrSsimParams(C.Structure):
     ]
 
 
+class GsrLossParams(C.Structure):
+    _fields_ = [
+        ("image", _fp), ("gt", _fp), ("invdepth", _fp), ("mono_invdepth", _fp), ("depth_mask", _fp),
+        ("CH", C.c_int32), ("H", C.c_int32), ("W", C.c_int32),
+        ("lambda_dssim", C.c_float), ("depth_weight", C.c_float), ("C1", C.c_float), ("C2", C.c_float),
+        ("reserved", C.c_int32),
+    ]
+
+
 DENSIFY_COPY, DENSIFY_MOMENT, DENSIFY_XYZ, DENSIFY_SCALING = 0, 1, 2, 3
 DENSIFY_MAX_TENSORS = 24
 
@@ -99,7 +108,7 @@ EXPORTS = (
     "gsr_profile_enable", "gsr_profile_collect", "gsr_stage_name", "gsr_launch_count", "gsr_adam_update",
     "gsr_ssim_partials", "gsr_ssim_forward", "gsr_ssim_forward_noalloc", "gsr_ssim_backward", "gsr_exchange_expand",
     "gsr_densify_plan_words", "gsr_densify_plan", "gsr_densify_apply", "gsr_densify_stats", "gsr_reset_opacity",
-    "gsr_ply_pack", "gsr_ply_unpack",
+    "gsr_ply_pack", "gsr_ply_unpack", "gsr_loss_partials", "gsr_loss_forward", "gsr_loss_backward",
 )
 STAGE_COUNT = 8
 
@@ -186,6 +195,13 @@ def load():
     lib.gsr_ssim_forward_noalloc.argtypes = [PS] + [C.c_void_p] * 6
     lib.gsr_ssim_backward.restype = C.c_int
     lib.gsr_ssim_backward.argtypes = [PS] + [C.c_void_p] * 7
+    PL = C.POINTER(GsrLossParams)
+    lib.gsr_loss_partials.restype = C.c_int64
+    lib.gsr_loss_partials.argtypes = [C.c_int32] * 3
+    lib.gsr_loss_forward.restype = C.c_int
+    lib.gsr_loss_forward.argtypes = [PL] + [C.c_void_p] * 6
+    lib.gsr_loss_backward.restype = C.c_int
+    lib.gsr_loss_backward.argtypes = [PL] + [C.c_void_p] * 7
     bind_densify(lib)
     _lib = lib
     return lib

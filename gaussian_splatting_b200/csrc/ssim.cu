@@ -93,12 +93,13 @@ __device__ __forceinline__ float rcp_newton(float x) {
     return fmaf(r, fmaf(-x, r, 1.0f), r);
 }
 
-// TRAIN: write the three partial-derivative maps.  `map` and `partial` are optional (nullptr).
+// TRAIN: write the three partial-derivative maps.  `map`, `partial` and `l1_partial` are optional (nullptr);
+// l1_partial: per-tile sums of |img1 - img2| (the L1 term of the training loss, from the staged pixels).
 template <bool TRAIN>
-__global__ void __launch_bounds__(SS_THREADS, SS_MIN_BLOCKS)
-ssim_fwd_kernel(const float* __restrict__ img1, const float* __restrict__ img2, float* __restrict__ map,
-                float* __restrict__ dm_dmu1, float* __restrict__ dm_dsigma1_sq, float* __restrict__ dm_dsigma12,
-                float* __restrict__ partial, int H, int W, float C1, float C2, int crop) {
+__device__ __forceinline__ void
+ssim_fwd_body(const float* __restrict__ img1, const float* __restrict__ img2, float* __restrict__ map,
+              float* __restrict__ dm_dmu1, float* __restrict__ dm_dsigma1_sq, float* __restrict__ dm_dsigma12,
+              float* __restrict__ partial, float* __restrict__ l1_partial, int H, int W, float C1, float C2, int crop) {
     __shared__ __align__(16) float s_in[2][SS_IN][SS_PITCH];
     __shared__ __align__(16) float s_x[5][SS_IN][SS_T];
     __shared__ float s_red[SS_THREADS / 32];
@@ -163,11 +164,12 @@ ssim_fwd_kernel(const float* __restrict__ img1, const float* __restrict__ img2, 
     vtaps4(s_x[4], row0, col, e12);
 
     const int x = x0 + col;
-    float local = 0.f;
+    float local = 0.f, l1 = 0.f;
 #pragma unroll
     for (int j = 0; j < 4; j++) {
         const int y = y0 + row0 + j;
         if (x >= W || y >= H) continue;
+        if (l1_partial) l1 += fabsf(s_in[0][row0 + j + SS_R][col + SS_R] - s_in[1][row0 + j + SS_R][col + SS_R]);
         const float m1 = mu1[j], m2 = mu2[j];
         const float mu1_sq = m1 * m1, mu2_sq = m2 * m2, mu1_mu2 = m1 * m2;
         const float sigma1_sq = e11[j] - mu1_sq, sigma2_sq = e22[j] - mu2_sq, sigma12 = e12[j] - mu1_mu2;
@@ -198,6 +200,103 @@ ssim_fwd_kernel(const float* __restrict__ img1, const float* __restrict__ img2, 
             for (int w = 0; w < SS_THREADS / 32; w++) s += s_red[w];
             partial[((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x] = s;
         }
+        __syncthreads();
+    }
+    if (l1_partial) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) l1 += __shfl_xor_sync(0xffffffffu, l1, o);
+        if ((tid & 31) == 0) s_red[tid >> 5] = l1;
+        __syncthreads();
+        if (tid == 0) {
+            float s = 0.f;
+#pragma unroll
+            for (int w = 0; w < SS_THREADS / 32; w++) s += s_red[w];
+            l1_partial[((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x] = s;
+        }
+    }
+}
+
+template <bool TRAIN>
+__global__ void __launch_bounds__(SS_THREADS, SS_MIN_BLOCKS)
+ssim_fwd_kernel(const float* __restrict__ img1, const float* __restrict__ img2, float* __restrict__ map,
+                float* __restrict__ dm_dmu1, float* __restrict__ dm_dsigma1_sq, float* __restrict__ dm_dsigma12,
+                float* __restrict__ partial, int H, int W, float C1, float C2, int crop) {
+    ssim_fwd_body<TRAIN>(img1, img2, map, dm_dmu1, dm_dsigma1_sq, dm_dsigma12, partial, nullptr, H, W, C1, C2, crop);
+}
+
+// ---- the training loss of train.py:155-174 in one forward and one backward launch ------------------------------
+//   loss = (1 - lambda) * mean|image - gt| + lambda * (1 - mean SSIM(image, gt)) + w_d * mean|(invdepth - mono) * mask|
+// Planes 0..CH-1 of the grid are the SSIM tiles above (which also sum |image - gt| from the pixels they staged);
+// plane CH holds the 32x32 tiles of the single-channel inverse-depth term.
+struct LossArgs {
+    const float *image, *gt, *invdepth, *mono, *mask;
+    int CH, H, W;
+    float C1, C2;
+};
+
+// |(invdepth - mono) * mask| summed over one tile -> depth_partial[tile]
+__device__ __forceinline__ void loss_depth_fwd_tile(const LossArgs& a, float* __restrict__ depth_partial) {
+    __shared__ float s_redd[SS_THREADS / 32];
+    const int tid = threadIdx.x, col = tid & 31, row0 = (tid >> 5) * 4;
+    const int x = blockIdx.x * SS_T + col;
+    float sum = 0.f;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const int y = blockIdx.y * SS_T + row0 + j;
+        if (x >= a.W || y >= a.H) continue;
+        const size_t g = (size_t)y * a.W + x;
+        float v = __ldg(a.invdepth + g) - __ldg(a.mono + g);
+        if (a.mask) v *= __ldg(a.mask + g);
+        sum += fabsf(v);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if ((tid & 31) == 0) s_redd[tid >> 5] = sum;
+    __syncthreads();
+    if (tid == 0) {
+        float s = 0.f;
+#pragma unroll
+        for (int w = 0; w < SS_THREADS / 32; w++) s += s_redd[w];
+        depth_partial[blockIdx.y * gridDim.x + blockIdx.x] = s;
+    }
+}
+
+__global__ void __launch_bounds__(SS_THREADS, SS_MIN_BLOCKS)
+loss_fwd_kernel(LossArgs a, float* __restrict__ dm_dmu1, float* __restrict__ dm_dsigma1_sq, float* __restrict__ dm_dsigma12,
+                float* __restrict__ ssim_partial, float* __restrict__ l1_partial, float* __restrict__ depth_partial) {
+    if ((int)blockIdx.z == a.CH) {       // uniform per CTA
+        loss_depth_fwd_tile(a, depth_partial);
+        return;
+    }
+    ssim_fwd_body<true>(a.image, a.gt, nullptr, dm_dmu1, dm_dsigma1_sq, dm_dsigma12, ssim_partial, l1_partial, a.H, a.W,
+                        a.C1, a.C2, 0);
+}
+
+// out = {loss, L1, mean SSIM, depth L1}: fixed-order fp64 sums of the three partial arrays (deterministic)
+__global__ void __launch_bounds__(1024)
+loss_finish_kernel(const float* __restrict__ ssim_partial, const float* __restrict__ l1_partial, long long n_img,
+                   const float* __restrict__ depth_partial, long long n_depth, double inv_img, double inv_depth,
+                   float lambda_dssim, float depth_weight, float* __restrict__ out) {
+    __shared__ double s_red[3][32];
+    double s[3] = {0.0, 0.0, 0.0};
+    for (long long i = threadIdx.x; i < n_img; i += 1024) { s[0] += (double)ssim_partial[i]; s[1] += (double)l1_partial[i]; }
+    for (long long i = threadIdx.x; i < n_depth; i += 1024) s[2] += (double)depth_partial[i];
+#pragma unroll
+    for (int q = 0; q < 3; q++) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s[q] += __shfl_xor_sync(0xffffffffu, s[q], o);
+        if ((threadIdx.x & 31) == 0) s_red[q][threadIdx.x >> 5] = s[q];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t[3] = {0.0, 0.0, 0.0};
+        for (int q = 0; q < 3; q++)
+            for (int w = 0; w < 32; w++) t[q] += s_red[q][w];
+        const float ssim = (float)(t[0] * inv_img), l1 = (float)(t[1] * inv_img), dl1 = (float)(t[2] * inv_depth);
+        // the reference's expression order (train.py:162,173-174)
+        float loss = (1.0f - lambda_dssim) * l1 + lambda_dssim * (1.0f - ssim);
+        if (n_depth > 0) loss += depth_weight * dl1;
+        out[0] = loss; out[1] = l1; out[2] = ssim; out[3] = dl1;
     }
 }
 
@@ -221,18 +320,21 @@ __global__ void __launch_bounds__(1024) ssim_mean_kernel(const float* __restrict
 // dL_dimg1 = G * (dL_dmap dm_dmu1) + 2 img1 . G * (dL_dmap dm_dsigma1_sq) + img2 . G * (dL_dmap dm_dsigma12)
 // (ssim.cu:309-358).  SCALAR: dL_dmap is the constant  *dL_dmean * inv_count  inside the crop window
 // and zero outside — the gradient of map[crop].mean() — so no dL_dmap tensor is read.
+// l1_coef != 0 (training loss): the result also gets  l1_coef * *dL_dmean * sign(img1 - img2), the gradient of the
+// L1 term; inv_count then carries the SSIM term's factor -lambda / count.
 template <bool SCALAR>
-__global__ void __launch_bounds__(SS_THREADS, SS_MIN_BLOCKS)
-ssim_bwd_kernel(const float* __restrict__ img1, const float* __restrict__ img2, const float* __restrict__ dL_dmap,
-                const float* __restrict__ dL_dmean, float inv_count, const float* __restrict__ dm_dmu1,
-                const float* __restrict__ dm_dsigma1_sq, const float* __restrict__ dm_dsigma12,
-                float* __restrict__ dL_dimg1, int H, int W, int crop) {
+__device__ __forceinline__ void
+ssim_bwd_body(const float* __restrict__ img1, const float* __restrict__ img2, const float* __restrict__ dL_dmap,
+              const float* __restrict__ dL_dmean, float inv_count, const float* __restrict__ dm_dmu1,
+              const float* __restrict__ dm_dsigma1_sq, const float* __restrict__ dm_dsigma12,
+              float* __restrict__ dL_dimg1, int H, int W, int crop, float l1_coef) {
     __shared__ __align__(16) float s_in[3][SS_IN][SS_PITCH];
     __shared__ __align__(16) float s_x[3][SS_IN][SS_T];
     const int tid = threadIdx.x;
     const int x0 = blockIdx.x * SS_T, y0 = blockIdx.y * SS_T;
     const size_t pbase = (size_t)blockIdx.z * H * W;
     const float gscale = SCALAR ? __ldg(dL_dmean) * inv_count : 0.f;
+    const float l1_scale = (SCALAR && l1_coef != 0.f) ? __ldg(dL_dmean) * l1_coef : 0.f;
 
     {
         const int lane = tid & 31, warp = tid >> 5;
@@ -291,8 +393,43 @@ ssim_bwd_kernel(const float* __restrict__ img1, const float* __restrict__ img2, 
         float d = ga[j];
         d += pix1 * 2.0f * gb[j];
         d += pix2 * gc[j];
+        if (l1_coef != 0.f) d += l1_scale * (float)((pix1 > pix2) - (pix1 < pix2));      // torch.abs backward: sign(x)
         dL_dimg1[g] = d;
     }
+}
+
+template <bool SCALAR>
+__global__ void __launch_bounds__(SS_THREADS, SS_MIN_BLOCKS)
+ssim_bwd_kernel(const float* __restrict__ img1, const float* __restrict__ img2, const float* __restrict__ dL_dmap,
+                const float* __restrict__ dL_dmean, float inv_count, const float* __restrict__ dm_dmu1,
+                const float* __restrict__ dm_dsigma1_sq, const float* __restrict__ dm_dsigma12,
+                float* __restrict__ dL_dimg1, int H, int W, int crop) {
+    ssim_bwd_body<SCALAR>(img1, img2, dL_dmap, dL_dmean, inv_count, dm_dmu1, dm_dsigma1_sq, dm_dsigma12, dL_dimg1, H, W, crop, 0.f);
+}
+
+// dL_dimage = dL_dloss * ((1 - lambda) / N * sign(image - gt) - lambda / N * dSSIM/dimage) on planes 0..CH-1,
+// dL_dinvdepth = dL_dloss * w_d / (H W) * sign((invdepth - mono) * mask) * mask on plane CH.
+__global__ void __launch_bounds__(SS_THREADS, SS_MIN_BLOCKS)
+loss_bwd_kernel(LossArgs a, const float* __restrict__ dL_dloss, float ssim_coef, float l1_coef, float depth_coef,
+                const float* __restrict__ dm_dmu1, const float* __restrict__ dm_dsigma1_sq,
+                const float* __restrict__ dm_dsigma12, float* __restrict__ dL_dimage, float* __restrict__ dL_dinvdepth) {
+    if ((int)blockIdx.z == a.CH) {       // uniform per CTA
+        const int tid = threadIdx.x, col = tid & 31, row0 = (tid >> 5) * 4;
+        const int x = blockIdx.x * SS_T + col;
+        const float gd = __ldg(dL_dloss) * depth_coef;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int y = blockIdx.y * SS_T + row0 + j;
+            if (x >= a.W || y >= a.H) continue;
+            const size_t g = (size_t)y * a.W + x;
+            const float m = a.mask ? __ldg(a.mask + g) : 1.0f;
+            const float v = (__ldg(a.invdepth + g) - __ldg(a.mono + g)) * m;
+            dL_dinvdepth[g] = gd * (float)((v > 0.f) - (v < 0.f)) * m;
+        }
+        return;
+    }
+    ssim_bwd_body<true>(a.image, a.gt, nullptr, dL_dloss, ssim_coef, dm_dmu1, dm_dsigma1_sq, dm_dsigma12, dL_dimage, a.H, a.W,
+                        0, l1_coef);
 }
 
 // several CTAs per SM only fit with the large shared-memory carveout
@@ -306,6 +443,8 @@ static void ssim_init_once() {
         ssim_prefer_smem(ssim_fwd_kernel<false>);
         ssim_prefer_smem(ssim_bwd_kernel<true>);
         ssim_prefer_smem(ssim_bwd_kernel<false>);
+        ssim_prefer_smem(loss_fwd_kernel);
+        ssim_prefer_smem(loss_bwd_kernel);
         return true;
     }();
     (void)done;
@@ -469,4 +608,65 @@ extern "C" int gsr_ssim_forward_noalloc(const GsrSsimParams* p, float* ssim_map,
     const double inv = count > 0 ? 1.0 / count : std::numeric_limits<double>::quiet_NaN();
     GSR_LAUNCH(ssim_mean_kernel, 1, 1024, 0, st, (const float*)part, tiles, inv, mean_out);
     return check_stage("ssim forward (no-alloc)", false, st);
+}
+
+
+// ---------------------------------------------------------------------------------------------------------------
+// Training loss (train.py:155-174): C-ABI.
+static int loss_check(const GsrLossParams* p, const char* who) {
+    if (!p || p->CH <= 0 || p->CH > 65534 || p->H <= 0 || p->W <= 0 || (long long)p->H * p->W >= (1LL << 31)) {
+        gsr::set_error("%s: bad dimensions", who);
+        return GSR_ERR_INVALID_ARG;
+    }
+    if (!p->image || !p->gt || ((p->invdepth == nullptr) != (p->mono_invdepth == nullptr)) || (p->depth_mask && !p->invdepth)) {
+        gsr::set_error("%s: image and gt are required; invdepth and mono_invdepth come together", who);
+        return GSR_ERR_INVALID_ARG;
+    }
+    return GSR_OK;
+}
+
+extern "C" int64_t gsr_loss_partials(int32_t CH, int32_t H, int32_t W) {
+    return 2 * (int64_t)gsr::ssim_tiles(1, CH, H, W) + (int64_t)gsr::ssim_tiles(1, 1, H, W);
+}
+
+extern "C" int gsr_loss_forward(const GsrLossParams* p, float* dm_dmu1, float* dm_dsigma1_sq, float* dm_dsigma12,
+                                float* out4, float* partials, void* stream) {
+    using namespace gsr;
+    if (int rc = loss_check(p, "gsr_loss_forward")) return rc;
+    if (!dm_dmu1 || !dm_dsigma1_sq || !dm_dsigma12 || !out4 || !partials) {
+        set_error("gsr_loss_forward: null output pointer");
+        return GSR_ERR_INVALID_ARG;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    ssim_init_once();
+    const long long n_img = ssim_tiles(1, p->CH, p->H, p->W), n_depth = p->invdepth ? ssim_tiles(1, 1, p->H, p->W) : 0;
+    const LossArgs a{p->image, p->gt, p->invdepth, p->mono_invdepth, p->depth_mask, p->CH, p->H, p->W, p->C1, p->C2};
+    const dim3 grid((p->W + SS_T - 1) / SS_T, (p->H + SS_T - 1) / SS_T, p->CH + (p->invdepth ? 1 : 0));
+    float* l1p = partials + n_img;
+    float* dp = partials + 2 * n_img;
+    GSR_LAUNCH(loss_fwd_kernel, grid, SS_THREADS, 0, st, a, dm_dmu1, dm_dsigma1_sq, dm_dsigma12, partials, l1p, dp);
+    const double inv_img = 1.0 / ((double)p->CH * p->H * p->W), inv_depth = 1.0 / ((double)p->H * p->W);
+    GSR_LAUNCH(loss_finish_kernel, 1, 1024, 0, st, (const float*)partials, (const float*)l1p, n_img, (const float*)dp, n_depth,
+               inv_img, inv_depth, p->lambda_dssim, p->depth_weight, out4);
+    return check_stage("training loss forward", false, st);
+}
+
+extern "C" int gsr_loss_backward(const GsrLossParams* p, const float* dL_dloss, const float* dm_dmu1,
+                                 const float* dm_dsigma1_sq, const float* dm_dsigma12, float* dL_dimage,
+                                 float* dL_dinvdepth, void* stream) {
+    using namespace gsr;
+    if (int rc = loss_check(p, "gsr_loss_backward")) return rc;
+    if (!dL_dloss || !dm_dmu1 || !dm_dsigma1_sq || !dm_dsigma12 || !dL_dimage || (p->invdepth && !dL_dinvdepth)) {
+        set_error("gsr_loss_backward: null pointer");
+        return GSR_ERR_INVALID_ARG;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    ssim_init_once();
+    const LossArgs a{p->image, p->gt, p->invdepth, p->mono_invdepth, p->depth_mask, p->CH, p->H, p->W, p->C1, p->C2};
+    const dim3 grid((p->W + SS_T - 1) / SS_T, (p->H + SS_T - 1) / SS_T, p->CH + (p->invdepth ? 1 : 0));
+    const double inv_img = 1.0 / ((double)p->CH * p->H * p->W), inv_depth = 1.0 / ((double)p->H * p->W);
+    GSR_LAUNCH(loss_bwd_kernel, grid, SS_THREADS, 0, st, a, dL_dloss, (float)(-(double)p->lambda_dssim * inv_img),
+               (float)((1.0 - (double)p->lambda_dssim) * inv_img), (float)((double)p->depth_weight * inv_depth), dm_dmu1,
+               dm_dsigma1_sq, dm_dsigma12, dL_dimage, dL_dinvdepth);
+    return check_stage("training loss backward", false, st);
 }

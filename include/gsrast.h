@@ -253,6 +253,35 @@ int gsr_ssim_backward(const GsrSsimParams* p, const float* dL_dmap, const float*
                       float* dL_dimg1, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * The training loss in one forward and one backward launch.  Replaces, for the image the rasterizer just produced,
+ * l1_loss (utils/loss_utils.py:40), fused_ssim (train.py:155-159), the weighted sum of train.py:162 and the
+ * inverse-depth regulariser of train.py:165-174:
+ *   loss = (1 - lambda_dssim) * mean|image - gt| + lambda_dssim * (1 - mean SSIM(image, gt))
+ *          [+ depth_weight * mean|(invdepth - mono_invdepth) * depth_mask|     when invdepth != NULL]
+ * Forward: the SSIM tiles also sum |image - gt| from the pixels they stage; the inverse-depth term rides on one
+ * extra plane of the same grid; out4 = {loss, L1, mean SSIM, depth L1} (device), deterministic.  Backward: dL_dimage
+ * and dL_dinvdepth (what the rasterizer's backward consumes) from the device scalar *dL_dloss.  `partials`:
+ * gsr_loss_partials(CH, H, W) floats of scratch. */
+typedef struct GsrLossParams {
+    const float* image;          /* CH*H*W  rendered image */
+    const float* gt;             /* CH*H*W */
+    const float* invdepth;       /* H*W rendered inverse depth, or NULL: no depth term */
+    const float* mono_invdepth;  /* H*W */
+    const float* depth_mask;     /* H*W or NULL (= ones) */
+    int32_t CH, H, W;
+    float lambda_dssim;          /* opt.lambda_dssim (arguments/__init__.py: 0.2) */
+    float depth_weight;          /* depth_l1_weight(iteration) */
+    float C1, C2;                /* 0.01^2, 0.03^2 */
+    int32_t reserved;
+} GsrLossParams;
+int64_t gsr_loss_partials(int32_t CH, int32_t H, int32_t W);
+int gsr_loss_forward(const GsrLossParams* p, float* dm_dmu1, float* dm_dsigma1_sq, float* dm_dsigma12,
+                     float* out4, float* partials, void* stream);
+int gsr_loss_backward(const GsrLossParams* p, const float* dL_dloss, const float* dm_dmu1,
+                      const float* dm_dsigma1_sq, const float* dm_dsigma12, float* dL_dimage,
+                      float* dL_dinvdepth, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * Adaptive density control on the device.  Replaces the tensor surgery of
  * GaussianModel.densify_and_prune / densify_and_clone / densify_and_split / prune_points /
  * cat_tensors_to_optimizer / _prune_optimizer (scene/gaussian_model.py:414-621), reset_opacity

@@ -41,7 +41,8 @@ def test_struct_layouts_match_header():
     h = _header()
     for name, cls in (("GsrParams", _lib.GsrParams), ("GsrBuffers", _lib.GsrBuffers),
                       ("GsrForwardOut", _lib.GsrForwardOut), ("GsrBackwardIO", _lib.GsrBackwardIO),
-                      ("GsrSsimParams", _lib.GsrSsimParams), ("GsrDensifyPlanArgs", _lib.GsrDensifyPlanArgs),
+                      ("GsrSsimParams", _lib.GsrSsimParams), ("GsrLossParams", _lib.GsrLossParams),
+                      ("GsrDensifyPlanArgs", _lib.GsrDensifyPlanArgs),
                       ("GsrDensifyTensor", _lib.GsrDensifyTensor), ("GsrDensifyApplyArgs", _lib.GsrDensifyApplyArgs)):
         body = re.search(r"typedef struct %s \{(.*?)\} %s;" % (name, name), h, re.S).group(1)
         body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
@@ -59,6 +60,7 @@ def test_struct_layouts_match_header():
     assert C.sizeof(_lib.GsrParams) == 12 * 4 + 12 * 8
     assert C.sizeof(_lib.GsrBuffers) == 10 * 8
     assert C.sizeof(_lib.GsrSsimParams) == 2 * 8 + 8 * 4        # 7 ints/floats + tail padding
+    assert C.sizeof(_lib.GsrLossParams) == 5 * 8 + 8 * 4
     assert C.sizeof(_lib.GsrDensifyPlanArgs) == 8 * 4 + 5 * 8
     assert C.sizeof(_lib.GsrDensifyTensor) == 24
     n = int(re.search(r"#define GSR_DENSIFY_MAX_TENSORS (\d+)", h).group(1))

@@ -252,6 +252,42 @@ def test_sparse_adam_and_fused_ssim(emulated_cuda):
     assert abs(float(v.detach()) - v_ref) < 1e-5 and rel_err(img1.grad.numpy(), g_ref) < 1e-3
 
 
+@pytest.mark.parametrize("depth,mask", [(False, False), (True, True)])
+def test_fused_training_loss_matches_torch_and_the_ssim_oracle(emulated_cuda, depth, mask):
+    """loss.training_loss (one forward + one backward launch) on the emulation: L1 and inverse-depth terms against
+    torch, the SSIM term against oracle/ssim_ref.py (fp64), gradients against torch autograd + the oracle's gradient."""
+    from gaussian_splatting_b200 import loss as L
+    H, W, lam, wd = 37, 52, 0.2, 0.37
+    g = torch.Generator().manual_seed(5)
+    image = torch.rand(3, H, W, generator=g)
+    gt = (image + 0.2 * torch.randn(3, H, W, generator=g)).clamp(0, 1)
+    gt[:, :10] = image[:, :10]
+    invd = torch.rand(1, H, W, generator=g) if depth else None
+    mono = torch.rand(1, H, W, generator=g) if depth else None
+    msk = (torch.rand(1, H, W, generator=g) > 0.3).float() if mask else None
+    a_img = image.clone().requires_grad_(True)
+    a_inv = invd.clone().requires_grad_(True) if depth else None
+    loss, parts = L.training_loss(a_img, gt, lam, invdepth=a_inv, mono_invdepth=mono, depth_mask=msk, depth_weight=wd,
+                                  return_parts=True)
+    (loss * 1.7).backward()
+    v_ref, g_ref = ssim_ref.fused_ssim(image[None].numpy(), gt[None].numpy(), dtype=np.float64)
+    b_img = image.clone().requires_grad_(True)
+    b_inv = invd.clone().requires_grad_(True) if depth else None
+    l1 = (b_img - gt).abs().mean()
+    want = (1 - lam) * l1 + lam * (1 - float(v_ref))
+    d = torch.zeros(())
+    if depth:
+        d = ((b_inv - mono) * msk).abs().mean()
+        want = want + wd * d
+    (want * 1.7).backward()
+    grad_want = b_img.grad.numpy() - 1.7 * lam * g_ref[0]
+    assert abs(float(loss) - float(want)) < 2e-6 and abs(float(parts[0]) - float(l1)) < 2e-6
+    assert abs(float(parts[1]) - float(v_ref)) < 2e-6 and abs(float(parts[2]) - float(d)) < 2e-6
+    assert rel_err(a_img.grad.numpy(), grad_want) < 1e-4
+    if depth:
+        assert rel_err(a_inv.grad.numpy(), b_inv.grad.numpy()) < 1e-6
+
+
 def test_training_slice_of_the_gpu_suite(emulated_cuda, tmp_path, monkeypatch):
     """tests/test_zz_densify_gpu.py::test_training_slice_render_stats_step_densify_save_load — the callers either side
     of the rasterizer in one piece — executed here on the emulation."""
