@@ -634,37 +634,23 @@ tile_ranges_kernel(const uint32_t* __restrict__ totals, TileBinPlan pl, uint2* _
 }
 
 // Step 3.  One CTA of TB_FILL_WARPS warps per unit.  run[tile] = next free slot of the tile's list for this chunk.
-// Every warp owns a stripe of the band's tile rows (cut by tile_ranges_kernel at equal instance counts).  The chunk's
-// Gaussians are taken TB_SB at a time, one per thread: the thread clips its rectangle to the band, finds the stripes
-// it reaches and appends, IN DEPTH ORDER (ballots inside a warp, packed counts across warps), what a step needs to
-// the queue of each of those stripes in shared memory.  Each warp then drains its own queue: one Gaussian per step,
-// lanes = tiles of the rectangle clipped to the stripe (row-major): slot = run[tile]++, point_list[slot] = id.
-// Within one Gaussian all tiles differ, a tile belongs to one warp, and a queue is in depth order: every list is
-// filled in order without any ranking, and every Gaussian is looked at once per CTA.  Lanes beyond the rectangle do
-// the same read-modify-write on a scratch word of their own (no branch in the step).  Queues hold TB_QCAP entries
-// per stripe (a warp reaches the next round's barrier only after draining its queue, so one buffer suffices); a
-// super-batch that would overflow one (most of its rectangles reach the same stripe) is taken in
-// TB_SB / TB_QCAP rounds of TB_QCAP Gaussians instead.
+// Every warp owns a stripe of the band's tile rows (cut by tile_ranges_kernel at equal instance counts) and walks
+// ALL Gaussians of the chunk in depth order, 32 at a time: each lane clips one rectangle to the stripe and the ones
+// that reach it are compacted (in order) into a parameter list in shared memory; the warp then takes them one after
+// the other, lanes = tiles of the clipped rectangle (row-major): slot = run[tile]++, point_list[slot] = id.
+// Within one Gaussian all tiles differ, a tile belongs to one warp, and a warp takes Gaussians in depth order: every
+// list is filled in order without any ranking.  Lanes beyond the rectangle do the same read-modify-write on a
+// scratch word of their own (no branch in the step).  The warps of a CTA never wait for each other after the
+// counters are set up.
 #ifndef GSR_TB_FILL_BLOCKS
-#define GSR_TB_FILL_BLOCKS 5            // CTAs per SM: 42 KB of shared memory each
+#define GSR_TB_FILL_BLOCKS 6            // CTAs per SM: 37 KB of shared memory each
 #endif
-constexpr int TB_SB = 32 * TB_FILL_WARPS;
-constexpr int TB_QCAP = 64;
-static_assert(TB_FILL_WARPS <= 8 && TB_SB % TB_QCAP == 0 && TB_QCAP % 32 == 0, "packed 16-bit counts: 8 stripes in 128 bits");
-
-struct Cnt8 { unsigned long long lo, hi; };            // eight 16-bit counters (stripes 0-3 | 4-7)
-__device__ __forceinline__ uint32_t cnt8_get(const Cnt8& c, int w) {
-    return (uint32_t)((w < 4 ? c.lo >> (16 * w) : c.hi >> (16 * (w - 4))) & 0xffffull);
-}
-
-__global__ void __launch_bounds__(TB_SB, GSR_TB_FILL_BLOCKS)
+__global__ void __launch_bounds__(32 * TB_FILL_WARPS, GSR_TB_FILL_BLOCKS)
 tile_fill_kernel(const uint4* __restrict__ srects, const uint32_t* __restrict__ bounds, TileBinPlan pl,
                  const uint32_t* __restrict__ M, const uint32_t* __restrict__ tile_start,
                  const uint32_t* __restrict__ stripes, uint32_t* __restrict__ point_list) {
-    __shared__ uint32_t run[TB_MAX_CELLS + TB_SB];               // tile counters, then one scratch word per thread
-    __shared__ __align__(16) uint4 s_q[TB_FILL_WARPS][TB_QCAP];      // {id, first cell, n | (gx - w) << 21, div_magic(w)}
-    __shared__ __align__(16) Cnt8 s_cnt[2][TB_FILL_WARPS];       // per producer warp: entries appended to every stripe
-    __shared__ uint32_t s_cut[TB_FILL_WARPS + 1];                // first tile row of every stripe
+    __shared__ uint32_t run[TB_MAX_CELLS + 32 * TB_FILL_WARPS];  // tile counters, then one scratch word per thread
+    __shared__ __align__(16) uint4 s_par[TB_FILL_WARPS][32];     // {id, first cell, n | (gx - w) << 21, div_magic(w)}
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, chunk = blockIdx.x, band = blockIdx.y;
     const uint32_t r0 = band * pl.band_rows, r1 = min(pl.gy, r0 + pl.band_rows);
     const uint32_t rows = r1 - r0, gx = pl.gx, cells = rows * gx;
@@ -673,10 +659,12 @@ tile_fill_kernel(const uint4* __restrict__ srects, const uint32_t* __restrict__ 
     {
         const uint32_t* m = M + (size_t)chunk * pl.T + (size_t)r0 * gx;
         const uint32_t* ts = tile_start + (size_t)r0 * gx;
-        for (uint32_t i = threadIdx.x; i < cells; i += TB_SB) run[i] = ts[i] + m[i];
+        for (uint32_t i = threadIdx.x; i < cells; i += 32 * TB_FILL_WARPS) run[i] = ts[i] + m[i];
     }
-    if (threadIdx.x <= TB_FILL_WARPS) s_cut[threadIdx.x] = stripes[band * (TB_FILL_WARPS + 1) + threadIdx.x];
     __syncthreads();
+    const uint32_t s0 = stripes[band * (TB_FILL_WARPS + 1) + warp], s1 = stripes[band * (TB_FILL_WARPS + 1) + warp + 1];
+    if (s0 >= s1) return;                // an empty stripe (one very dense row next to it)
+    uint4* par = s_par[warp];
     uint32_t run_s = smem_u32(run);                           // shared-window address: the steps use 32-bit addressing
     uint32_t lane2 = lane + lane;
     const uint32_t dummy = TB_MAX_CELLS + threadIdx.x;
@@ -694,72 +682,31 @@ tile_fill_kernel(const uint4* __restrict__ srects, const uint32_t* __restrict__ 
         if (l < n) point_list[slot] = q.x;
         step_fence();                    // the next Gaussian's lanes may read the counters this one wrote
     };
-    int buf = 0;
-    // one super-batch is fetched ahead of the one being binned
-    uint4 next = k0 + threadIdx.x < k1 ? srects[k0 + threadIdx.x] : make_uint4(0u, 0u, 0u, 0u);
-    for (uint32_t k = k0; k < k1; k += TB_SB) {
+    // one batch of 32 Gaussians is fetched ahead of the one being walked
+    uint4 next = k0 + lane < k1 ? srects[k0 + lane] : make_uint4(0u, 0u, 0u, 0u);
+    for (uint32_t k = k0; k < k1; k += 32) {
         const uint4 g = next;
-        const uint32_t kn = k + TB_SB + threadIdx.x;
+        const uint32_t kn = k + 32 + lane;
         next = kn < k1 ? srects[kn] : make_uint4(0u, 0u, 0u, 0u);
         uint32_t x0, x1, ya, yb;
-        clip_rect(make_uint2(g.x, g.y), r0, r1, x0, x1, ya, yb);
+        clip_rect(make_uint2(g.x, g.y), s0, s1, x0, x1, ya, yb);
         const bool hit = x1 > x0 && yb > ya;
-        // stripes wa..wb that the clipped rows [ya, yb) reach
-        uint32_t wa = 0, wb = 0;
-#pragma unroll
-        for (int w = 1; w < TB_FILL_WARPS; w++) { const uint32_t c = s_cut[w]; wa += ya >= c; wb += yb > c; }
-        int rounds = 1;
-        for (int r = 0; r < rounds; r++) {
-            // a round takes all TB_SB Gaussians, or (overflow) the TB_QCAP of them held by threads r * TB_QCAP ...
-            const bool act = hit && (rounds == 1 || (int)(threadIdx.x / TB_QCAP) == r);
-            uint32_t bits[TB_FILL_WARPS];
-            Cnt8 mine = {0ull, 0ull};
-#pragma unroll
-            for (int w = 0; w < TB_FILL_WARPS; w++) {
-                bits[w] = __ballot_sync(0xffffffffu, act && wa <= (uint32_t)w && (uint32_t)w <= wb);
-                const unsigned long long c = (unsigned long long)__popc(bits[w]) << (16 * (w & 3));
-                if (w < 4) mine.lo |= c; else mine.hi |= c;
-            }
-            if (lane == 0) s_cnt[buf][warp] = mine;
-            __syncthreads();
-            Cnt8 before = {0ull, 0ull}, total = {0ull, 0ull};
-#pragma unroll
-            for (int pw = 0; pw < TB_FILL_WARPS; pw++) {
-                const Cnt8 c = s_cnt[buf][pw];
-                if ((uint32_t)pw < warp) { before.lo += c.lo; before.hi += c.hi; }
-                total.lo += c.lo; total.hi += c.hi;
-            }
-            if (rounds == 1) {
-                bool over = false;
-#pragma unroll
-                for (int w = 0; w < TB_FILL_WARPS; w++) over |= cnt8_get(total, w) > (uint32_t)TB_QCAP;
-                if (over) {              // uniform over the CTA: every thread sees the same totals
-                    rounds = TB_SB / TB_QCAP;
-                    r = -1;
-                    buf ^= 1;
-                    continue;
-                }
-            }
-#pragma unroll
-            for (int w = 0; w < TB_FILL_WARPS; w++) {
-                if (act && wa <= (uint32_t)w && (uint32_t)w <= wb) {
-                    const uint32_t ys = max(ya, s_cut[w]), ye = min(yb, s_cut[w + 1]), wd = x1 - x0;
-                    s_q[w][cnt8_get(before, w) + __popc(bits[w] & lt)] =
-                        make_uint4(g.w, (ys - r0) * gx + x0, (wd * (ye - ys)) | ((gx - wd) << 21), g.z);
-                }
-            }
-            __syncthreads();
-            const uint32_t cnt = cnt8_get(total, (int)warp);
-            const uint4* q_mine = s_q[warp];
-            for (uint32_t e = 0; e < cnt; e++) {
-                const uint4 q = q_mine[e];
-                const uint32_t n = q.z & 0x1fffffu, skip = q.z >> 21;
-                append(q, n, skip, lane, lane2);
-                if (n > 32)              // uniform and rare: a clipped rectangle of more than 32 tiles
-                    for (uint32_t l = lane + 32; l - lane < n; l += 32) append(q, n, skip, l, l + l);
-            }
-            buf ^= 1;
+        const uint32_t bits = __ballot_sync(0xffffffffu, hit);
+        if (bits == 0) continue;
+        if (hit) {
+            const uint32_t w = x1 - x0;
+            par[__popc(bits & lt)] = make_uint4(g.w, (ya - r0) * gx + x0, (w * (yb - ya)) | ((gx - w) << 21), g.z);
         }
+        __syncwarp();
+        const uint32_t cnt = __popc(bits);
+        for (uint32_t e = 0; e < cnt; e++) {
+            const uint4 q = par[e];
+            const uint32_t n = q.z & 0x1fffffu, skip = q.z >> 21;
+            append(q, n, skip, lane, lane2);
+            if (n > 32)                  // uniform and rare: a clipped rectangle of more than 32 tiles
+                for (uint32_t l = lane + 32; l - lane < n; l += 32) append(q, n, skip, l, l + l);
+        }
+        __syncwarp();                    // everybody has read this batch's parameters
     }
 }
 

@@ -125,7 +125,7 @@ constexpr int TB_MAX_GX = 2048;                          // widest tile grid (32
 constexpr int TB_COUNT_CELLS = 10304;                    // difference grid: ((gx + 1) | 1) x (band_rows + 1) <= this
 constexpr int TB_COUNT_THREADS = 256;
 #ifndef GSR_TB_TARGET_UNITS
-#define GSR_TB_TARGET_UNITS 740                          // 148 SMs x 5 resident CTAs of the fill kernel (42 KB of shared memory each)
+#define GSR_TB_TARGET_UNITS 888                          // 148 SMs x 6 resident CTAs of the fill kernel (37 KB of shared memory each)
 #endif
 constexpr int TB_TARGET_UNITS = GSR_TB_TARGET_UNITS;
 constexpr int TB_MIN_CHUNK = 64;                         // Gaussians

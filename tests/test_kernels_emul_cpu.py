@@ -419,10 +419,9 @@ def test_tile_lists_many_chunks_and_bands(oracle, P, W, H, scale):
     assert er.R > 64
 
 
-def test_tile_lists_queue_overflow_rounds(klib, oracle):
-    """Screen-filling Gaussians: every rectangle of a super-batch of 256 reaches the same stripes, more than a stripe
-    queue holds (64), so the list-filling kernel takes the super-batch in four rounds of 64 (binning.cu); clipped
-    rectangles also exceed 32 tiles (several passes per step)."""
+def test_tile_lists_screen_filling_gaussians(klib, oracle):
+    """Screen-filling Gaussians: every rectangle reaches every stripe of the list-filling kernel and the clipped
+    rectangles exceed 32 tiles (several passes per step, binning.cu)."""
     gs, s = small_scene(P=900, W=200, H=136, seed=27, scale_mult=25.0, antialiasing=True)
     er = check_against_oracle(klib, oracle, gs, s)
     assert er.R > 900 * 40
