@@ -468,24 +468,30 @@ def base_line(args, wl, world, impl):
     }
 
 
-def reduce_check(module, wl, device, world):
-    """N > 1: the gradients the fused exchange delivers against the same gradients computed per rank without it and
-    summed with dist.all_reduce.  Raises above 1e-5 (norm-wise), so a SCALE line only exists for correct sums."""
+def reduce_check(module, wl, device, world, flat=None):
+    """N > 1: the gradients the step's reduction delivers (the fused exchange inside the backward kernel, or the packed
+    all-reduce of FlatGradients with --reduce nccl) against the same gradients computed per rank without it and summed
+    tensor by tensor with dist.all_reduce.  Raises above 1e-5 (norm-wise), so a SCALE line only exists for correct sums."""
     from gaussian_splatting_b200 import rasterizer as rz
     params, means2D = wl["params"], wl["means2D"]
     rast = module.GaussianRasterizer(settings_of(module, wl["s"], device))
     dc, dd = wl["dc_dev"], wl["dd_dev"]
 
     def grads():
+        nonlocal use_flat
         for t in list(params.values()) + [means2D]:
             t.grad = None
         color, radii, invd = rast(means3D=params["means3D"], means2D=means2D, opacities=params["opacities"],
                                   shs=params["shs"], scales=params["scales"], rotations=params["rotations"])
         torch.autograd.backward([color, invd], [dc, dd])
+        if use_flat and flat is not None:
+            flat.all_reduce()
         torch.cuda.synchronize(device)
         return {k: v.grad.detach().clone() for k, v in params.items()}
 
+    use_flat = True
     fused = grads()
+    use_flat = False
     red = rz._gradient_reducer
     rz.set_gradient_reducer(None)
     try:
@@ -621,7 +627,7 @@ def run_gpu_arm(args, module, impl, rank, world, local):
         fig["what"] = "e2e protocol with the full loss of train.py:155-174 (lambda_dssim 0.2, depth weight 0.1)"
         line["e2e_full_loss"] = fig
     if ours and world > 1:
-        line["reduce_check"] = reduce_check(module, wl, device, world)
+        line["reduce_check"] = reduce_check(module, wl, device, world, flat)
         line["trace_ms"] = traced_gaps(step, device)
     if ours:
         peaks = load_peaks()

@@ -682,12 +682,15 @@ tile_fill_kernel(const uint4* __restrict__ srects, const uint32_t* __restrict__ 
         if (l < n) point_list[slot] = q.x;
         step_fence();                    // the next Gaussian's lanes may read the counters this one wrote
     };
-    // one batch of 32 Gaussians is fetched ahead of the one being walked
+    // two batches of 32 Gaussians are in flight ahead of the one being walked (a batch's steps are too short to
+    // cover the latency of one load)
     uint4 next = k0 + lane < k1 ? srects[k0 + lane] : make_uint4(0u, 0u, 0u, 0u);
+    uint4 next2 = k0 + 32 + lane < k1 ? srects[k0 + 32 + lane] : make_uint4(0u, 0u, 0u, 0u);
     for (uint32_t k = k0; k < k1; k += 32) {
         const uint4 g = next;
-        const uint32_t kn = k + 32 + lane;
-        next = kn < k1 ? srects[kn] : make_uint4(0u, 0u, 0u, 0u);
+        next = next2;
+        const uint32_t kn = k + 64 + lane;
+        next2 = kn < k1 ? srects[kn] : make_uint4(0u, 0u, 0u, 0u);
         uint32_t x0, x1, ya, yb;
         clip_rect(make_uint2(g.x, g.y), s0, s1, x0, x1, ya, yb);
         const bool hit = x1 > x0 && yb > ya;

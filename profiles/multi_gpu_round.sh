@@ -7,22 +7,22 @@ TAG=${1:-r02}
 NG=$(nvidia-smi -L | wc -l)
 OUT=gpurun_out/${TAG}_scaling
 mkdir -p $OUT
-tr() { local n=$1; shift; timeout 420 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 \
+trun() { local n=$1; shift; timeout 420 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 \
         --master-port $((29500 + RANDOM % 400)) "$@"; }
 for N in 2 4 8; do
   [ $N -gt $NG ] && break
-  tr $N tests/multi_gpu_check.py > $OUT/check_$N.txt 2>&1; echo "check N=$N rc=$? $(grep -h 'fused multimem\|max rel' $OUT/check_$N.txt | tail -2 | tr '\n' ' ')"
+  trun $N tests/multi_gpu_check.py > $OUT/check_$N.txt 2>&1; echo "check N=$N rc=$? $(grep -h 'fused multimem\|max rel' $OUT/check_$N.txt | tail -2 | tr '\n' ' ')"
 done
 for WL in C3 C4; do
   timeout 420 python bench.py --steps 30 --warmup 8 --no-cpu-baseline --workload $WL 2> $OUT/${WL}_1.err | tail -1 > $OUT/${WL}_1.json
   for N in 2 4 8; do
     [ $N -gt $NG ] && break
     [ $WL = C4 ] && [ $N -ne $NG ] && continue
-    tr $N bench.py --gpus $N --steps 30 --warmup 8 --workload $WL 2> $OUT/${WL}_$N.err | tail -1 > $OUT/${WL}_$N.json
+    trun $N bench.py --gpus $N --steps 30 --warmup 8 --workload $WL 2> $OUT/${WL}_$N.err | tail -1 > $OUT/${WL}_$N.json
   done
 done
 # the NCCL fallback at the largest rank count, for the comparison in DESIGN.md
-tr $NG bench.py --gpus $NG --steps 30 --warmup 8 --reduce nccl 2> $OUT/C3_${NG}_nccl.err | tail -1 > $OUT/C3_${NG}_nccl.json
+trun $NG bench.py --gpus $NG --steps 30 --warmup 8 --reduce nccl 2> $OUT/C3_${NG}_nccl.err | tail -1 > $OUT/C3_${NG}_nccl.json
 python - <<PY
 import glob, json
 for f in sorted(glob.glob("$OUT/C*.json")):
