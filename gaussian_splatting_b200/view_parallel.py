@@ -58,6 +58,8 @@ class FlatGradients:
 
     def all_reduce(self, average: bool = False, async_op: bool = False):
         """Sum (or mean) the packed gradients over the group; returns the work handle if async."""
+        if average and async_op:
+            raise ValueError("FlatGradients.all_reduce: average=True needs the result (async_op=False); divide after wait()")
         flat = self.pack()
         work = None
         if dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1:

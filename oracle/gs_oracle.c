@@ -11,8 +11,10 @@
  * contraction: build with -ffp-contract=off) and cites the file:line it follows.
  * Paths are relative to DGR/cuda_rasterizer/ unless stated.
  *
- * Parity status: pinned against outputs of the repaired reference CUDA build run on a
- * B200 (tests/golden/ *.npz, generated by oracle/make_golden.py); the reference ships no
+ * Parity status: pinned.  tests/golden/raster_golden.npz holds outputs of the reference's own CUDA
+ * rasterizer (oracle/_ref, built from /root/reference by oracle/build_ref.py) run on a B200 by
+ * tests/golden/make_raster_golden_gpu.py; tests/test_raster_golden_cpu.py checks this oracle against it on
+ * every CPU run, and tests/test_parity_gpu.py checks the CUDA path against both.  The reference ships no
  * golden vectors of its own for this path.
  */
 #include <math.h>
