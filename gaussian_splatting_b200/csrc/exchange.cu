@@ -93,18 +93,26 @@ exchange_expand_kernel(int P, int D, int M, int world, const float* __restrict__
         if (dL_drotations) reinterpret_cast<float4*>(dL_drotations)[idx] = r2;
         if (dL_dsh) {
             const float3 mean = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
-            for (int r = 0; r < world; r++) {
-                const float4 c = rgb[(size_t)r * P + idx];
-                if (c.x == 0.f && c.y == 0.f && c.z == 0.f) continue;
-                rgb[(size_t)r * P + idx] = z4;
-                const float4 cam = s_cam[r];
-                float w[16];
-                sh_basis(D, make_float3(mean.x - cam.x, mean.y - cam.y, mean.z - cam.z), w);
+            // the ranks' slots are fetched four at a time before any of them is used or cleared: with one load per
+            // iteration (and the clearing store between two loads) a thread paid the memory latency `world` times
+            // in a row — 0.37 ms at 8 ranks for 1.27 GB.  The order of the sum over ranks stays fixed.
+            for (int rb = 0; rb < world; rb += 4) {
+                float4 c[4];
 #pragma unroll
-                for (int k = 0; k < 16; k++) {
-                    sh[3 * k] = fmaf(w[k], c.x, sh[3 * k]);
-                    sh[3 * k + 1] = fmaf(w[k], c.y, sh[3 * k + 1]);
-                    sh[3 * k + 2] = fmaf(w[k], c.z, sh[3 * k + 2]);
+                for (int j = 0; j < 4; j++) c[j] = rb + j < world ? rgb[(size_t)(rb + j) * P + idx] : z4;
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    if (c[j].x == 0.f && c[j].y == 0.f && c[j].z == 0.f) continue;      // (also the slots past `world`)
+                    rgb[(size_t)(rb + j) * P + idx] = z4;
+                    const float4 cam = s_cam[rb + j];
+                    float w[16];
+                    sh_basis(D, make_float3(mean.x - cam.x, mean.y - cam.y, mean.z - cam.z), w);
+#pragma unroll
+                    for (int k = 0; k < 16; k++) {
+                        sh[3 * k] = fmaf(w[k], c[j].x, sh[3 * k]);
+                        sh[3 * k + 1] = fmaf(w[k], c[j].y, sh[3 * k + 1]);
+                        sh[3 * k + 2] = fmaf(w[k], c[j].z, sh[3 * k + 2]);
+                    }
                 }
             }
         }
