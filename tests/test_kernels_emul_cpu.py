@@ -30,7 +30,7 @@ VP = C.c_void_p
 def load_full_emul(defines=(), tag="full"):
     """defines / tag: a variant of the emulated library (e.g. a lowered threshold) next to the default one."""
     out = os.path.join(HERE, "host_emul", f"libgsrast_{tag}_emul.so")
-    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(EMU, f) for f in ("cuda_runtime.h", "emul.cpp")]
+    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(EMU, f) for f in ("cuda_runtime.h", "emul.cpp", "async_copy_emul.cuh")]
     deps.append(os.path.join(HERE, "..", "include", "gsrast.h"))
     if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(d) for d in deps):
         objs = []
