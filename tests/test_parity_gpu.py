@@ -272,7 +272,7 @@ def test_gradients_vs_reference_cuda(dgr, ref_restored, ref_asis, P, W, H, scale
     want = {k: np.mean([r["grads"][k] for r in runs], axis=0) for k in runs[0]["grads"]}
     assert np.array_equal(got["radii"], runs[0]["radii"])
     assert np.abs(got["color"] - runs[0]["color"]).max() <= IMG_TOL
-    _check_grads(got["grads"], want, ("means3D", "means2D", "opacities", "shs", "scales", "rotations"))
+    _check_grads(got["grads"], want, ("means3D", "means2D", "opacities", "shs", "scales", "rotations"), outliers=1e-6)
     # the fork as shipped (truncated computeCov2DCUDA) is a valid oracle for these:
     asis = run_module(ref_asis, gs, s, dc, dd)["grads"]
     _check_grads(got["grads"], asis, ("means2D", "opacities", "shs"))
