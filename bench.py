@@ -661,6 +661,11 @@ def run_gpu_arm(args, module, impl, rank, world, local):
         hbm = [s for s in stages if s["bound"] == "hbm"]
         if hbm:
             line["roofline_hbm"] = hbm[0]
+        xch = [s for s in stages if s["stage"] == "exchange"]
+        if xch:
+            # N > 1: the receiver half of the gradient exchange (gsr_exchange_expand) against the HBM peak; the two
+            # rank barriers and the publishing kernels are in trace_ms
+            line["roofline_exchange"] = xch[0]
     else:
         line["gpu_launches"] = 0          # none of this repo's kernels run in the reference arm
     return line, wl
