@@ -420,7 +420,7 @@ def measure_work(wl, device):
     W, H = wl["W"], wl["H"]
     gx, gy = (W + 15) // 16, (H + 15) // 16
     band_rows = max(1, min(gy, 512, 8192 // gx))                       # common.cuh: tile_bin_plan
-    chunks = max(1, min(888 // ((gy + band_rows - 1) // band_rows), wl["P"] // 64))
+    chunks = max(1, min(888, (32 << 20) // (gx * gy), wl["P"] // 64))
     return dict(P=wl["P"], V=int((radii > 0).sum()), R=int(R), T=gx * gy, N=W * H,
                 Wf=int(c[0]), Bp=int(c[1]), Wb=int(c[2]), chunks=chunks)
 

@@ -129,6 +129,7 @@ constexpr int TB_COUNT_THREADS = 256;
 #endif
 constexpr int TB_TARGET_UNITS = GSR_TB_TARGET_UNITS;
 constexpr int TB_MIN_CHUNK = 64;                         // Gaussians
+constexpr unsigned long long TB_MAX_MATRIX_WORDS = 32ull << 20;   // 128 MB of (chunk, tile) counts at most
 constexpr int TB_MAX_WBLOCKS = 4096;                     // weight blocks (multiples of 256 depth ranks) used to balance the chunks
 
 struct TileBinPlan { uint32_t gx, gy, T, band_rows, n_bands, n_chunks, stride, wblock, n_wblocks; };
@@ -144,7 +145,10 @@ inline TileBinPlan tile_bin_plan(int P, int W, int H) {
     pl.band_rows = rows;
     pl.n_bands = (pl.gy + rows - 1) / rows;
     pl.stride = (pl.gx + 1) | 1u;
-    uint32_t chunks = (uint32_t)TB_TARGET_UNITS / (pl.n_bands ? pl.n_bands : 1u);
+    // The list-filling kernel runs band after band (one launch each), so every band gets the full number of chunks;
+    // the (chunk, tile) count matrix is capped at TB_MAX_MATRIX_WORDS.
+    uint32_t chunks = (uint32_t)TB_TARGET_UNITS;
+    if ((unsigned long long)chunks * pl.T > TB_MAX_MATRIX_WORDS) chunks = (uint32_t)(TB_MAX_MATRIX_WORDS / (pl.T ? pl.T : 1u));
     const uint32_t most = (uint32_t)(P > 0 ? P : 1) / TB_MIN_CHUNK;
     if (chunks > most) chunks = most;
     if (chunks < 1) chunks = 1;
