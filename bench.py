@@ -390,7 +390,11 @@ def ncu_evidence(stage):
         return None
     kernel, src = STAGE_KERNELS[stage]
     now = source_sha1(src)
-    found = sorted(glob.glob(os.path.join(ROOT, "profiles", "**", "r*_kernels*.json"), recursive=True))
+    import re
+    # rNN<letter>_kernels[_fwd|_bwd].json are captures of the bench workload (profiles/gpu_round.sh); the *_misc_* and
+    # *_densify_* files hold other workloads' launches of the same kernels and must not be matched
+    found = sorted(f for f in glob.glob(os.path.join(ROOT, "profiles", "**", "r*_kernels*.json"), recursive=True)
+                   if re.fullmatch(r"r\d+[a-z]*_kernels(_fwd|_bwd)?\.json", os.path.basename(f)))
     for path in reversed(found):
         try:
             entries = json.load(open(path))

@@ -645,6 +645,43 @@ tile_ranges_kernel(const uint32_t* __restrict__ totals, TileBinPlan pl, uint2* _
 #ifndef GSR_TB_FILL_BLOCKS
 #define GSR_TB_FILL_BLOCKS 6            // CTAs per SM: 37 KB of shared memory each
 #endif
+// L2 eviction priorities of the kernel's three streams (bit 0: point_list stores evict-last, bit 1: the Gaussians'
+// rectangles evict-first, bit 2: the count matrix and list starts evict-first).  point_list is written in partial
+// sectors that are completed later by other CTAs: the longer they stay in L2 the fewer of them go to DRAM half-written.
+// Measured (B200): policy 3 takes the kernel from 0.283 to 0.276 ms at C3 and from 1.37 to 1.13 ms at C4 (6M, 4K);
+// bit 2 adds nothing.
+#ifndef GSR_TB_FILL_POLICY
+#define GSR_TB_FILL_POLICY 3
+#endif
+#if GSR_TB_FILL_POLICY && !defined(GSR_HOST_EMUL)
+__device__ __forceinline__ uint64_t l2_evict_last() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ uint64_t l2_evict_first() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ void stg_u32_hint(uint32_t* a, uint32_t v, uint64_t pol) {
+    asm volatile("st.global.L2::cache_hint.u32 [%0], %1, %2;" ::"l"(a), "r"(v), "l"(pol) : "memory");
+}
+__device__ __forceinline__ uint4 ldg_u4_hint(const uint4* a, uint64_t pol) {
+    uint4 v;
+    asm volatile("ld.global.nc.L2::cache_hint.v4.u32 {%0, %1, %2, %3}, [%4], %5;"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(a), "l"(pol));
+    return v;
+}
+__device__ __forceinline__ uint32_t ldg_u32_hint(const uint32_t* a, uint64_t pol) {
+    uint32_t v;
+    asm volatile("ld.global.nc.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(a), "l"(pol));
+    return v;
+}
+#define TB_FILL_HINTS 1
+#else
+#define TB_FILL_HINTS 0
+#endif
 __global__ void __launch_bounds__(32 * TB_FILL_WARPS, GSR_TB_FILL_BLOCKS)
 tile_fill_kernel(const uint4* __restrict__ srects, const uint32_t* __restrict__ bounds, TileBinPlan pl,
                  const uint32_t* __restrict__ M, const uint32_t* __restrict__ tile_start,
@@ -659,8 +696,23 @@ tile_fill_kernel(const uint4* __restrict__ srects, const uint32_t* __restrict__ 
     {
         const uint32_t* m = M + (size_t)chunk * pl.T + (size_t)r0 * gx;
         const uint32_t* ts = tile_start + (size_t)r0 * gx;
+#if TB_FILL_HINTS && (GSR_TB_FILL_POLICY & 4)
+        const uint64_t once = l2_evict_first();
+        for (uint32_t i = threadIdx.x; i < cells; i += 32 * TB_FILL_WARPS)
+            run[i] = ts[i] + ldg_u32_hint(m + i, once);
+#else
         for (uint32_t i = threadIdx.x; i < cells; i += 32 * TB_FILL_WARPS) run[i] = ts[i] + m[i];
+#endif
     }
+#if TB_FILL_HINTS && (GSR_TB_FILL_POLICY & 1)
+    const uint64_t keep = l2_evict_last();
+#endif
+#if TB_FILL_HINTS && (GSR_TB_FILL_POLICY & 2)
+    const uint64_t stream = l2_evict_first();
+    auto load_rect = [&](uint32_t i) { return ldg_u4_hint(srects + i, stream); };
+#else
+    auto load_rect = [&](uint32_t i) { return srects[i]; };
+#endif
     __syncthreads();
     const uint32_t s0 = stripes[band * (TB_FILL_WARPS + 1) + warp], s1 = stripes[band * (TB_FILL_WARPS + 1) + warp + 1];
     if (s0 >= s1) return;                // an empty stripe (one very dense row next to it)
@@ -679,7 +731,9 @@ tile_fill_kernel(const uint4* __restrict__ srects, const uint32_t* __restrict__ 
         const uint32_t a = run_s + 4u * cell;
         const uint32_t slot = lds_u32(a);
         sts_u32(a, slot + 1u);
-#ifndef GSR_TB_EXPERIMENT_NO_STORE
+#if TB_FILL_HINTS && (GSR_TB_FILL_POLICY & 1)
+        if (l < n) stg_u32_hint(point_list + slot, q.x, keep);
+#elif !defined(GSR_TB_EXPERIMENT_NO_STORE)
         if (l < n) point_list[slot] = q.x;
 #else   // measurement variant only (profiles/build_variants.py): how much of the kernel is the scattered store
         if (l < n && q.x == 0xFFFFFFFFu) point_list[slot] = q.x;
@@ -688,13 +742,13 @@ tile_fill_kernel(const uint4* __restrict__ srects, const uint32_t* __restrict__ 
     };
     // two batches of 32 Gaussians are in flight ahead of the one being walked (a batch's steps are too short to
     // cover the latency of one load)
-    uint4 next = k0 + lane < k1 ? srects[k0 + lane] : make_uint4(0u, 0u, 0u, 0u);
-    uint4 next2 = k0 + 32 + lane < k1 ? srects[k0 + 32 + lane] : make_uint4(0u, 0u, 0u, 0u);
+    uint4 next = k0 + lane < k1 ? load_rect(k0 + lane) : make_uint4(0u, 0u, 0u, 0u);
+    uint4 next2 = k0 + 32 + lane < k1 ? load_rect(k0 + 32 + lane) : make_uint4(0u, 0u, 0u, 0u);
     for (uint32_t k = k0; k < k1; k += 32) {
         const uint4 g = next;
         next = next2;
         const uint32_t kn = k + 64 + lane;
-        next2 = kn < k1 ? srects[kn] : make_uint4(0u, 0u, 0u, 0u);
+        next2 = kn < k1 ? load_rect(kn) : make_uint4(0u, 0u, 0u, 0u);
         uint32_t x0, x1, ya, yb;
         clip_rect(make_uint2(g.x, g.y), s0, s1, x0, x1, ya, yb);
         const bool hit = x1 > x0 && yb > ya;
