@@ -79,6 +79,15 @@ preprocess_fwd_kernel(GsrParams p, float focal_x, float focal_y, int gx, int gy,
 
     if (in_range) {
         p_orig = make_float3(p.means3D[3 * idx], p.means3D[3 * idx + 1], p.means3D[3 * idx + 2]);
+        // every per-Gaussian input is requested up front: behind the tests below the four loads were four dependent
+        // round trips to HBM per warp (a culled Gaussian now costs 32 B more, a visible one the same)
+        float3 sc = {0.f, 0.f, 0.f};
+        float4 rot = {0.f, 0.f, 0.f, 0.f};
+        if (p.cov3D_precomp == nullptr) {
+            sc = make_float3(p.scales[3 * idx], p.scales[3 * idx + 1], p.scales[3 * idx + 2]);
+            rot = reinterpret_cast<const float4*>(p.rotations)[idx];
+        }
+        const float o_raw = p.opacities[idx];
         // in_frustum, auxiliary.h:164-190 (only the z test culls in this fork)
         float3 p_view = transform_point_4x3(p_orig, s_view);
         if (p_view.z <= 0.2f) {
@@ -96,8 +105,6 @@ preprocess_fwd_kernel(GsrParams p, float focal_x, float focal_y, int gx, int gy,
 #pragma unroll
                 for (int k = 0; k < 6; k++) cov3D[k] = p.cov3D_precomp[6 * idx + k];
             } else {
-                float3 sc = make_float3(p.scales[3 * idx], p.scales[3 * idx + 1], p.scales[3 * idx + 2]);
-                float4 rot = reinterpret_cast<const float4*>(p.rotations)[idx];
                 if (p.raw_inputs & GSR_RAW_SCALES) sc = act_scale(sc);
                 if (p.raw_inputs & GSR_RAW_ROTATIONS) rot = act_rotation(rot, nullptr);
                 compute_cov3D(sc, p.scale_modifier, rot, cov3D);
@@ -125,7 +132,6 @@ preprocess_fwd_kernel(GsrParams p, float focal_x, float focal_y, int gx, int gy,
                 if ((maxx - minx) * (maxy - miny) != 0) {
                     visible = true;
                     depth = p_view.z;
-                    const float o_raw = p.opacities[idx];
                     opacity_aa = ((p.raw_inputs & GSR_RAW_OPACITIES) ? act_opacity(o_raw) : o_raw) * h_convolution_scaling;
                 }
             }
