@@ -12,6 +12,7 @@ LIB_PATH = os.environ.get("GSR_LIB") or os.path.join(_HERE, "libgsrast.so")
 
 GSR_OK = 0
 RAW_SCALES, RAW_ROTATIONS, RAW_OPACITIES = 1, 2, 4
+ACC_CLEAR_IN_FORWARD, ACC_IS_CLEAR = 1, 2      # GsrBuffers.accumulator (GSR_ACC_*)
 GSR_ERR_INVALID_ARG = -1
 GSR_ERR_CUDA = -2
 GSR_ERR_CAPACITY = -3
@@ -39,6 +40,7 @@ class GsrBuffers(C.Structure):
         ("bin", _fp), ("bin_bytes", C.c_size_t),
         ("scratch", _fp), ("scratch_bytes", C.c_size_t),
         ("num_rendered_host", _fp), ("num_rendered_event", _fp),
+        ("accumulator", C.c_int32), ("reserved2", C.c_int32),
     ]
 
 

@@ -247,7 +247,8 @@ int gsr_forward_stage2(const GsrParams* p, const GsrBuffers* buf, const GsrForwa
     Scratch s = Scratch::carve(buf->scratch, p->P, p->W, p->H, nullptr);
     rc = launch_tile_lists(*p, g, im, b, s, R, st);
     if (rc) return rc;
-    return launch_render_forward(*p, g, im, b, out->out_color, out->out_invdepth, st);
+    return launch_render_forward(*p, g, im, b, out->out_color, out->out_invdepth,
+                                 (buf->accumulator & GSR_ACC_CLEAR_IN_FORWARD) ? s.acc : nullptr, st);
 }
 
 int gsr_forward(const GsrParams* p, const GsrBuffers* buf, const GsrForwardOut* out, int64_t* num_rendered,
@@ -278,6 +279,7 @@ int gsr_backward(const GsrParams* p, const GsrBuffers* buf, int64_t R, const int
     const int gy = (p->H + TILE_Y - 1) / TILE_Y;
     const bool have_invdepth = io->dL_dout_invdepth != nullptr;
     const bool fact = io->xchg_records != nullptr;
+    const bool acc_is_clear = (buf->accumulator & GSR_ACC_IS_CLEAR) != 0;   // zeroed by this view's forward
     if (p->sh_dc && !fact && ((io->dL_dsh == nullptr) != (io->dL_dsh_dc == nullptr))) {
         set_error("split SH storage: pass both dL_dsh (coefficients 1..M-1) and dL_dsh_dc, or neither");
         return GSR_ERR_INVALID_ARG;
@@ -300,7 +302,7 @@ int gsr_backward(const GsrParams* p, const GsrBuffers* buf, int64_t R, const int
                          ((p->M & 3) == 0 && (reinterpret_cast<uintptr_t>(p->shs) & 15) == 0 &&
                           (reinterpret_cast<uintptr_t>(io->dL_dsh) & 15) == 0);
     if (bands <= 1 || side == nullptr || !list_ok) {
-        rc = launch_render_backward(*p, g, im, b, s, io->dL_dout_color, io->dL_dout_invdepth, 0, gy, true, st);
+        rc = launch_render_backward(*p, g, im, b, s, io->dL_dout_color, io->dL_dout_invdepth, 0, gy, !acc_is_clear, st);
         if (rc) return rc;
         return launch_preprocess_backward(*p, g, s, radii, have_invdepth, *io, -1, st);
     }
@@ -317,7 +319,8 @@ int gsr_backward(const GsrParams* p, const GsrBuffers* buf, int64_t R, const int
     if (rc) return rc;
     for (int k = 0; k < bands; k++) {
         const int lo = k == 0 ? 0 : band_hi[k - 1];
-        rc = launch_render_backward(*p, g, im, b, s, io->dL_dout_color, io->dL_dout_invdepth, lo, band_hi[k], k == 0, st);
+        rc = launch_render_backward(*p, g, im, b, s, io->dL_dout_color, io->dL_dout_invdepth, lo, band_hi[k],
+                                    k == 0 && !acc_is_clear, st);
         if (rc) return rc;
         GSR_CUDA_TRY(cudaEventRecord(side->band_done[k], st));
         GSR_CUDA_TRY(cudaStreamWaitEvent(side->stream, side->band_done[k], 0));

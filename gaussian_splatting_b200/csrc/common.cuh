@@ -257,8 +257,9 @@ int launch_mark_visible(int P, const float* means, const float* view, uint8_t* p
 int launch_depth_order_and_count(const GsrParams& p, GeomState g, ImgState im, Scratch s, int32_t* num_rendered_host,
                                  void* num_rendered_event, cudaStream_t st);
 int launch_tile_lists(const GsrParams& p, GeomState g, ImgState im, BinState b, Scratch s, int64_t R, cudaStream_t st);
+// acc_clear: the backward's accumulator (Scratch::acc) to zero along the way, or nullptr
 int launch_render_forward(const GsrParams& p, GeomState g, ImgState im, BinState b,
-                          float* out_color, float* out_invdepth, cudaStream_t st);
+                          float* out_color, float* out_invdepth, float* acc_clear, cudaStream_t st);
 int launch_render_backward(const GsrParams& p, GeomState g, ImgState im, BinState b, Scratch s,
                            const float* dL_dpix, const float* dL_dinvdepth, int row_lo, int row_hi, bool zero_acc,
                            cudaStream_t st);

@@ -59,6 +59,9 @@ class _DeviceWorkspace:
         self.counted.record(torch.cuda.current_stream(device))     # materialises the cudaEvent_t handle
         self.last_R = 0
         self.regrows = 0
+        # (P, W, H) of the forward that left the backward's gradient accumulator (a part of `scratch`) zeroed, while
+        # nothing else has used the arena since (GsrBuffers.accumulator, include/gsrast.h)
+        self.acc_clear_for = None
 
     def ensure(self, nbytes, keep_prefix=0):
         """Grow the scratch arena to >= nbytes, preserving its first keep_prefix bytes."""
@@ -69,6 +72,7 @@ class _DeviceWorkspace:
             new[:keep_prefix].copy_(self.scratch[:keep_prefix])
         self.scratch = new
         self.regrows += 1
+        self.acc_clear_for = None
 
 
 _workspaces = {}
@@ -169,13 +173,14 @@ def _params(P, M, rs, bg, means3D, sh, colors_precomp, opacities, scales, rotati
 
 
 def _forward_native(rs, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
-                    state_out=None, dc=None, raw=0):
+                    state_out=None, dc=None, raw=0, clear_accumulator=False):
     """Role of _C.rasterize_gaussians (ext.cpp:16 -> rasterize_points.cu:45-146).
 
     Returns (num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, invdepths).
     state_out: optional dict that receives views of the binning / image state (parity tests).
     dc: split SH storage — degree-0 coefficients (P,1,3); `sh` then holds coefficients 1..M-1.
-    raw: bit mask _lib.RAW_*: scales / rotations / opacities are the model's raw parameters (fused activations)."""
+    raw: bit mask _lib.RAW_*: scales / rotations / opacities are the model's raw parameters (fused activations).
+    clear_accumulator: a backward will follow: the blend forward also zeroes the backward's accumulator."""
     lib = _lib.load()
     if means3D.ndim != 2 or means3D.shape[1] != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
@@ -220,6 +225,10 @@ def _forward_native(rs, means3D, sh, colors_precomp, opacities, scales, rotation
         buf.scratch, buf.scratch_bytes = ws.scratch.data_ptr(), ws.scratch.numel()
         buf.num_rendered_host = ws.pinned.data_ptr()
         buf.num_rendered_event = ws.counted.cuda_event
+        if ws.acc_clear_for != (P, W, H):
+            ws.acc_clear_for = None          # this forward lays its buffers out differently: they may cover the zeros
+        if clear_accumulator:
+            buf.accumulator = _lib.ACC_CLEAR_IN_FORWARD
         out = GsrForwardOut(color.data_ptr(), invdepth.data_ptr(), radii.data_ptr())
 
         _lib.check(lib.gsr_forward_stage1(C.byref(p), C.byref(buf), C.byref(out), stream.cuda_stream))
@@ -234,6 +243,8 @@ def _forward_native(rs, means3D, sh, colors_precomp, opacities, scales, rotation
         binb = torch.empty(lib.gsr_bin_bytes(R), dtype=torch.uint8, device=device)
         buf.bin, buf.bin_bytes = binb.data_ptr(), binb.numel()
         _lib.check(lib.gsr_forward_stage2(C.byref(p), C.byref(buf), C.byref(out), R, stream.cuda_stream))
+        if clear_accumulator:
+            ws.acc_clear_for = (P, W, H)
         if state_out is not None:
             state_out.update(_inspect_state(lib, p, buf, R, geom, binb, img, stream))
     return R, color, radii, geom, binb, img, invdepth
@@ -324,6 +335,9 @@ def _backward_native(rs, means3D, radii, colors_precomp, opacities, scales, rota
         buf.bin, buf.bin_bytes = binb.data_ptr(), binb.numel()
         buf.scratch, buf.scratch_bytes = ws.scratch.data_ptr(), ws.scratch.numel()
         buf.num_rendered_host = ws.pinned.data_ptr()
+        if ws.acc_clear_for == (P, W, H):    # zeroed by the forward of a view of this size, untouched since
+            buf.accumulator = _lib.ACC_IS_CLEAR
+        ws.acc_clear_for = None              # this backward dirties it
 
         dL_dmeans2D = torch.empty((P, 3), **f32)
         names, shapes = _grad_layout(P, M, colors_precomp, cov3Ds_precomp, sh_c, scales, rotations, split)
@@ -401,7 +415,8 @@ class _RasterizeGaussians(torch.autograd.Function):
             xchg = hasattr(red, "use_exchange") and red.use_exchange(names)
             red.prepare(shapes, means3D.device, exchange_P=means3D.shape[0] if xchg else None)
         num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, invdepths = _forward_native(
-            raster_settings, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, dc=dc, raw=raw)
+            raster_settings, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, dc=dc, raw=raw,
+            clear_accumulator=any(ctx.needs_input_grad))
         ctx.raster_settings = raster_settings
         ctx.raw = raw
         ctx.num_rendered = num_rendered

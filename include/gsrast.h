@@ -110,7 +110,19 @@ typedef struct GsrBuffers {
     void*    num_rendered_event;           /* optional cudaEvent_t recorded by stage 1 right after the copy into
                                             * num_rendered_host: waiting on it (instead of the stream) lets the host
                                             * size `bin` while the device is still ordering the Gaussians */
+    int32_t  accumulator;                  /* GSR_ACC_* bits, 0 = the backward clears its accumulator itself */
+    int32_t  reserved2;
 } GsrBuffers;
+
+/* GsrBuffers.accumulator.  The backward sums per-Gaussian gradients into 12*P floats inside `scratch`, which must
+ * start from zero (the reference zero-fills its ten gradient tensors per call instead, rasterize_points.cu:186-204).
+ * GSR_ACC_CLEAR_IN_FORWARD (gsr_forward_stage2 / gsr_forward): the blend forward, which is bound by instruction
+ *   issue and leaves the memory system idle, also zeroes that accumulator.
+ * GSR_ACC_IS_CLEAR (gsr_backward): the accumulator is still zero, skip the memset.  Only valid when the LAST call
+ *   that used this scratch was a forward with GSR_ACC_CLEAR_IN_FORWARD and the same P, W, H (any other forward may
+ *   lay its own buffers over the same bytes; a backward leaves the accumulator dirty). */
+#define GSR_ACC_CLEAR_IN_FORWARD 1
+#define GSR_ACC_IS_CLEAR         2
 
 typedef struct GsrForwardOut {
     float*   out_color;     /* 3*H*W */

@@ -58,7 +58,7 @@ def test_struct_layouts_match_header():
         fields = [f.split("[")[0] for f in fields]          # array members: name[COUNT]
         assert fields == [f[0] for f in cls._fields_], name
     assert C.sizeof(_lib.GsrParams) == 12 * 4 + 12 * 8
-    assert C.sizeof(_lib.GsrBuffers) == 10 * 8
+    assert C.sizeof(_lib.GsrBuffers) == 11 * 8          # + accumulator flags
     assert C.sizeof(_lib.GsrSsimParams) == 2 * 8 + 8 * 4        # 7 ints/floats + tail padding
     assert C.sizeof(_lib.GsrLossParams) == 5 * 8 + 8 * 4
     assert C.sizeof(_lib.GsrDensifyPlanArgs) == 8 * 4 + 5 * 8

@@ -354,6 +354,58 @@ def test_workspace_regrowth_keeps_results(dgr):
     assert st["scratch_bytes"] > 0 and st["regrows"] >= 1
 
 
+def test_accumulator_cleared_by_the_forward_survives_interleaving(dgr):
+    """GSR_ACC_CLEAR_IN_FORWARD / GSR_ACC_IS_CLEAR (include/gsrast.h): the blend forward of a view that needs gradients
+    zeroes the backward's accumulator; the backward may only rely on that when nothing used the arena in between.
+    Forwards and backwards of views of different and of equal sizes interleaved on one stream must give the gradients
+    of the views run one after the other."""
+    from gaussian_splatting_b200 import rasterizer
+    from tests.helpers import settings_for
+    dev = torch.device("cuda", torch.cuda.current_device())
+    views = [small_scene(P=20000, W=320, H=240, seed=41), small_scene(P=15000, W=200, H=152, seed=42),
+             small_scene(P=20000, W=320, H=240, seed=43, bg=(0.2, 0.5, 0.1))]
+    ups = [_upstream(s["image_width"], s["image_height"], seed=7 + i) for i, (_, s) in enumerate(views)]
+    want = [run_module(dgr, gs, s, dc, dd)["grads"] for (gs, s), (dc, dd) in zip(views, ups)]
+    keys = ("means3D", "means2D", "opacities", "shs", "scales", "rotations")
+
+    def forward(i):
+        gs, s = views[i]
+        leaves = {k: v.cuda().clone().requires_grad_(True) for k, v in gs.items()}
+        m2 = torch.zeros(gs["means3D"].shape[0], 3, device="cuda", requires_grad=True)
+        color, radii, invd = dgr.GaussianRasterizer(settings_for(dgr, s))(
+            means3D=leaves["means3D"], means2D=m2, opacities=leaves["opacities"], shs=leaves["shs"],
+            scales=leaves["scales"], rotations=leaves["rotations"])
+        dc, dd = ups[i]
+        return leaves, m2, (color * dc.cuda()).sum() + (invd * dd.cuda()).sum()
+
+    def grads(leaves, m2):
+        g = {k: v.grad.cpu().numpy() for k, v in leaves.items()}
+        g["means2D"] = m2.grad.cpu().numpy()
+        return g
+
+    for order in ([0, 1], [0, 2], [1, 0, 2], [2, 2]):
+        fw = [forward(i) for i in order]
+        P, s = views[order[-1]][0]["means3D"].shape[0], views[order[-1]][1]
+        assert rasterizer._workspace(dev).acc_clear_for == (P, s["image_width"], s["image_height"])
+        for i, (leaves, m2, loss) in reversed(list(zip(order, fw))):
+            loss.backward()
+            assert rasterizer._workspace(dev).acc_clear_for is None
+            _check_grads(grads(leaves, m2), want[i], keys, tol=1e-4)
+    # a forward without gradients in between (other size: its buffers overlay the zeros; same size: they do not)
+    for other in (1, 2):
+        leaves, m2, loss = forward(0)
+        with torch.no_grad():
+            run_module(dgr, *views[other])
+        loss.backward()
+        _check_grads(grads(leaves, m2), want[0], keys, tol=1e-4)
+    # twice through the same graph: the second backward must clear the accumulator itself
+    leaves, m2, loss = forward(0)
+    loss.backward(retain_graph=True)
+    loss.backward()
+    g = grads(leaves, m2)
+    _check_grads({k: 0.5 * v for k, v in g.items()}, want[0], keys, tol=1e-4)
+
+
 # ---------------------------------------------------------------- multi-GPU (only where >= 2 GPUs are visible)
 def test_fused_multicast_reduction_matches_nccl():
     """tests/multi_gpu_check.py under torchrun: in-kernel NVLink-multicast gradient reduction vs NCCL."""
